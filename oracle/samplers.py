@@ -118,3 +118,10 @@ def gather_positions(indices, decoded_frames):
     ``pos = clamp(idx - min(idx), 0, decoded-1)``."""
     start = min(indices)
     return [max(0, min(i - start, decoded_frames - 1)) for i in indices]
+
+
+def pure_indices(method, total_frames, num_frames, rng=_random):
+    """visualize_sampling.py:105-178 -- the stand-alone copies: T is clamped to N first
+    (:116, :134, :158), then the N >= T formulas of a1 on the CPython stream."""
+    N = int(total_frames)
+    return dataset_indices(method, N, min(int(num_frames), N), rng)

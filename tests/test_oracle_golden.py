@@ -1,0 +1,116 @@
+"""The oracle against the golden vectors produced by executing the reference
+(tests/golden/make_golden.py).  CPU only."""
+import hashlib
+import random
+
+import numpy as np
+import pytest
+
+from oracle import patch_embed as ope
+from oracle import processors as op
+from oracle import resize as orz
+from oracle import samplers as osm
+
+METHODS = ["uniform", "random_window", "random"]
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def synth_video(seed, n, h, w, mode="noise"):
+    from lvc_b200.synth import synth_video as sv
+
+    return sv(seed, n, h, w, mode)
+
+
+def test_samplers_match_reference(golden):
+    g = golden("samplers.npz")
+    rows, want = g["rows"], g["indices"]
+    state = {}
+    bad = 0
+    for (copy, m, N, T, seed, call), w in zip(rows, want):
+        method = METHODS[m]
+        key = (copy, m, N, T, seed)
+        if copy in (0, 1):
+            if call == 0:
+                state[key] = random.Random(int(seed))
+            got = osm.dataset_indices(method, N, T, state[key])
+        elif copy == 2:
+            got = osm.dataset_indices(method, N, T, random.Random(42))
+        elif copy == 3:
+            got = osm.inference_indices_np(method, N, T, 42)
+        else:
+            got = osm.pure_indices(method, N, T, random.Random(int(seed)))
+        w = [int(v) for v in w if v >= 0]
+        bad += got != w
+    assert bad == 0
+
+
+def test_sample_frame_indices_matches_reference(golden):
+    g = golden("samplers.npz")
+    st = None
+    for (clip_len, rate, seg, seed, call), w in zip(g["a2_rows"], g["a2_indices"]):
+        if call == 0:
+            st = np.random.RandomState(int(seed))
+        got = osm.sample_frame_indices(int(clip_len), int(rate), int(seg), st)
+        assert got.tolist() == w[:clip_len].tolist()
+
+
+def test_cv2_restatement_matches_cv2(golden):
+    g = golden("resize.npz")
+    for i, (seed, h, w, ramp) in enumerate(g["cases"]):
+        img = synth_video(int(seed), 1, int(h), int(w), "ramp" if ramp else "noise")[0]
+        r = orz.cv2_resize_linear_u8(img)
+        assert sha(r) == str(g[f"cv2_sha_{i}"]), (i, h, w)
+    img = synth_video(31, 1, 720, 1280)[0]
+    for i, box in enumerate(g["roi_boxes"]):
+        r = op.resize_clip_cv2(img[None], [box])[0]
+        assert sha(r) == str(g[f"roi_sha_{i}"]), i
+
+
+def test_pil_restatement_matches_pillow(golden):
+    g = golden("resize.npz")
+    img = synth_video(41, 1, 224, 224)[0]
+    assert sha(orz.pil_resize_bilinear_u8(img, 256, 256)) == str(g["pil_sha_224_256"])
+
+
+def test_config1_recipe_matches_reference_predict_video(golden):
+    g = golden("pixels.npz")
+    for k in range(3):
+        seed, n, h, w, m, T = (int(v) for v in g[f"infer_case_{k}"])
+        vid = synth_video(seed, n, h, w)
+        idx = osm.inference_indices_np(METHODS[m], n, T, 42)
+        assert idx == g[f"infer_idx_{k}"].tolist()
+        x = op.manual_normalize(op.resize_clip_cv2(vid[idx]))[None]
+        assert sha(x) == str(g[f"infer_sha_{k}"])
+
+
+def test_hf_processors(golden):
+    g = golden("pixels.npz")
+    x = op.vivit_processor(synth_video(111, 4, 224, 224))[None]
+    assert list(x.shape) == g["vivit_shape"].tolist() and sha(x) == str(g["vivit_sha"])
+    fr = synth_video(112, 4, 224, 224)
+    for tag, (m, s) in {"045": (0.45, 0.225), "05": (0.5, 0.5)}.items():
+        x = op.videomae_processor(fr, (m,) * 3, (s,) * 3)[None]
+        assert sha(x) == str(g[f"videomae_sha_{tag}"]), tag
+
+
+def test_patch_embed_restatements(golden):
+    import torch
+
+    g = golden("embed.npz")
+
+    def sd(shape, seed, scale=1.0):
+        return torch.from_numpy((np.random.default_rng(seed).standard_normal(shape) * scale).astype(np.float32))
+
+    y = ope.vivit_tubelet_embed(sd((2, 4, 3, 64, 64), 3), sd((768, 3, 2, 16, 16), 1, 0.02), sd((768,), 2, 0.02))
+    assert np.allclose(y.numpy(), g["vivit_out"], atol=2e-5)
+    y, nf, pw = ope.timesformer_patch_embed(sd((2, 3, 3, 64, 64), 6), sd((768, 3, 16, 16), 4, 0.02), sd((768,), 5, 0.02))
+    assert np.allclose(y.numpy(), g["tsf_out"], atol=2e-5) and [nf, pw] == g["tsf_meta"].tolist()
+    w, b = sd((128, 3, 2, 4, 4), 7, 0.02), sd((128,), 8, 0.02)
+    lw, lb = 1 + sd((128,), 9, 0.1), sd((128,), 10, 0.1)
+    y = ope.swin_patch_embed(sd((2, 3, 4, 32, 32), 11), w, b, lw, lb)
+    assert np.allclose(y.numpy(), g["swin_out"], atol=5e-5)
+    y = ope.swin_patch_embed(sd((1, 3, 3, 30, 29), 12), w, b, lw, lb)
+    assert np.allclose(y.numpy(), g["swin_out_pad"], atol=5e-5)
