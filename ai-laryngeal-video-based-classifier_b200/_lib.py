@@ -1,0 +1,112 @@
+"""ctypes binding of liblvc_b200.so (the C ABI declared in include/lvc_b200.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` / ``make -C csrc``.  There is no
+fallback: a missing library raises ImportError with the build command.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblvc_b200.so")
+
+OK, E_INVAL, E_SHAPE, E_CUDA, E_ALIGN, E_NOTSUP = 0, -1, -2, -3, -4, -5
+SAMPLE = {"uniform": 0, "random_window": 1, "random": 2}
+VARIANT_DATASET, VARIANT_CLAMPED, VARIANT_NUMPY_INFER = 0, 1, 2
+LUT_DIV, LUT_MUL64 = 0, 1
+RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL = 0, 1, 2
+LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC = 0, 1, 2
+DT_F32, DT_BF16, DT_U8 = 0, 1, 2
+EMBED_VIVIT, EMBED_TIMESFORMER, EMBED_SWIN = 0, 1, 2
+
+
+class Rng(C.Structure):
+    _fields_ = [("mt", C.c_uint32 * 624), ("pos", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Video(C.Structure):
+    _fields_ = [("base", C.c_uint64), ("nbytes", C.c_int64), ("n_frames", C.c_int32),
+                ("height", C.c_int32), ("width", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ClipDesc(C.Structure):
+    _fields_ = [("resample", C.c_int32), ("layout", C.c_int32), ("out_dtype", C.c_int32),
+                ("out_size", C.c_int32), ("batch", C.c_int32), ("num_frames", C.c_int32),
+                ("max_width", C.c_int32), ("reserved", C.c_int32),
+                ("mean", C.c_float * 3), ("std", C.c_float * 3)]
+
+
+class EmbedDesc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("x_dtype", C.c_int32), ("x_layout", C.c_int32),
+                ("out_dtype", C.c_int32), ("batch", C.c_int32), ("frames", C.c_int32),
+                ("height", C.c_int32), ("width", C.c_int32), ("kt", C.c_int32), ("kh", C.c_int32),
+                ("kw", C.c_int32), ("embed_dim", C.c_int32), ("ln_eps", C.c_float),
+                ("reserved", C.c_int32)]
+
+
+_SIGS = {
+    "lvc_last_error": (C.c_char_p, []),
+    "lvc_version": (C.c_int, []),
+    "lvc_rng_seed_py": (C.c_int, [C.POINTER(Rng), C.c_uint64]),
+    "lvc_rng_seed_np": (C.c_int, [C.POINTER(Rng), C.c_uint32]),
+    "lvc_rng_random": (C.c_double, [C.POINTER(Rng)]),
+    "lvc_rng_u32": (C.c_uint32, [C.POINTER(Rng)]),
+    "lvc_sample_indices": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int32, C.POINTER(Rng),
+                                     C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
+    "lvc_sample_frame_indices": (C.c_int, [C.c_int32, C.c_double, C.c_int64, C.POINTER(Rng),
+                                           C.POINTER(C.c_int64)]),
+    "lvc_uniform_temporal_subsample": (C.c_int, [C.c_int64, C.c_int32, C.POINTER(C.c_int64)]),
+    "lvc_dynamic_fps": (C.c_double, [C.c_int64, C.c_int32, C.c_double]),
+    "lvc_build_lut": (C.c_int, [C.c_int, C.c_double, C.c_int, C.POINTER(C.c_float),
+                                C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "lvc_clip_forward": (C.c_int, [C.POINTER(ClipDesc), C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lvc_clip_launch_count": (C.c_int, [C.POINTER(ClipDesc)]),
+}
+# entry points added by later translation units; bound when the library exports them
+_OPTIONAL_SIGS = {
+    "lvc_patch_embed_workspace": (C.c_int64, [C.POINTER(EmbedDesc)]),
+    "lvc_patch_embed_pack_weights": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lvc_patch_embed": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lvc_patch_embed_launch_count": (C.c_int, [C.POINTER(EmbedDesc)]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library (loads on first use)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                f"or `make -C {os.path.join(_HERE, 'csrc')}` (there is no CPU fallback)")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in {**_SIGS, **_OPTIONAL_SIGS}.items():
+            try:
+                fn = getattr(l, name)
+            except AttributeError:
+                if name in _OPTIONAL_SIGS:
+                    continue
+                raise
+            fn.restype, fn.argtypes = res, args
+        _lib = l
+    return _lib
+
+
+def declared_symbols():
+    """Every entry point include/lvc_b200.h declares."""
+    return sorted({**_SIGS, **_OPTIONAL_SIGS})
+
+
+def check(status, what=""):
+    """Map a negative lvc_status to the exception the reference's Python seam would raise."""
+    if status == OK:
+        return
+    msg = lib().lvc_last_error().decode("utf-8", "replace")
+    if status in (E_INVAL, E_SHAPE, E_ALIGN):
+        raise ValueError(f"{what}: {msg}")
+    if status == E_NOTSUP:
+        raise NotImplementedError(f"{what}: {msg}")
+    raise RuntimeError(f"{what}: {msg}")

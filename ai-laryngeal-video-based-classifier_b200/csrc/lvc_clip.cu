@@ -1,0 +1,415 @@
+// Fused clip-construction kernel for sm_100a: frame gather by index -> optional ROI window ->
+// cv2-exact fixed-point bilinear resize to 224x224 -> LUT normalisation -> clip layout, one pass
+// over HBM.  Replaces (paths relative to the reference root)
+//   vivit_transformer/vivit_classifier/data_config/dataset.py:246-284   gather + cv2.resize loop
+//   resnet50-2d-lstm/inference.py:158-178                               resize + /255 + mean/std + permute
+//   vivit_transformer/vivit_classifier/trainers/trainer.py:62-95        image processor + torch.cat
+//
+// Design (DESIGN.md "clip kernel"): a persistent CTA per SM; one producer warp streams the TAPPED
+// source rows (2 of every ~scale rows; duplicates inside a stage are fetched once) into a
+// shared-memory ring with 1-D bulk async copies (cp.async.bulk, the TMA engine) completing on
+// mbarriers; 14 consumer warps (2 groups x 224 threads, one thread per output column, x taps in
+// registers for the whole frame) do the horizontal + vertical fixed-point passes out of shared
+// memory, look the result up in the float LUT and write coalesced 128-byte rows.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdlib>
+
+#include "lvc_internal.h"
+
+namespace {
+
+constexpr int S = 224;                    // output width/height
+constexpr int kGroups = 2;                // consumer groups working on different rows of a stage
+constexpr int kConsumers = kGroups * S;   // 448 threads = 14 warps
+constexpr int kThreads = 32 + kConsumers; // + 1 producer warp
+constexpr int kMaxRPS = 8;                // output rows per stage (2*RPS source-row slots <= 32 lanes)
+constexpr int kMaxStages = 16;
+
+struct RowDesc {  // one output row of a stage
+  int off0, off1; // byte offsets in the ring of source pixel (x_origin, y0) / (x_origin, y1)
+  int b0, b1;     // 11-bit vertical coefficients
+};
+struct StageHdr {
+  int frame;      // output frame id b*T + t
+  int sw;         // source window width (pixels)
+  int oy0;        // first output row of this stage
+  int flags;      // bit 0: exact 2x2 down-scale (cv::resize switches to INTER_AREA)
+  RowDesc rows[kMaxRPS];
+};
+
+struct ClipParams {
+  const lvc_video* videos;
+  const int32_t* indices;
+  const int32_t* boxes;
+  const float* lut;
+  void* out;
+  unsigned long long* stats;
+  int T;
+  int layout, out_dtype;
+  int bands, rows_per_band;  // bands per frame, output rows per band
+  int total_items;           // B*T*bands
+  int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
+};
+
+// ---- PTX wrappers -------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
+// Source rows are read once: evict-first L2 policy.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar,
+                                         uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
+// OpenCV INTER_LINEAR tap for destination coordinate d: fx = (float)((d+0.5)*scale - 0.5) in
+// double without contraction, then floor / fraction in float (cv::resize table set-up).
+__device__ __forceinline__ void cv_tap(int d, double scale, int& s, float& fr) {
+  float f = (float)__dadd_rn(__dmul_rn((double)d + 0.5, scale), -0.5);
+  float fl = floorf(f);
+  s = (int)fl;
+  fr = __fsub_rn(f, fl);
+}
+__device__ __forceinline__ double cv_scale(int src) {
+  double inv = __ddiv_rn((double)S, (double)src);
+  return __ddiv_rn(1.0, inv);
+}
+__device__ __forceinline__ int coef(float w) { return __float2int_rn(__fmul_rn(w, 2048.0f)); }
+
+}  // namespace
+
+namespace {
+
+// Shared memory map: [0,256) full/empty mbarriers | StageHdr[kMaxStages] | LUT 3x256 f32 | ring.
+constexpr int kHdrOff = 256;
+constexpr int kLutOff = kHdrOff + kMaxStages * (int)sizeof(StageHdr);
+constexpr int kRingOff = (kLutOff + 3 * 256 * 4 + 127) / 128 * 128;
+
+__global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_constant__ ClipParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + kMaxStages;
+  StageHdr* hdrs = reinterpret_cast<StageHdr*>(smem + kHdrOff);
+  float* lut = reinterpret_cast<float*>(smem + kLutOff);
+  uint8_t* ring = smem + kRingOff;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int stages_per_item = p.rows_per_band / p.rps;
+
+  if (tid == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kConsumers / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (p.lut)
+    for (int i = tid; i < 3 * 256; i += kThreads) lut[i] = p.lut[i];
+  __syncthreads();
+
+  if (warp == 0) {
+    // ================= producer warp: lane j fetches source row (j&1 ? y1 : y0) of output row j>>1
+    const uint64_t policy = policy_evict_first();
+    const int nrows = 2 * p.rps;
+    const unsigned lanes = nrows >= 32 ? 0xffffffffu : ((1u << nrows) - 1u);
+    uint32_t it = 0;
+    for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+      const int f = item / p.bands, band = item - f * p.bands;
+      const int b = f / p.T;
+      const lvc_video v = p.videos[b];
+      int idx = p.indices[f];
+      idx = min(max(idx, 0), v.n_frames - 1);
+      int ox = 0, oy = 0, sw = v.width, sh = v.height;
+      if (p.boxes) {
+        const int4 bx = reinterpret_cast<const int4*>(p.boxes)[f];
+        if (bx.x >= 0) {  // numpy half-open slice of the box clipped to the frame, at least 1x1
+          ox = min(max(bx.x, 0), v.width - 1);
+          oy = min(max(bx.y, 0), v.height - 1);
+          sw = min(max(bx.z, ox + 1), v.width) - ox;
+          sh = min(max(bx.w, oy + 1), v.height) - oy;
+        }
+      }
+      const bool area = (sw == 2 * S) && (sh == 2 * S);
+      const double scale_y = cv_scale(sh);
+      const uint64_t row_bytes = (uint64_t)v.width * 3u;
+      const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
+      const uint64_t buf_end = v.base + (uint64_t)v.nbytes;
+      for (int st = 0; st < stages_per_item; ++st, ++it) {
+        const int slot = it % p.stages;
+        const uint32_t phase = (it / p.stages) & 1u;
+        const int oy_first = band * p.rows_per_band + st * p.rps;
+        if (lane == 0) mbar_wait(&empty[slot], phase ^ 1u);
+        __syncwarp();
+        uint32_t my_bytes = 0, bulk_bytes = 0;
+        int my_off = 0, cb = 0;
+        uint64_t a = 0;
+        bool leader = false;
+        uint8_t* stage_base = ring + (size_t)slot * nrows * p.pitch;
+        if (lane < nrows) {
+          const int r = lane >> 1, oyr = oy_first + r;
+          int sy; float fr;
+          cv_tap(oyr, scale_y, sy, fr);
+          int ysrc;
+          if (area) { ysrc = 2 * oyr + (lane & 1); cb = 0; }
+          else {
+            ysrc = min(max(sy + (lane & 1), 0), sh - 1);
+            cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
+          }
+          const uint64_t addr = frame_base + (uint64_t)(oy + ysrc) * row_bytes + (uint64_t)ox * 3u;
+          a = addr & ~(uint64_t)15;
+          const uint32_t shift = (uint32_t)(addr - a);
+          my_bytes = (shift + (uint32_t)sw * 3u + 15u) & ~15u;
+          if (my_bytes > (uint32_t)p.pitch) __trap();  // video wider than desc.max_width
+          const unsigned same = __match_any_sync(lanes, ysrc);
+          const int lead = __ffs(same) - 1;
+          leader = (lead == lane);
+          my_off = (int)(stage_base - ring) + lead * p.pitch + (int)shift;
+          bulk_bytes = my_bytes;
+          if (a + my_bytes > buf_end) bulk_bytes = (uint32_t)((buf_end - a) & ~(uint64_t)15);
+          if (!leader) bulk_bytes = 0;
+        }
+        uint32_t total = bulk_bytes;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        const int off_next = __shfl_down_sync(0xffffffffu, my_off, 1);
+        const int cb_next = __shfl_down_sync(0xffffffffu, cb, 1);
+        StageHdr* h = &hdrs[slot];
+        if (lane < nrows && !(lane & 1)) {
+          RowDesc rd;
+          rd.off0 = my_off; rd.off1 = off_next; rd.b0 = cb; rd.b1 = cb_next;
+          h->rows[lane >> 1] = rd;
+        }
+        if (lane == 0) { h->frame = f; h->sw = sw; h->oy0 = oy_first; h->flags = area ? 1 : 0; }
+        if (leader && bulk_bytes < my_bytes) {
+          // last bytes of the buffer: not a whole 16-byte granule, copy them by hand
+          uint8_t* slot_ptr = stage_base + (size_t)lane * p.pitch;
+          for (uint64_t q = a + bulk_bytes; q < buf_end && q < a + my_bytes; ++q)
+            slot_ptr[q - a] = *reinterpret_cast<const uint8_t*>(q);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_expect_tx(&full[slot], total);
+        __syncwarp();
+        if (leader && bulk_bytes)
+          bulk_g2s(stage_base + (size_t)lane * p.pitch, reinterpret_cast<const void*>(a), bulk_bytes,
+                   &full[slot], policy);
+      }
+    }
+    return;
+  }
+
+  // ================= consumer warps: thread -> output column x, group -> rows g, g+G, ...
+  const int ct = tid - 32;
+  const int g = ct / S;
+  const int x = ct - g * S;
+  int cached_sw = -1, cached_flags = -1;
+  int xo = 0, d1 = 0, a0 = 0, a1 = 0;
+  unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
+  int acc_b = -1;
+  uint32_t it = 0;
+  const size_t plane = (size_t)S * S;
+  for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+    for (int st = 0; st < stages_per_item; ++st, ++it) {
+      const int slot = it % p.stages;
+      mbar_wait(&full[slot], (it / p.stages) & 1u);
+      const StageHdr* h = &hdrs[slot];
+      const int f = h->frame, sw = h->sw, flags = h->flags, oy0 = h->oy0;
+      if (sw != cached_sw || flags != cached_flags) {
+        cached_sw = sw; cached_flags = flags;
+        if (flags & 1) { xo = 6 * x; d1 = 3; a0 = 1; a1 = 1; }
+        else {
+          int sx; float fr;
+          cv_tap(x, cv_scale(sw), sx, fr);
+          if (sx < 0) { sx = 0; fr = 0.f; }
+          if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }
+          a0 = coef(__fsub_rn(1.0f, fr));
+          a1 = coef(fr);
+          xo = 3 * sx;
+          d1 = (sx + 1 <= sw - 1) ? 3 : 0;
+        }
+      }
+      const int b = f / p.T, t = f - b * p.T;
+      if (p.stats && b != acc_b) {
+        if (acc_b >= 0) {
+#pragma unroll
+          for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+          if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
+        }
+        acc = 0; acc_b = b;
+      }
+      // element offsets of channel 0 of this frame and the channel stride
+      size_t base, cstride;
+      if (p.layout == LVC_LAYOUT_BTCHW) { base = (size_t)f * 3 * plane; cstride = plane; }
+      else if (p.layout == LVC_LAYOUT_BCTHW) { base = ((size_t)b * 3 * p.T + t) * plane; cstride = (size_t)p.T * plane; }
+      else { base = (size_t)f * plane * 3; cstride = 1; }
+      for (int r = g; r < p.rps; r += kGroups) {
+        const RowDesc rd = h->rows[r];
+        const uint8_t* p0 = ring + rd.off0 + xo;
+        const uint8_t* p1 = ring + rd.off1 + xo;
+        int v[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const int p00 = p0[c], p01 = p0[c + d1], p10 = p1[c], p11 = p1[c + d1];
+          if (flags & 1) {
+            v[c] = (p00 + p01 + p10 + p11 + 2) >> 2;
+          } else {
+            const int s0 = a0 * p00 + a1 * p01;
+            const int s1 = a0 * p10 + a1 * p11;
+            v[c] = (((rd.b0 * (s0 >> 4)) >> 16) + ((rd.b1 * (s1 >> 4)) >> 16) + 2) >> 2;
+          }
+        }
+        acc += (unsigned)(v[0] + v[1] + v[2]);
+        const int oyr = oy0 + r;
+        if (p.out_dtype == LVC_DT_F32) {
+          float* o = reinterpret_cast<float*>(p.out) + base + (size_t)oyr * S + x;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
+        } else if (p.out_dtype == LVC_DT_BF16) {
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + base + (size_t)oyr * S + x;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(lut[c * 256 + v[c]]);
+        } else {
+          uint8_t* o = reinterpret_cast<uint8_t*>(p.out);
+          if (p.layout == LVC_LAYOUT_BTHWC) {
+            o += base + ((size_t)oyr * S + x) * 3;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o[c] = (uint8_t)v[c];
+          } else {
+            o += base + (size_t)oyr * S + x;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+    }
+  }
+  if (p.stats && acc_b >= 0) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+namespace {
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+struct DeviceInfo {
+  int sms = 0, max_smem = 0;
+  cudaError_t err = cudaSuccess;
+};
+const DeviceInfo& device_info() {
+  static thread_local DeviceInfo di;
+  static thread_local int cached_dev = -1;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e == cudaSuccess && dev != cached_dev) {
+    e = cudaDeviceGetAttribute(&di.sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&di.max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e == cudaSuccess) cached_dev = dev;
+  }
+  di.err = e;
+  return di;
+}
+
+}  // namespace
+
+extern "C" int lvc_clip_launch_count(const lvc_clip_desc* d) { return d ? 1 : 0; }
+
+extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
+                                const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
+                                void* stream) {
+  if (!d || !videos || !indices || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: NULL argument");
+  if (d->out_size != S) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: out_size %d unsupported (224 only)", d->out_size);
+  if (d->batch <= 0 || d->num_frames <= 0 || d->max_width <= 0)
+    return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: batch, num_frames and max_width must be positive");
+  if (d->layout < LVC_LAYOUT_BTCHW || d->layout > LVC_LAYOUT_BTHWC || d->out_dtype < LVC_DT_F32 || d->out_dtype > LVC_DT_U8)
+    return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: unknown layout or dtype");
+  if (d->layout == LVC_LAYOUT_BTHWC && d->out_dtype != LVC_DT_U8)
+    return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: BTHWC layout is the uint8 Dataset clip only");
+  if (d->out_dtype != LVC_DT_U8 && !lut && d->resample != LVC_RESAMPLE_PTV_EVAL)
+    return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: float output needs a LUT (lvc_build_lut)");
+  if (d->resample != LVC_RESAMPLE_CV2)
+    return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: resample mode %d not implemented", d->resample);
+  if (boxes && (reinterpret_cast<uintptr_t>(boxes) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: boxes must be 16-byte aligned");
+  if ((int64_t)d->batch * d->num_frames > (1 << 24)) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: too many frames in one call");
+
+  const DeviceInfo& di = device_info();
+  if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "lvc_clip_forward: no usable CUDA device: %s", cudaGetErrorString(di.err));
+
+  ClipParams p{};
+  p.videos = videos; p.indices = indices; p.boxes = boxes; p.lut = lut; p.out = out;
+  p.stats = reinterpret_cast<unsigned long long*>(stats);
+  p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
+  // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)
+  p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
+  p.rps = env_int("LVC_CLIP_RPS", 4);
+  if (p.rps < kGroups || p.rps > kMaxRPS || (p.rps % kGroups) || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
+  const int smem_budget = std::min(di.max_smem, env_int("LVC_CLIP_SMEM_KB", 200) * 1024);
+  int stage_bytes = 2 * p.rps * p.pitch;
+  while ((smem_budget - kRingOff) / stage_bytes < 2 && p.rps > kGroups) { p.rps -= kGroups; while (S % p.rps) p.rps -= kGroups; stage_bytes = 2 * p.rps * p.pitch; }
+  p.stages = std::min(kMaxStages, (smem_budget - kRingOff) / stage_bytes);
+  if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: max_width %d does not fit the shared-memory ring", d->max_width);
+  const size_t smem = (size_t)kRingOff + (size_t)p.stages * stage_bytes;
+
+  const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)di.max_smem / (smem + 1024)));
+  const int grid_max = di.sms * ctas_per_sm;
+  const int frames = d->batch * d->num_frames;
+  // band = output rows per work item: the largest divisor of 224 that still leaves >= 8 items per CTA
+  static const int kBands[] = {224, 112, 56, 32, 28, 16, 8, 4, 2};
+  p.rows_per_band = p.rps;
+  const int forced = env_int("LVC_CLIP_BAND", 0);
+  for (int rb : kBands) {
+    if (rb % p.rps) continue;
+    if (forced ? rb == forced : (int64_t)frames * (S / rb) >= 8LL * grid_max) { p.rows_per_band = rb; break; }
+  }
+  p.bands = S / p.rows_per_band;
+  p.total_items = frames * p.bands;
+  const int grid = std::min(p.total_items, grid_max);
+
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_cv2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lvc_clip_cv2_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}

@@ -1,0 +1,195 @@
+/* lvc_b200 -- C ABI of the B200-native clip-construction path.
+ *
+ * The reference (shaunliewsmu/ai-laryngeal-video-based-classifier) is pure Python and has no
+ * FFI; its seams for this path are Python call signatures.  Each entry point
+ * below names the reference interface it replaces (paths relative to the reference root).
+ * INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions: every function returns 0 (LVC_OK) or a negative lvc_status; lvc_last_error()
+ * returns a thread-local message for the last failure.  No ownership transfer: all buffers
+ * are caller-allocated.  Device work is enqueued on the caller's stream (a cudaStream_t passed
+ * as void*) and never synchronises.  There is no CPU fallback: without a CUDA device the
+ * device entry points return LVC_E_CUDA.
+ */
+#ifndef LVC_B200_H
+#define LVC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  LVC_OK = 0,
+  LVC_E_INVAL = -1,  /* bad argument (NULL, negative size, unknown enum) */
+  LVC_E_SHAPE = -2,  /* shape the kernels do not support (e.g. output size != 224) */
+  LVC_E_CUDA = -3,   /* CUDA runtime / driver error, message in lvc_last_error() */
+  LVC_E_ALIGN = -4,  /* pointer alignment requirement violated */
+  LVC_E_NOTSUP = -5
+} lvc_status;
+
+const char* lvc_last_error(void);
+int lvc_version(void);
+
+/* ------------------------------------------------------------------ samplers (host) ---- */
+
+/* MT19937 state shared by the CPython-`random` and numpy-legacy emulations. */
+typedef struct {
+  uint32_t mt[624];
+  int32_t pos;
+  int32_t reserved;
+} lvc_rng;
+
+/* random.seed(int)  -- e.g. vivit_transformer/vivit_classifier/data_config/dataset.py:39,
+ * resnet50-2d-lstm/src/data_config/dataset.py:97 (init_by_array on |seed|). */
+int lvc_rng_seed_py(lvc_rng* st, uint64_t seed);
+/* np.random.seed(int) -- resnet50-2d-lstm/inference.py:77,114 (init_genrand). */
+int lvc_rng_seed_np(lvc_rng* st, uint32_t seed);
+/* random.random() / next 32-bit word, exposed for tests of the stream itself. */
+double lvc_rng_random(lvc_rng* st);
+uint32_t lvc_rng_u32(lvc_rng* st);
+
+enum { LVC_SAMPLE_UNIFORM = 0, LVC_SAMPLE_RANDOM_WINDOW = 1, LVC_SAMPLE_RANDOM = 2 };
+enum {
+  /* VideoDataset.get_sampling_indices: vivit .../data_config/dataset.py:129-193 and its copies
+   * (timesformer :137-207, swin :64-149, resnet50-3d-video :79-169, resnet50-2d-lstm :85-163).
+   * CPython stream; short videos (N < T) use the duplicate-allowing branch. */
+  LVC_VARIANT_DATASET = 0,
+  /* visualize_sampling.py:105-178: T clamped to N, CPython stream. */
+  LVC_VARIANT_CLAMPED = 1,
+  /* resnet50-2d-lstm/inference.py:74-130: T clamped to N, numpy legacy stream
+   * (np.random.choice without replacement / np.random.randint). */
+  LVC_VARIANT_NUMPY_INFER = 2
+};
+
+/* Writes *n_out (<= num_frames) indices to out[num_frames].  `st` is consumed exactly like the
+ * reference consumes its global stream; may be NULL for LVC_SAMPLE_UNIFORM. */
+int lvc_sample_indices(int method, int variant, int64_t total_frames, int32_t num_frames,
+                       lvc_rng* st, int64_t* out, int32_t* n_out);
+/* data_handling.py:41-56 sample_frame_indices(clip_len, frame_sample_rate, seg_len); numpy stream. */
+int lvc_sample_frame_indices(int32_t clip_len, double frame_sample_rate, int64_t seg_len,
+                             lvc_rng* st, int64_t* out);
+/* pytorchvideo UniformTemporalSubsample(T) index rule (videoswintransformer/.../dataset.py:157):
+ * clamp(linspace_f32(0, t-1, T), 0, t-1).long(). */
+int lvc_uniform_temporal_subsample(int64_t t, int32_t num_samples, int64_t* out);
+/* Swin copy's second return value (videoswintransformer/.../dataset.py:104-121); NaN = None. */
+double lvc_dynamic_fps(int64_t total_frames, int32_t num_frames, double original_fps);
+
+/* -------------------------------------------------- normalisation look-up table (host) ---- */
+
+enum {
+  /* f32(x) / f32(scale)      -- resnet50-2d-lstm/inference.py:166-167 (`astype(float32) / 255.0`) */
+  LVC_LUT_DIV = 0,
+  /* f32(f64(x) * scale)      -- transformers image_transforms.rescale as called by
+   *                             VivitImageProcessor (scale 1/127.5, offset) and the VideoMAE-class
+   *                             processor (scale 1/255): vivit .../trainers/trainer.py:77,
+   *                             timesformer .../trainers/trainer.py:91-98 */
+  LVC_LUT_MUL64 = 1
+};
+/* out[c*256 + v] = ((rescale(v) [- 1 if offset]) - mean[c]) / std[c], every step rounded to
+ * float32 in the reference's order, so a uint8 input gives the reference's float32 bit for bit. */
+int lvc_build_lut(int kind, double scale, int offset, const float mean[3], const float std[3],
+                  float* out /* [3*256] host */);
+
+/* --------------------------------------------------------------- fused clip kernel ---- */
+
+/* One decoded video resident in device memory: uint8 RGB, (n_frames, height, width, 3) contiguous.
+ * `base` must be 16-byte aligned; `nbytes` is the readable size of the buffer. */
+typedef struct {
+  uint64_t base;
+  int64_t nbytes;
+  int32_t n_frames;
+  int32_t height;
+  int32_t width;
+  int32_t reserved;
+} lvc_video;
+
+enum {
+  /* cv2.resize(frame, (224,224)) INTER_LINEAR uint8, bit-exact (vivit .../dataset.py:275,
+   * resnet50-2d-lstm/inference.py:162), then the LUT. */
+  LVC_RESAMPLE_CV2 = 0,
+  /* LVC_RESAMPLE_CV2 followed on-chip by the VivitImageProcessor geometry: Pillow BILINEAR
+   * 224->256 and centre crop 224 (vivit .../trainers/trainer.py:77), then the LUT. */
+  LVC_RESAMPLE_CV2_PIL256 = 1,
+  /* pytorchvideo eval chain on float frames: ShortSideScale(256) via torch bilinear
+   * (align_corners=False), CenterCrop(224), (x-mean)/std without /255
+   * (videoswintransformer/.../dataset.py:164-172).  Uses mean/std, not the LUT. */
+  LVC_RESAMPLE_PTV_EVAL = 2
+};
+enum { LVC_LAYOUT_BTCHW = 0, LVC_LAYOUT_BCTHW = 1, LVC_LAYOUT_BTHWC = 2 };
+enum { LVC_DT_F32 = 0, LVC_DT_BF16 = 1, LVC_DT_U8 = 2 };
+
+typedef struct {
+  int32_t resample;   /* LVC_RESAMPLE_* */
+  int32_t layout;     /* LVC_LAYOUT_*; BTHWC only with LVC_DT_U8 (the Dataset's uint8 clip,
+                         vivit .../dataset.py:287-292) */
+  int32_t out_dtype;  /* LVC_DT_* ; U8 = resized bytes before normalisation */
+  int32_t out_size;   /* 224 */
+  int32_t batch;      /* B clips, one per video entry */
+  int32_t num_frames; /* T */
+  int32_t max_width;  /* largest frame width (pixels) among the B videos: sizes the shared-memory
+                         row slots.  A wider video in `videos` is a contract violation (the kernel
+                         traps). */
+  int32_t reserved;
+  float mean[3];      /* PTV_EVAL only */
+  float std[3];
+} lvc_clip_desc;
+
+/* Replaces, for a batch of B videos: the gather (vivit .../dataset.py:246-268), the per-frame
+ * cv2.resize loop (:271-277), the image-processor call in _process_batch
+ * (vivit .../trainers/trainer.py:62-95) or the manual normalise + permute
+ * (resnet50-2d-lstm/inference.py:166-178), and the collate (model_configuration.py:11-31).
+ *   videos   device  lvc_video[B]
+ *   indices  device  int32[B*T]   frame index per output frame (clamped to the video)
+ *   boxes    device  int32[B*T*4] xyxy ROI per output frame (src/yolo_detector.py:76-85), x1 < 0 =
+ *                    no detection = full frame; NULL = no ROI
+ *   lut      device  float[3*256] from lvc_build_lut (ignored for PTV_EVAL / U8 output)
+ *   out      device  B*T*3*224*224 elements of out_dtype in `layout`
+ *   stats    device  uint64[B] or NULL: += sum of the clip's resized uint8 samples (checksum)
+ */
+int lvc_clip_forward(const lvc_clip_desc* desc, const lvc_video* videos, const int32_t* indices,
+                     const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
+                     void* stream);
+
+/* Number of kernel launches lvc_clip_forward enqueues for this descriptor (for accounting). */
+int lvc_clip_launch_count(const lvc_clip_desc* desc);
+
+/* ------------------------------------------------------------ patch / tubelet embedding ---- */
+
+enum {
+  LVC_EMBED_VIVIT = 0,       /* VivitTubeletEmbeddings: Conv3d(3,E,k=s=(2,16,16)); vivit_model.py:27-41 */
+  LVC_EMBED_TIMESFORMER = 1, /* TimesformerPatchEmbeddings: Conv2d(3,E,k=s=16); timesformer_model.py:27-42 */
+  LVC_EMBED_SWIN = 2         /* PatchEmbed3d: Conv3d(3,E,k=s=(2,4,4)) + LayerNorm(E); swin3d.py:22-44 */
+};
+
+typedef struct {
+  int32_t kind;      /* LVC_EMBED_* */
+  int32_t x_dtype;   /* LVC_DT_F32 or LVC_DT_BF16 */
+  int32_t x_layout;  /* LVC_LAYOUT_BTCHW (HF models) or LVC_LAYOUT_BCTHW (torchvision swin) */
+  int32_t out_dtype; /* LVC_DT_BF16 or LVC_DT_F32 */
+  int32_t batch, frames, height, width; /* B, T, H, W of x; channels are 3 */
+  int32_t kt, kh, kw; /* patch size: (2,16,16) / (1,16,16) / (2,4,4) */
+  int32_t embed_dim;  /* N: 768 / 768 / 128 */
+  float ln_eps;       /* SWIN: LayerNorm eps (1e-5); ignored otherwise */
+  int32_t reserved;
+} lvc_embed_desc;
+
+/* Bytes of device scratch lvc_patch_embed needs (the bf16 token-major patch matrix A[M][K]). */
+int64_t lvc_patch_embed_workspace(const lvc_embed_desc* d);
+/* Packs conv weights (E, 3, kt, kh, kw) fp32 (device) into the bf16 [N][K] K-major operand the
+ * tcgen05 GEMM reads; call once per weight update. */
+int lvc_patch_embed_pack_weights(const lvc_embed_desc* d, const float* w_f32, void* w_packed_bf16,
+                                 void* stream);
+/* out[M][N] = patches(x)[M][K] . W[K][N] + bias (+ LayerNorm for SWIN), token order as the
+ * reference modules produce it: VIVIT (B, T/2*H/16*W/16, E); TIMESFORMER (B*T, H/16*W/16, E);
+ * SWIN (B, T/2, H/4, W/4, E).  x, w_packed, bias, ln_w, ln_b, out, workspace: device pointers. */
+int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const void* w_packed_bf16,
+                    const float* bias, const float* ln_w, const float* ln_b, void* out,
+                    void* workspace, void* stream);
+int lvc_patch_embed_launch_count(const lvc_embed_desc* d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LVC_B200_H */
