@@ -1,0 +1,172 @@
+"""Clip construction on the GPU: the Python face of ``lvc_clip_forward``.
+
+``ClipBuilder`` turns B decoded videos resident in HBM (uint8 ``(N, H, W, 3)`` CUDA tensors) plus a
+``(B, T)`` index table (and optional per-frame ROI boxes) into one clip tensor in the layout and
+normalisation of a reference recipe, in a single fused kernel launch.  Presets:
+
+  resnet_infer  cv2.resize 224 -> /255 -> (x-0.45)/0.225 -> (B,C,T,H,W)   resnet50-2d-lstm/inference.py:158-178
+  timesformer   cv2.resize 224 -> VideoMAE-class processor -> (B,T,C,H,W) timesformer .../trainers/trainer.py:91-98
+  vivit         cv2.resize 224 -> VivitImageProcessor -> (B,T,C,H,W)      vivit .../trainers/trainer.py:62-95
+  dataset_u8    cv2.resize 224 -> uint8 (B,T,H,W,3)                       vivit .../dataset.py:271-292
+  ptv_eval      ShortSideScale(256)+CenterCrop(224)+Normalize (float)     videoswintransformer/.../dataset.py:164-172
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+IMAGENET_STANDARD = ((0.5, 0.5, 0.5), (0.5, 0.5, 0.5))
+KINETICS = ((0.45, 0.45, 0.45), (0.225, 0.225, 0.225))
+
+_LAYOUTS = {"BTCHW": _lib.LAYOUT_BTCHW, "BCTHW": _lib.LAYOUT_BCTHW, "BTHWC": _lib.LAYOUT_BTHWC}
+_DTYPES = {torch.float32: _lib.DT_F32, torch.bfloat16: _lib.DT_BF16, torch.uint8: _lib.DT_U8}
+
+# name -> (resample, lut kind, lut scale, offset, (mean, std), layout, dtype)
+PRESETS = {
+    "resnet_infer": (_lib.RESAMPLE_CV2, _lib.LUT_DIV, 255.0, False, KINETICS, "BCTHW", torch.float32),
+    "timesformer": (_lib.RESAMPLE_CV2, _lib.LUT_MUL64, 1 / 255, False, KINETICS, "BTCHW", torch.float32),
+    "vivit": (_lib.RESAMPLE_CV2_PIL256, _lib.LUT_MUL64, 1 / 127.5, True, IMAGENET_STANDARD, "BTCHW", torch.float32),
+    "dataset_u8": (_lib.RESAMPLE_CV2, None, 0.0, False, KINETICS, "BTHWC", torch.uint8),
+    "ptv_eval": (_lib.RESAMPLE_PTV_EVAL, None, 0.0, False, KINETICS, "BCTHW", torch.float32),
+}
+
+
+def build_lut(kind, scale, offset, mean, std):
+    """(3, 256) float32 host tensor: the reference's normalisation of every uint8 value, bit-exact."""
+    out = np.empty(768, np.float32)
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*std)
+    _lib.check(_lib.lib().lvc_build_lut(kind, float(scale), int(bool(offset)), m, s,
+                                        out.ctypes.data_as(C.POINTER(C.c_float))), "build_lut")
+    return torch.from_numpy(out).view(3, 256)
+
+
+def _shape(layout, B, T, S=224):
+    return {"BTCHW": (B, T, 3, S, S), "BCTHW": (B, 3, T, S, S), "BTHWC": (B, T, S, S, 3)}[layout]
+
+
+class ClipBuilder:
+    """Callable that builds clips with one fused kernel launch per batch.
+
+    Parameters mirror what the reference recipes fix: ``preset`` picks the resampler and the
+    normalisation; ``mean``/``std`` override the preset's (the TimeSformer checkpoint's values are
+    not available offline); ``layout``/``dtype`` override the output format.
+    """
+
+    def __init__(self, preset="resnet_infer", num_frames=32, mean=None, std=None, layout=None, dtype=None,
+                 device=None):
+        if preset not in PRESETS:
+            raise ValueError(f"unknown preset {preset!r}; choose from {sorted(PRESETS)}")
+        if not torch.cuda.is_available():
+            raise RuntimeError("lvc_b200.ClipBuilder needs a CUDA device (there is no CPU fallback)")
+        rs, kind, scale, offset, (m, s), lay, dt = PRESETS[preset]
+        self.preset, self.resample, self.num_frames = preset, rs, int(num_frames)
+        self.mean = tuple(float(v) for v in (mean if mean is not None else m))
+        self.std = tuple(float(v) for v in (std if std is not None else s))
+        self.layout = layout or lay
+        self.dtype = dtype or dt
+        if self.layout not in _LAYOUTS or self.dtype not in _DTYPES:
+            raise ValueError(f"unsupported layout/dtype {self.layout}/{self.dtype}")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.lut = None
+        if kind is not None:
+            self.lut = build_lut(kind, scale, offset, self.mean, self.std).to(self.device)
+        _lib.lib()  # fail now, loudly, if the CUDA library is missing
+        self.launches = 0
+
+    # -- host-side packing of the small per-batch tables into ONE pinned upload ------------------
+    def _tables(self, videos, indices, boxes):
+        B, T = len(videos), self.num_frames
+        idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int32).reshape(B, T))
+        nb = 0 if boxes is None else B * T * 16
+        vt_bytes = B * C.sizeof(_lib.Video)
+        off_idx = (vt_bytes + 15) // 16 * 16
+        off_box = (off_idx + idx.nbytes + 15) // 16 * 16
+        host = torch.empty(off_box + nb, dtype=torch.uint8).pin_memory()
+        hv = host.numpy()
+        vt = (_lib.Video * B).from_buffer(hv)  # writes straight into the pinned buffer
+        max_w = 0
+        for i, v in enumerate(videos):
+            if v.dtype != torch.uint8 or v.dim() != 4 or v.shape[-1] != 3 or not v.is_cuda or not v.is_contiguous():
+                raise ValueError("each video must be a contiguous CUDA uint8 tensor of shape (N, H, W, 3)")
+            if v.data_ptr() % 16:
+                raise ValueError("video storage must be 16-byte aligned")
+            vt[i].base, vt[i].nbytes = v.data_ptr(), v.numel()
+            vt[i].n_frames, vt[i].height, vt[i].width = v.shape[0], v.shape[1], v.shape[2]
+            max_w = max(max_w, v.shape[2])
+        hv[off_idx:off_idx + idx.nbytes] = idx.view(np.uint8).reshape(-1)
+        if boxes is not None:
+            bx = np.ascontiguousarray(np.asarray(boxes, dtype=np.int32).reshape(B, T, 4))
+            hv[off_box:off_box + nb] = bx.view(np.uint8).reshape(-1)
+        dev = host.to(self.device, non_blocking=True)
+        p = dev.data_ptr()
+        return dev, host, p, p + off_idx, (p + off_box if boxes is not None else None), max_w
+
+    def prepare(self, videos, indices, boxes=None):
+        """Upload the per-batch tables (video descriptors, indices, boxes: a few KB, one pinned copy)
+        and return a ``ClipBatch`` that ``run`` can launch any number of times."""
+        B, T = len(videos), self.num_frames
+        tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes)
+        d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, 0,
+                          (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std))
+        return ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos), _shape(self.layout, B, T))
+
+    def run(self, batch, out=None, stats=None):
+        """Enqueue the fused kernel for a prepared batch on the current stream (no synchronisation)."""
+        if out is None:
+            out = torch.empty(batch.shape, dtype=self.dtype, device=self.device)
+        elif tuple(out.shape) != batch.shape or out.dtype != self.dtype or not out.is_contiguous():
+            raise ValueError("out has the wrong shape, dtype or strides")
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        st = _lib.lib().lvc_clip_forward(C.byref(batch.desc), batch.p_vid, batch.p_idx, batch.p_box,
+                                         self.lut.data_ptr() if self.lut is not None else None,
+                                         out.data_ptr(), stats.data_ptr() if stats is not None else None, stream)
+        _lib.check(st, "lvc_clip_forward")
+        self.launches += _lib.lib().lvc_clip_launch_count(C.byref(batch.desc))
+        return out
+
+    def __call__(self, videos, indices, boxes=None, out=None, stats=None):
+        """videos: list of B CUDA uint8 (N,H,W,3) tensors; indices: (B,T) ints; boxes: (B,T,4) int
+        xyxy or None (a box with x1 < 0 = no detection = full frame); out: optional preallocated
+        output; stats: optional CUDA int64 (B,) checksum accumulator.  Returns the clip tensor
+        (enqueued on the current stream, not synchronised)."""
+        if len(videos) == 0:
+            return torch.empty(_shape(self.layout, 0, self.num_frames), dtype=self.dtype, device=self.device)
+        batch = self.prepare(videos, indices, boxes)
+        out = self.run(batch, out, stats)
+        batch.tables.record_stream(torch.cuda.current_stream(self.device))
+        self._keep = batch  # staging buffers must outlive the enqueued work
+        return out
+
+
+    def build_from_host(self, host_videos, indices, boxes=None, out=None, stats=None):
+        """End-to-end entry for decoded frames that live in HOST memory (pinned uint8 ``(N,H,W,3)``
+        tensors, what a decoder hands over): uploads only the frames the index table selects
+        (each distinct frame once), then runs the fused kernel on the staged frames."""
+        T = self.num_frames
+        idx = np.asarray(indices, dtype=np.int64).reshape(len(host_videos), T)
+        staged, remap, h2d = [], [], 0
+        for b, hv in enumerate(host_videos):
+            if hv.dtype != torch.uint8 or hv.dim() != 4 or hv.shape[-1] != 3 or hv.is_cuda:
+                raise ValueError("each host video must be a CPU uint8 tensor of shape (N, H, W, 3)")
+            cl = np.clip(idx[b], 0, hv.shape[0] - 1)
+            uniq, inv = np.unique(cl, return_inverse=True)
+            dv = torch.empty((len(uniq),) + tuple(hv.shape[1:]), dtype=torch.uint8, device=self.device)
+            for j, fi in enumerate(uniq.tolist()):
+                dv[j].copy_(hv[fi], non_blocking=True)
+            h2d += dv.numel()
+            staged.append(dv)
+            remap.append(inv.astype(np.int32))
+        self.last_h2d_bytes = h2d
+        return self(staged, np.stack(remap), boxes=boxes, out=out, stats=stats)
+
+
+class ClipBatch:
+    """Device-resident tables of one prepared batch (keeps the videos and staging buffers alive)."""
+
+    def __init__(self, desc, tables, host, p_vid, p_idx, p_box, videos, shape):
+        self.desc, self.tables, self.host = desc, tables, host
+        self.p_vid, self.p_idx, self.p_box = p_vid, p_idx, p_box
+        self.videos, self.shape = videos, shape

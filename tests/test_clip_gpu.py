@@ -1,0 +1,183 @@
+"""Parity of the fused CUDA clip kernel (through the C ABI) against the oracle and the golden
+fixtures generated from the reference.  Needs a B200: run with `pytest -m gpu`.
+
+Tolerances (BASELINE.json north_star): resized uint8 within 1 LSB -- asserted at 0 LSB;
+normalised fp32 within 1e-5 -- asserted bit-exact where the LUT makes it so; bf16 = rounding of fp32.
+"""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import processors as op
+from oracle import samplers as osm
+
+pytestmark = pytest.mark.gpu
+
+METHODS = ["uniform", "random_window", "random"]
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def _videos(specs):
+    from lvc_b200.synth import synth_video
+
+    host = [synth_video(*s) for s in specs]
+    return host, [torch.from_numpy(v).cuda() for v in host]
+
+
+SHAPES = [  # (seed, N, H, W, mode)
+    (1, 6, 720, 1280, "noise"), (2, 5, 480, 640, "ramp"), (3, 4, 100, 150, "noise"),
+    (4, 4, 448, 448, "noise"), (5, 4, 449, 447, "noise"), (6, 3, 37, 1000, "noise"),
+    (7, 3, 1, 1, "noise"), (8, 4, 224, 224, "noise"), (9, 4, 1080, 1920, "noise"),
+    (10, 4, 223, 225, "ramp"), (11, 3, 2, 3, "noise"), (12, 4, 300, 200, "noise"),
+]
+
+
+def test_resized_uint8_bit_exact_all_shapes():
+    from lvc_b200 import ClipBuilder
+
+    T = 4
+    host, dev = _videos(SHAPES)
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    cb = ClipBuilder("dataset_u8", num_frames=T)
+    out = cb(dev, idx).cpu().numpy()
+    assert out.shape == (len(host), T, 224, 224, 3)
+    for b, v in enumerate(host):
+        want = op.resize_clip_cv2(v[idx[b]])
+        diff = np.abs(out[b].astype(int) - want.astype(int))
+        assert diff.max() == 0, (SHAPES[b], int(diff.max()), int((diff > 0).sum()))
+
+
+@pytest.mark.parametrize("preset,layout", [("resnet_infer", "BCTHW"), ("timesformer", "BTCHW")])
+def test_normalised_fp32_matches_reference_recipes(preset, layout):
+    from lvc_b200 import ClipBuilder
+
+    T = 8
+    host, dev = _videos(SHAPES[:5])
+    idx = [osm.dataset_indices("random_window", v.shape[0], T, __import__("random").Random(3)) for v in host]
+    cb = ClipBuilder(preset, num_frames=T)
+    assert cb.layout == layout
+    out = cb(dev, idx).cpu().numpy()
+    for b, v in enumerate(host):
+        r = op.resize_clip_cv2(v[idx[b]])
+        want = op.manual_normalize(r) if preset == "resnet_infer" else op.videomae_processor(r)
+        assert out[b].shape == want.shape
+        assert np.abs(out[b] - want).max() <= 1e-5
+        assert (out[b] != want).sum() == 0  # LUT makes it bit-exact
+
+
+def test_golden_config1_predict_video(golden):
+    """The GPU path reproduces the sha256 of the tensor the reference's own predict_video fed its model."""
+    from lvc_b200 import ClipBuilder, sampling, _lib
+    from lvc_b200.synth import synth_video
+
+    g = golden("pixels.npz")
+    for k in range(3):
+        seed, n, h, w, m, T = (int(v) for v in g[f"infer_case_{k}"])
+        vid = synth_video(seed, n, h, w)
+        idx = sampling.get_sampling_indices(METHODS[m], n, T, sampling.SamplerRng(42, "np"), _lib.VARIANT_NUMPY_INFER)
+        assert idx == g[f"infer_idx_{k}"].tolist()
+        out = ClipBuilder("resnet_infer", num_frames=T)([torch.from_numpy(vid).cuda()], [idx]).cpu().numpy()
+        assert out.shape == (1, 3, T, 224, 224)
+        assert sha(out) == str(g[f"infer_sha_{k}"])
+
+
+def test_golden_cv2_resize(golden):
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.synth import synth_video
+
+    g = golden("resize.npz")
+    cb = ClipBuilder("dataset_u8", num_frames=1)
+    for i, (seed, h, w, ramp) in enumerate(g["cases"]):
+        img = synth_video(int(seed), 1, int(h), int(w), "ramp" if ramp else "noise")
+        out = cb([torch.from_numpy(img).cuda()], [[0]]).cpu().numpy()[0, 0]
+        assert sha(out) == str(g[f"cv2_sha_{i}"]), (i, h, w)
+    # ROI crops: numpy slice + cv2.resize
+    img = synth_video(31, 1, 720, 1280)
+    dev = torch.from_numpy(img).cuda()
+    for i, box in enumerate(g["roi_boxes"]):
+        out = cb([dev], [[0]], boxes=[[box]]).cpu().numpy()[0, 0]
+        assert sha(out) == str(g[f"roi_sha_{i}"]), i
+
+
+def test_roi_boxes_layouts_bf16_and_stats():
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.synth import synth_boxes
+
+    T = 8
+    host, dev = _videos([(21, 12, 720, 1280, "noise"), (22, 9, 360, 640, "ramp"), (23, 8, 1080, 1920, "noise")])
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    boxes = np.stack([synth_boxes(2000 + b, T, v.shape[1], v.shape[2], p_none=0.25) for b, v in enumerate(host)])
+    boxes[0, 0] = [-5, -7, 100000, 100000]  # x1 < 0 = no detection
+    boxes[1, 1] = [10, 20, 10, 20]          # empty box -> 1x1 crop
+    boxes[2, 2] = [1900, 1000, 5000, 5000]  # clipped to the frame
+    want_u8 = np.stack([op.resize_clip_cv2(v[idx[b]], boxes[b]) for b, v in enumerate(host)])
+    stats = torch.zeros(len(host), dtype=torch.int64, device="cuda")
+    u8 = ClipBuilder("dataset_u8", num_frames=T)(dev, idx, boxes=boxes, stats=stats).cpu().numpy()
+    assert np.array_equal(u8, want_u8)
+    assert stats.cpu().tolist() == [int(w.astype(np.int64).sum()) for w in want_u8]
+    want = np.stack([op.manual_normalize(w) for w in want_u8])  # (B,C,T,H,W)
+    f32 = ClipBuilder("resnet_infer", num_frames=T)(dev, idx, boxes=boxes)
+    assert np.array_equal(f32.cpu().numpy(), want)
+    btchw = ClipBuilder("resnet_infer", num_frames=T, layout="BTCHW")(dev, idx, boxes=boxes)
+    assert torch.equal(btchw, f32.permute(0, 2, 1, 3, 4))
+    bf = ClipBuilder("resnet_infer", num_frames=T, dtype=torch.bfloat16)(dev, idx, boxes=boxes)
+    assert torch.equal(bf, f32.to(torch.bfloat16))
+    planar = ClipBuilder("dataset_u8", num_frames=T, layout="BTCHW")(dev, idx, boxes=boxes)
+    assert torch.equal(planar.cpu(), torch.from_numpy(want_u8).permute(0, 1, 4, 2, 3))
+
+
+def test_edge_cases_empty_ragged_short_and_out_of_range():
+    from lvc_b200 import ClipBuilder, sampling
+
+    cb = ClipBuilder("dataset_u8", num_frames=16)
+    assert tuple(cb([], []).shape) == (0, 16, 224, 224, 3)
+    # short video (N < T): duplicate-allowing branch; ragged sizes in one batch
+    host, dev = _videos([(31, 5, 120, 160, "noise"), (32, 40, 90, 300, "ramp")])
+    rng = sampling.SamplerRng(42)
+    idx = [sampling.get_sampling_indices("random_window", v.shape[0], 16, rng) for v in host]
+    out = cb(dev, idx).cpu().numpy()
+    for b, v in enumerate(host):
+        assert np.array_equal(out[b], op.resize_clip_cv2(v[idx[b]]))
+    # indices beyond the video repeat the last frame (vivit .../dataset.py:256-265), negatives clamp to 0
+    bad = [[-3, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 99, 10 ** 6]] * 2
+    out = cb(dev, bad).cpu().numpy()
+    for b, v in enumerate(host):
+        cl = np.clip(bad[b], 0, v.shape[0] - 1)
+        assert np.array_equal(out[b], op.resize_clip_cv2(v[cl]))
+    with pytest.raises(ValueError):
+        cb([dev[0].float()], [idx[0]])
+    with pytest.raises(ValueError):
+        ClipBuilder("nope")
+
+
+def test_full_size_properties_1080p():
+    """BASELINE config 5 frame size: size-independent checks (checksum of checksums, identity,
+    constant images, determinism) plus oracle spot checks."""
+    from lvc_b200 import ClipBuilder
+
+    B, N, T = 8, 48, 32
+    g = torch.Generator(device="cuda").manual_seed(5)
+    vids = [torch.randint(0, 256, (N, 1080, 1920, 3), dtype=torch.uint8, device="cuda", generator=g) for _ in range(B)]
+    idx = [osm.dataset_indices("uniform", N, T) for _ in range(B)]
+    cb = ClipBuilder("dataset_u8", num_frames=T)
+    stats = torch.zeros(B, dtype=torch.int64, device="cuda")
+    u8 = cb(vids, idx, stats=stats)
+    assert torch.equal(stats, u8.to(torch.int64).sum(dim=(1, 2, 3, 4)))
+    assert torch.equal(u8, cb(vids, idx))  # deterministic
+    for b, t in [(0, 0), (3, 17), (7, 31)]:
+        want = op.resize_clip_cv2(vids[b][idx[b][t]][None].cpu().numpy())[0]
+        assert np.array_equal(u8[b, t].cpu().numpy(), want)
+    f32 = ClipBuilder("resnet_infer", num_frames=T, layout="BTCHW")(vids, idx)
+    lut = ClipBuilder("resnet_infer").lut
+    want = torch.stack([lut[c][u8[..., c].long()] for c in range(3)], dim=2)
+    assert torch.equal(f32, want)
+    # identity: a 224x224 source passes through unchanged; constant image stays constant
+    small = torch.randint(0, 256, (T, 224, 224, 3), dtype=torch.uint8, device="cuda", generator=g)
+    assert torch.equal(cb([small], [list(range(T))])[0], small)
+    const = torch.full((2, 1080, 1920, 3), 137, dtype=torch.uint8, device="cuda")
+    assert bool((ClipBuilder("dataset_u8", num_frames=2)([const], [[0, 1]]) == 137).all())
