@@ -1,0 +1,468 @@
+// Patch / tubelet embedding for sm_100a: Conv3d/Conv2d with kernel == stride as a bf16 GEMM on the
+// 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands staged by TMA).
+// Replaces the first layer of the three transformer models the reference fine-tunes:
+//   VivitTubeletEmbeddings       (vivit_transformer/vivit_classifier/models/vivit_model.py:27-41)
+//   TimesformerPatchEmbeddings   (timesformer/timesformer_classifier/models/timesformer_model.py:27-42)
+//   torchvision PatchEmbed3d     (videoswintransformer/swin_video_classifier/models/swin3d.py:22-44)
+//
+// Pipeline per call:  im2col (x -> A[M][K] bf16, token-major, K = (c,kt,kh,kw))  ->  persistent
+// warp-specialised GEMM  D[M][N] = A . W^T + bias (+ LayerNorm over N for Swin):
+//   warp 0    TMA producer   cp.async.bulk.tensor.2d, 128B/64B swizzle, mbarrier ring
+//   warp 1    MMA issuer     one elected lane: tcgen05.mma.cta_group::1.kind::f16, M=128, N=BN, K=16
+//   warps 2-5 epilogue       tcgen05.ld 32x32b -> bias/LayerNorm -> bf16/fp32 rows to global
+// Two TMEM accumulator buffers overlap tile i's epilogue with tile i+1's MMAs.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstdlib>
+
+#include "lvc_internal.h"
+
+namespace {
+
+constexpr int BM = 128;          // rows (tokens) per tile = UMMA M
+constexpr int kGemmThreads = 192;
+
+struct EmbedGeom {
+  int B, T, H, W;      // input extents (channels = 3)
+  int kt, kh, kw;
+  int To, Ho, Wo;      // output token grid (ceil: PatchEmbed3d pads)
+  int M, K, N;
+};
+
+int make_geom(const lvc_embed_desc* d, EmbedGeom* g) {
+  if (!d) return lvc_fail(LVC_E_INVAL, "patch_embed: NULL descriptor");
+  if (d->kind < LVC_EMBED_VIVIT || d->kind > LVC_EMBED_SWIN) return lvc_fail(LVC_E_INVAL, "patch_embed: unknown kind %d", d->kind);
+  if (d->batch <= 0 || d->frames <= 0 || d->height <= 0 || d->width <= 0 || d->kt <= 0 || d->kh <= 0 || d->kw <= 0 || d->embed_dim <= 0)
+    return lvc_fail(LVC_E_INVAL, "patch_embed: extents must be positive");
+  g->B = d->batch; g->T = d->frames; g->H = d->height; g->W = d->width;
+  g->kt = d->kt; g->kh = d->kh; g->kw = d->kw;
+  if (d->kind == LVC_EMBED_SWIN) {  // pads up to a multiple of the patch (swin_transformer.py:353-358)
+    g->To = (g->T + g->kt - 1) / g->kt; g->Ho = (g->H + g->kh - 1) / g->kh; g->Wo = (g->W + g->kw - 1) / g->kw;
+  } else {                          // Conv with stride == kernel and no padding floors
+    if (d->kind == LVC_EMBED_TIMESFORMER && d->kt != 1) return lvc_fail(LVC_E_INVAL, "patch_embed: TimeSformer patches are 2-D (kt must be 1)");
+    g->To = g->T / g->kt; g->Ho = g->H / g->kh; g->Wo = g->W / g->kw;
+  }
+  const long long M = 1LL * g->B * g->To * g->Ho * g->Wo;
+  if (M <= 0 || M > 0x7fffffffLL) return lvc_fail(LVC_E_SHAPE, "patch_embed: token count %lld out of range", M);
+  g->M = (int)M; g->K = 3 * g->kt * g->kh * g->kw; g->N = d->embed_dim;
+  if (g->K % 32) return lvc_fail(LVC_E_SHAPE, "patch_embed: K = 3*kt*kh*kw = %d must be a multiple of 32", g->K);
+  if (g->N % 16 || g->N < 16) return lvc_fail(LVC_E_SHAPE, "patch_embed: embed_dim %d must be a multiple of 16", g->N);
+  if (d->kind == LVC_EMBED_SWIN && g->N > 256) return lvc_fail(LVC_E_SHAPE, "patch_embed: fused LayerNorm needs embed_dim <= 256");
+  if (g->N > 256 && g->N % 128) return lvc_fail(LVC_E_SHAPE, "patch_embed: embed_dim %d > 256 must be a multiple of 128", g->N);
+  return LVC_OK;
+}
+
+// ---------------------------------------------------------------------------- im2col ----
+// One thread per (token, c, dt, dy) run of kw contiguous pixels.  Reads are contiguous along x
+// (kw elements) and across the w' tokens of an image row; writes are kw*2-byte runs of A.
+template <typename TIn>
+__global__ void lvc_im2col_kernel(const TIn* __restrict__ x, __nv_bfloat16* __restrict__ a, EmbedGeom g, int bcthw) {
+  const long long runs = 1LL * g.M * 3 * g.kt * g.kh;
+  const long long stride = 1LL * gridDim.x * blockDim.x;
+  for (long long r = 1LL * blockIdx.x * blockDim.x + threadIdx.x; r < runs; r += stride) {
+    // order: x-token fastest, then dy, c/dt, so a warp reads one image row contiguously
+    long long q = r;
+    const int wo = (int)(q % g.Wo); q /= g.Wo;
+    const int dy = (int)(q % g.kh); q /= g.kh;
+    const int ho = (int)(q % g.Ho); q /= g.Ho;
+    const int dt = (int)(q % g.kt); q /= g.kt;
+    const int c = (int)(q % 3); q /= 3;
+    const int to = (int)(q % g.To); q /= g.To;
+    const int b = (int)q;
+    const int t = to * g.kt + dt, y = ho * g.kh + dy, x0 = wo * g.kw;
+    const long long m = ((1LL * b * g.To + to) * g.Ho + ho) * g.Wo + wo;
+    __nv_bfloat16* dst = a + m * g.K + ((c * g.kt + dt) * g.kh + dy) * g.kw;
+    const bool in = (t < g.T) && (y < g.H);
+    const long long src = bcthw ? (((1LL * b * 3 + c) * g.T + t) * g.H + y) * g.W + x0
+                                : (((1LL * b * g.T + t) * 3 + c) * g.H + y) * g.W + x0;
+    for (int i = 0; i < g.kw; ++i) {
+      float v = 0.f;
+      if (in && x0 + i < g.W) v = (float)x[src + i];
+      dst[i] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
+// conv weight (N, 3, kt, kh, kw) fp32 is already [N][K] row-major: packing = bf16 rounding.
+__global__ void lvc_pack_w_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ o, long long n) {
+  for (long long i = 1LL * blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 1LL * gridDim.x * blockDim.x)
+    o[i] = __float2bfloat16_rn(w[i]);
+}
+
+}  // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------ PTX helpers ----
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mb_init(uint64_t* b, uint32_t n) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(b)), "r"(n));
+}
+__device__ __forceinline__ void mb_expect_tx(uint64_t* b, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mb_arrive(uint64_t* b) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(b)) : "memory");
+}
+__device__ __forceinline__ void mb_wait(uint64_t* b, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(s32(b)), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// 2-D tiled TMA load (SASS: UTMALDG): coordinates {c0 = element along K, c1 = row}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(s32(dst)), "l"(map), "r"(s32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+// tcgen05
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(slot)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// D[tmem] (+)= A[smem] . B[smem]^T, bf16 inputs, fp32 accumulate (SASS: UTCHMMA)
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// mbarrier arrives once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread i of the warp gets TMEM lane (base lane + i)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor for a K-major bf16 tile whose rows are one swizzle span wide
+// (BK*2 = 128 B -> SWIZZLE_128B, 64 B -> SWIZZLE_64B): 8-row groups are `span*8` bytes apart (SBO);
+// LBO is unused for swizzled K-major operands; bits 46-47 = descriptor version 1 (sm_100).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int span_bytes) {
+  const uint64_t layout = span_bytes == 128 ? 2ull : 4ull;  // SWIZZLE_128B = 2, SWIZZLE_64B = 4
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3ffff) >> 4);
+  d |= (uint64_t)(((uint32_t)span_bytes * 8u) >> 4) << 32;
+  d |= 1ull << 46;
+  d |= layout << 61;
+  return d;
+}
+// kind::f16 instruction descriptor: D = F32 (bits 4-5 = 1), A = B = BF16 (bits 7-9, 10-12 = 1),
+// both K-major, N>>3 at bits 17-22, M>>4 at bits 24-28.
+__device__ __forceinline__ uint32_t make_idesc(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+}  // namespace
+
+namespace {
+
+struct GemmParams {
+  int M, N, K;
+  int BN, BK;          // tile columns, K elements per stage (64 -> 128B swizzle, 32 -> 64B swizzle)
+  int stages, num_k_blocks, m_tiles, n_tiles;
+  uint32_t tmem_cols;  // power of two >= 2*BN
+  const float* bias;
+  const float* ln_w;
+  const float* ln_b;
+  float ln_eps;
+  int do_ln, out_f32;
+  void* out;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                      const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int span = p.BK * 2;                       // bytes per tile row = swizzle span
+  const uint32_t a_bytes = BM * span, b_bytes = p.BN * span;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + (size_t)p.stages * a_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_b + (size_t)p.stages * b_bytes);
+  uint64_t* empty = full + p.stages;
+  uint64_t* tmem_full = empty + p.stages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_tiles = p.m_tiles * p.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile / p.n_tiles, n_blk = tile - m_blk * p.n_tiles;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+          const int s = it % p.stages;
+          mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
+          mb_expect_tx(&full[s], a_bytes + b_bytes);
+          tma_load_2d(smem_a + (size_t)s * a_bytes, &map_a, kb * p.BK, m_blk * BM, &full[s]);
+          tma_load_2d(smem_b + (size_t)s * b_bytes, &map_b, kb * p.BK, n_blk * p.BN, &full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc(BM, p.BN);
+      uint32_t it = 0, local = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+        const uint32_t acc = local & 1u, acc_phase = (local >> 1) & 1u;
+        mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.BN;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+          const int s = it % p.stages;
+          mb_wait(&full[s], (it / p.stages) & 1u);
+          tc_fence_after();
+          const uint64_t adesc = make_smem_desc(s32(smem_a + (size_t)s * a_bytes), span);
+          const uint64_t bdesc = make_smem_desc(s32(smem_b + (size_t)s * b_bytes), span);
+          for (int k = 0; k < p.BK / 16; ++k)  // +32 bytes (2 x 16 B units) per K=16 step inside the swizzle span
+            umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+          umma_commit(&empty[s]);    // smem stage free once these MMAs have read it
+        }
+        umma_commit(&tmem_full[acc]);  // accumulator complete
+      }
+    }
+  } else {
+    // ===================== epilogue: 4 warps, warp%4 selects its TMEM lane quarter =====================
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    uint32_t local = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      const int m_blk = tile / p.n_tiles, n_blk = tile - m_blk * p.n_tiles;
+      const uint32_t acc = local & 1u, acc_phase = (local >> 1) & 1u;
+      mb_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)p.BN;
+      const long long m = (long long)m_blk * BM + row;
+      const bool valid = m < p.M;
+      const int nchunks = p.BN / 32;
+      float mean = 0.f, rstd = 1.f;
+      float v[32];
+      if (p.do_ln) {  // LayerNorm over the N = BN columns this thread owns (one token row)
+        float sum = 0.f;
+        for (int ch = 0; ch < nchunks; ++ch) {
+          tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sum += v[j] + __ldg(p.bias + ch * 32 + j);
+        }
+        mean = sum / (float)p.N;
+        float sq = 0.f;
+        for (int ch = 0; ch < nchunks; ++ch) {
+          tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float dlt = v[j] + __ldg(p.bias + ch * 32 + j) - mean; sq += dlt * dlt; }
+        }
+        rstd = rsqrtf(sq / (float)p.N + p.ln_eps);
+      }
+      for (int ch = 0; ch < nchunks; ++ch) {
+        tmem_ld32(taddr + ch * 32, v);
+        const int n0 = n_blk * p.BN + ch * 32;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float y = v[j] + __ldg(p.bias + n0 + j);
+          if (p.do_ln) y = (y - mean) * rstd * __ldg(p.ln_w + n0 + j) + __ldg(p.ln_b + n0 + j);
+          v[j] = y;
+        }
+        if (valid) {
+          if (p.out_f32) {
+            float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + m * p.N + n0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          } else {
+            uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + m * p.N + n0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * j], v[8 * j + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
+              uint4 u;
+              u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+              u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+              o[j] = u;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mb_arrive(&tmem_empty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------ host ----
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// [rows][K] bf16 row-major, box = BK x box_rows, swizzle = BK*2 bytes
+int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t K, uint32_t BK, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return lvc_fail(LVC_E_CUDA, "patch_embed: cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {K, rows};
+  cuuint64_t strides[1] = {K * 2};
+  cuuint32_t box[2] = {BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return lvc_fail(LVC_E_CUDA, "patch_embed: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return LVC_OK;
+}
+
+int env_i(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+}  // namespace
+
+extern "C" int64_t lvc_patch_embed_workspace(const lvc_embed_desc* d) {
+  EmbedGeom g;
+  if (make_geom(d, &g) != LVC_OK) return -1;
+  return ((int64_t)g.M * g.K * 2 + 255) / 256 * 256;
+}
+
+extern "C" int lvc_patch_embed_launch_count(const lvc_embed_desc* d) { return d ? 2 : 0; }
+
+extern "C" int lvc_patch_embed_pack_weights(const lvc_embed_desc* d, const float* w_f32, void* w_packed, void* stream) {
+  EmbedGeom g;
+  int rc = make_geom(d, &g);
+  if (rc != LVC_OK) return rc;
+  if (!w_f32 || !w_packed) return lvc_fail(LVC_E_INVAL, "patch_embed_pack_weights: NULL pointer");
+  const long long n = 1LL * g.N * g.K;
+  lvc_pack_w_kernel<<<(int)std::min<long long>((n + 255) / 256, 1184), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w_f32, static_cast<__nv_bfloat16*>(w_packed), n);
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}
+
+extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const void* w_packed, const float* bias,
+                               const float* ln_w, const float* ln_b, void* out, void* workspace, void* stream) {
+  EmbedGeom g;
+  int rc = make_geom(d, &g);
+  if (rc != LVC_OK) return rc;
+  if (!x || !w_packed || !bias || !out || !workspace) return lvc_fail(LVC_E_INVAL, "patch_embed: NULL pointer");
+  if (d->kind == LVC_EMBED_SWIN && (!ln_w || !ln_b)) return lvc_fail(LVC_E_INVAL, "patch_embed: Swin needs LayerNorm weight and bias");
+  if (d->x_dtype != LVC_DT_F32 && d->x_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "patch_embed: x_dtype must be f32 or bf16");
+  if (d->out_dtype != LVC_DT_F32 && d->out_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "patch_embed: out_dtype must be f32 or bf16");
+  if (d->x_layout != LVC_LAYOUT_BTCHW && d->x_layout != LVC_LAYOUT_BCTHW) return lvc_fail(LVC_E_INVAL, "patch_embed: x_layout must be BTCHW or BCTHW");
+  if ((reinterpret_cast<uintptr_t>(workspace) & 127) || (reinterpret_cast<uintptr_t>(w_packed) & 127) || (reinterpret_cast<uintptr_t>(out) & 15))
+    return lvc_fail(LVC_E_ALIGN, "patch_embed: workspace / packed weights need 128-byte, out 16-byte alignment");
+  if (g.N % 32) return lvc_fail(LVC_E_SHAPE, "patch_embed: embed_dim %d must be a multiple of 32", g.N);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  int dev = 0, sms = 0, max_smem = 0;
+  LVC_CUDA_TRY(cudaGetDevice(&dev));
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+
+  // 1) im2col: x -> A[M][K] bf16
+  {
+    const long long runs = 1LL * g.M * 3 * g.kt * g.kh;
+    const int blocks = (int)std::min<long long>((runs + 255) / 256, (long long)sms * 16);
+    const int bcthw = d->x_layout == LVC_LAYOUT_BCTHW;
+    if (d->x_dtype == LVC_DT_F32)
+      lvc_im2col_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(workspace), g, bcthw);
+    else
+      lvc_im2col_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(workspace), g, bcthw);
+    LVC_CUDA_TRY(cudaGetLastError());
+  }
+  // 2) GEMM
+  GemmParams p{};
+  p.M = g.M; p.N = g.N; p.K = g.K;
+  p.BN = g.N <= 256 ? g.N : (g.N % 256 == 0 ? 256 : 128);
+  p.BK = (g.K % 64 == 0) ? 64 : 32;
+  p.num_k_blocks = g.K / p.BK;
+  p.m_tiles = (g.M + BM - 1) / BM;
+  p.n_tiles = g.N / p.BN;
+  p.tmem_cols = 32;
+  while (p.tmem_cols < 2u * p.BN) p.tmem_cols <<= 1;
+  p.bias = bias; p.ln_w = ln_w; p.ln_b = ln_b; p.ln_eps = d->ln_eps;
+  p.do_ln = d->kind == LVC_EMBED_SWIN;
+  p.out_f32 = d->out_dtype == LVC_DT_F32;
+  p.out = out;
+  const int stage_bytes = (BM + p.BN) * p.BK * 2;
+  p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (max_smem - 2048) / stage_bytes, std::max(2, p.num_k_blocks * 2)});
+  if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "patch_embed: tile does not fit shared memory");
+  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 4) * 8 + 16;
+
+  CUtensorMap map_a, map_b;
+  rc = make_map(&map_a, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
+  if (rc != LVC_OK) return rc;
+  rc = make_map(&map_b, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)p.BN);
+  if (rc != LVC_OK) return rc;
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = std::min(sms, p.m_tiles * p.n_tiles);
+  lvc_embed_gemm_kernel<<<grid, kGemmThreads, smem, st>>>(map_a, map_b, p);
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}

@@ -1,0 +1,203 @@
+"""Drop-in patch / tubelet embedding modules backed by the tcgen05 GEMM (csrc/lvc_embed.cu).
+
+Same class names, constructor meaning, parameter names (so reference checkpoints load unchanged:
+``projection.weight/bias``, ``proj.weight/bias``, ``norm.weight/bias``), forward signatures, return
+values and ValueError behaviour as the modules the reference instantiates:
+
+  VivitTubeletEmbeddings      transformers modeling_vivit.py:36-77      (vivit_model.py:27-41)
+  TimesformerPatchEmbeddings  transformers modeling_timesformer.py:38-64 (timesformer_model.py:27-42)
+  PatchEmbed3d                torchvision swin_transformer.py:321-363   (swin3d.py:22-44)
+
+Forward only (inference / frozen first layer): inputs are rounded to bf16, products accumulate in
+fp32 on the tensor cores, output is bf16 by default (``out_dtype=torch.float32`` to keep fp32).
+There is no fallback: forward raises if the input is not on a CUDA device.
+"""
+import ctypes as C
+from types import SimpleNamespace
+
+import torch
+from torch import nn
+
+from . import _lib
+
+_DT = {torch.float32: _lib.DT_F32, torch.bfloat16: _lib.DT_BF16}
+
+
+class _EmbedBase(nn.Module):
+    kind = None
+    x_layout = _lib.LAYOUT_BTCHW
+
+    def _init_runtime(self, out_dtype):
+        self.out_dtype = out_dtype
+        self._packed = None
+        self._packed_key = None
+        self._ws = None
+        self.launches = 0
+
+    def _conv(self):
+        raise NotImplementedError
+
+    def _ln(self):
+        return None, None, 0.0
+
+    def _desc(self, x, B, T, H, W):
+        conv = self._conv()
+        ks = conv.kernel_size
+        kt, kh, kw = (1, ks[0], ks[1]) if len(ks) == 2 else ks
+        return _lib.EmbedDesc(self.kind, _DT[x.dtype], self.x_layout, _DT[self.out_dtype], B, T, H, W,
+                              kt, kh, kw, conv.out_channels, float(self._ln()[2]), 0)
+
+    def _run(self, x, B, T, H, W, out_shape):
+        if not x.is_cuda:
+            raise RuntimeError(f"{type(self).__name__}: input must be on a CUDA device (no CPU fallback)")
+        if x.dtype not in _DT:
+            x = x.float()
+        x = x.contiguous()
+        conv = self._conv()
+        w, bias = conv.weight, conv.bias
+        if w.device != x.device:
+            raise RuntimeError("module parameters and input are on different devices")
+        lib = _lib.lib()
+        d = self._desc(x, B, T, H, W)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        key = (w.data_ptr(), w._version, tuple(w.shape))
+        if self._packed is None or self._packed_key != key:
+            self._packed = torch.empty(w.numel(), dtype=torch.bfloat16, device=x.device)
+            _lib.check(lib.lvc_patch_embed_pack_weights(C.byref(d), w.detach().float().contiguous().data_ptr(),
+                                                        self._packed.data_ptr(), stream), "pack_weights")
+            self._packed_key = key
+            self.launches += 1
+        need = lib.lvc_patch_embed_workspace(C.byref(d))
+        if need < 0:
+            _lib.check(_lib.E_SHAPE, type(self).__name__)
+        if self._ws is None or self._ws.numel() < need or self._ws.device != x.device:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=x.device)
+        out = torch.empty(out_shape, dtype=self.out_dtype, device=x.device)
+        if bias is None:
+            bias = torch.zeros(conv.out_channels, device=x.device)
+        lw, lb, _ = self._ln()
+        st = lib.lvc_patch_embed(C.byref(d), x.data_ptr(), self._packed.data_ptr(),
+                                 bias.detach().float().contiguous().data_ptr(),
+                                 lw.detach().float().contiguous().data_ptr() if lw is not None else None,
+                                 lb.detach().float().contiguous().data_ptr() if lb is not None else None,
+                                 out.data_ptr(), self._ws.data_ptr(), stream)
+        _lib.check(st, type(self).__name__)
+        self.launches += lib.lvc_patch_embed_launch_count(C.byref(d))
+        return out
+
+
+class VivitTubeletEmbeddings(_EmbedBase):
+    """(B, T, C, H, W) -> (B, T/2 * H/16 * W/16, hidden).  ``config`` needs num_frames, image_size,
+    tubelet_size, num_channels, hidden_size (a ``transformers.VivitConfig`` works)."""
+
+    kind = _lib.EMBED_VIVIT
+
+    def __init__(self, config=None, out_dtype=torch.bfloat16, **kw):
+        super().__init__()
+        if config is None:
+            config = SimpleNamespace(num_frames=32, image_size=224, tubelet_size=[2, 16, 16], num_channels=3,
+                                     hidden_size=768)
+            for k, v in kw.items():
+                setattr(config, k, v)
+        self.num_frames = config.num_frames
+        self.image_size = config.image_size if isinstance(config.image_size, (tuple, list)) else (config.image_size,) * 2
+        self.patch_size = list(config.tubelet_size)
+        self.num_patches = ((self.image_size[1] // self.patch_size[2]) * (self.image_size[0] // self.patch_size[1])
+                            * (self.num_frames // self.patch_size[0]))
+        self.embed_dim = config.hidden_size
+        self.projection = nn.Conv3d(config.num_channels, config.hidden_size, kernel_size=tuple(config.tubelet_size),
+                                    stride=tuple(config.tubelet_size))
+        self._init_runtime(out_dtype)
+
+    def _conv(self):
+        return self.projection
+
+    @torch.no_grad()
+    def forward(self, pixel_values, interpolate_pos_encoding=False):
+        B, T, Cc, H, W = pixel_values.shape
+        if not interpolate_pos_encoding and (H != self.image_size[0] or W != self.image_size[1]):
+            raise ValueError(f"Image image size ({H}*{W}) doesn't match model ({self.image_size[0]}*{self.image_size[1]}).")
+        if Cc != 3:
+            raise ValueError("lvc_b200 patch embedding supports 3 input channels")
+        kt, kh, kw = self.patch_size
+        return self._run(pixel_values, B, T, H, W, (B, (T // kt) * (H // kh) * (W // kw), self.embed_dim))
+
+
+class TimesformerPatchEmbeddings(_EmbedBase):
+    """(B, T, C, H, W) -> (embeddings (B*T, H/16*W/16, hidden), T, W/16)."""
+
+    kind = _lib.EMBED_TIMESFORMER
+
+    def __init__(self, config=None, out_dtype=torch.bfloat16, **kw):
+        super().__init__()
+        if config is None:
+            config = SimpleNamespace(image_size=224, patch_size=16, num_channels=3, hidden_size=768)
+            for k, v in kw.items():
+                setattr(config, k, v)
+        image_size = config.image_size if isinstance(config.image_size, (tuple, list)) else (config.image_size,) * 2
+        patch_size = config.patch_size if isinstance(config.patch_size, (tuple, list)) else (config.patch_size,) * 2
+        self.image_size, self.patch_size = tuple(image_size), tuple(patch_size)
+        self.num_patches = (image_size[1] // patch_size[1]) * (image_size[0] // patch_size[0])
+        self.projection = nn.Conv2d(config.num_channels, config.hidden_size, kernel_size=self.patch_size,
+                                    stride=self.patch_size)
+        self._init_runtime(out_dtype)
+
+    def _conv(self):
+        return self.projection
+
+    @torch.no_grad()
+    def forward(self, pixel_values):
+        B, T, Cc, H, W = pixel_values.shape
+        if Cc != 3:
+            raise ValueError("lvc_b200 patch embedding supports 3 input channels")
+        kh, kw = self.patch_size
+        emb = self._run(pixel_values, B, T, H, W, (B * T, (H // kh) * (W // kw), self.projection.out_channels))
+        return emb, T, W // kw
+
+
+class PatchEmbed3d(_EmbedBase):
+    """(B, C, T, H, W) -> (B, T/2, H/4, W/4, embed_dim), padded like torchvision's, LayerNorm fused."""
+
+    kind = _lib.EMBED_SWIN
+    x_layout = _lib.LAYOUT_BCTHW
+
+    def __init__(self, patch_size, in_channels=3, embed_dim=96, norm_layer=None, out_dtype=torch.bfloat16):
+        super().__init__()
+        if norm_layer is None:
+            raise NotImplementedError("lvc_b200.PatchEmbed3d fuses the LayerNorm every swin3d_* model uses; "
+                                      "norm_layer=None is not supported")
+        self.tuple_patch_size = (patch_size[0], patch_size[1], patch_size[2])
+        self.proj = nn.Conv3d(in_channels, embed_dim, kernel_size=self.tuple_patch_size, stride=self.tuple_patch_size)
+        self.norm = norm_layer(embed_dim)
+        if not isinstance(self.norm, nn.LayerNorm):
+            raise NotImplementedError("norm_layer must build an nn.LayerNorm")
+        self._init_runtime(out_dtype)
+
+    def _conv(self):
+        return self.proj
+
+    def _ln(self):
+        return self.norm.weight, self.norm.bias, self.norm.eps
+
+    @torch.no_grad()
+    def forward(self, x):
+        B, Cc, T, H, W = x.shape
+        if Cc != 3:
+            raise ValueError("lvc_b200 patch embedding supports 3 input channels")
+        kt, kh, kw = self.tuple_patch_size
+        shape = (B, -(-T // kt), -(-H // kh), -(-W // kw), self.proj.out_channels)
+        return self._run(x, B, T, H, W, shape)
+
+
+def smoke():
+    """Tiny ViViT tubelet embedding on cuda:0 against the fp32 oracle (called by __graft_entry__.smoke)."""
+    from oracle import patch_embed as ope
+
+    torch.manual_seed(0)
+    m = VivitTubeletEmbeddings(num_frames=4, image_size=64).cuda()
+    x = torch.randn(2, 4, 3, 64, 64, device="cuda")
+    y = m(x).float().cpu()
+    ref = ope.vivit_tubelet_embed(x.cpu(), m.projection.weight.detach().cpu(), m.projection.bias.detach().cpu())
+    e_max, e_l2 = ope.rel_err(y, ref)
+    assert e_max <= 1e-2 and e_l2 <= 1e-2, (e_max, e_l2)
+    print(f"smoke ok: tcgen05 tubelet embedding {tuple(y.shape)} rel err max {e_max:.2e} l2 {e_l2:.2e}")

@@ -183,6 +183,9 @@ def run_b200(args, wl):
     ms_per_step = total_ms / args.steps
     value = B * world / (ms_per_step * 1e-3)
 
+    if args.no_e2e:
+        return dict(rank=rank, world=world, ms_per_step=ms_per_step, value=value, launch_ms=launch_ms, launches=launches,
+                    clocks=clk.summary(), e2e=None, e2e_steps=0, h2d=0, d2h=0, checksum=int(stats.sum().item()))
     # ---- e2e: host (pinned) frames -> H2D of the sampled frames -> fused kernel -> D2H of the checksum
     e2e_steps = max(2, min(args.steps, 5))
     # (16 distinct pinned host videos stand in for the rank's 64: every entry still uploads its own
@@ -223,6 +226,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="sweep1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host->device leg (profiling runs only)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
