@@ -14,6 +14,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <cstdlib>
 
@@ -34,11 +35,16 @@ struct RowDesc {  // one output row of a stage
 };
 struct StageHdr {
   int frame;      // output frame id b*T + t
-  int sw;         // source window width (pixels)
+  int sw;         // source window width (pixels); PTV: full frame width
   int oy0;        // first output row of this stage
   int flags;      // bit 0: exact 2x2 down-scale (cv::resize switches to INTER_AREA)
+  int ox;         // PTV: first source column held in the row slots
+  int nw;         // PTV: width of the short-side-scaled image
+  int left;       // PTV: centre-crop offset in the scaled image
+  int pad;
   RowDesc rows[kMaxRPS];
 };
+enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
 
 struct ClipParams {
   const lvc_video* videos;
@@ -52,6 +58,7 @@ struct ClipParams {
   int bands, rows_per_band;  // bands per frame, output rows per band
   int total_items;           // B*T*bands
   int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
+  float mean[3], std[3];     // PTV normalisation
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------
@@ -113,18 +120,81 @@ __device__ __forceinline__ int coef(float w) { return __float2int_rn(__fmul_rn(w
 
 namespace {
 
-// Shared memory map: [0,256) full/empty mbarriers | StageHdr[kMaxStages] | LUT 3x256 f32 | ring.
+// Shared memory map: [0,256) full/empty mbarriers | StageHdr[kMaxStages] | LUT 3x256 f32 |
+// (MODE_VIVIT: Pillow tap table, 2x2 row buffers, 224x672 intermediate frame) | ring.
 constexpr int kHdrOff = 256;
 constexpr int kLutOff = kHdrOff + kMaxStages * (int)sizeof(StageHdr);
-constexpr int kRingOff = (kLutOff + 3 * 256 * 4 + 127) / 128 * 128;
+constexpr int kAuxOff = (kLutOff + 3 * 256 * 4 + 127) / 128 * 128;
+constexpr int kRowBytes = S * 3;                    // one resized RGB row
+constexpr int kVivitTapOff = kAuxOff;               // int4[224]: ymin, k0, k1, k2
+constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][672]
+constexpr int kVivitInterOff = kVivitRowBufOff + kGroups * 2 * kRowBytes;
+constexpr int kVivitEnd = (kVivitInterOff + S * kRowBytes + 127) / 128 * 128;
+__host__ __device__ constexpr int ring_off(int mode) { return mode == MODE_VIVIT ? kVivitEnd : kAuxOff; }
 
-__global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_constant__ ClipParams p) {
+// Pillow BILINEAR 224 -> 256 taps for cropped output coordinate d (source coordinate d + 16 of the
+// 256-wide image): precompute_coeffs + normalize_coeffs_8bpc in double, support 1 (up-scale).
+__device__ __forceinline__ int4 pil_tap(int d) {
+  const double scale = 224.0 / 256.0;
+  const double center = __dmul_rn((double)(d + 16) + 0.5, scale);
+  int xmin = (int)(__dadd_rn(__dadd_rn(center, -1.0), 0.5));
+  if (xmin < 0) xmin = 0;
+  int xmax = (int)(__dadd_rn(__dadd_rn(center, 1.0), 0.5));
+  if (xmax > S) xmax = S;
+  const int n = xmax - xmin;
+  double w[3] = {0.0, 0.0, 0.0}, ww = 0.0;
+  for (int i = 0; i < 3; ++i)
+    if (i < n) {
+      double t = __dadd_rn(__dadd_rn((double)(i + xmin), -center), 0.5);
+      t = t < 0 ? -t : t;
+      w[i] = t < 1.0 ? __dadd_rn(1.0, -t) : 0.0;
+      ww = __dadd_rn(ww, w[i]);
+    }
+  int k[3];
+  for (int i = 0; i < 3; ++i) {
+    double v = (ww != 0.0) ? __ddiv_rn(w[i], ww) : w[i];
+    k[i] = (int)(__dadd_rn(0.5, __dmul_rn(v, 4194304.0)));
+  }
+  return make_int4(xmin, k[0], k[1], k[2]);
+}
+__device__ __forceinline__ int clip8(int v) { return min(max(v, 0), 255); }
+
+// torch bilinear (align_corners=False) source coordinate, exactly as ATen's CPU kernel evaluates it:
+// src = max(fma(scale, dst + 0.5, -0.5), 0); i0 = min(floor(src), in-1); lambda = clamp(src - i0, 0, 1).
+__device__ __forceinline__ void torch_tap(int dst, float scale, int in, int& i0, int& i1, float& l0, float& l1) {
+  float src = fmaxf(__fmaf_rn(scale, (float)dst + 0.5f, -0.5f), 0.0f);
+  i0 = min((int)floorf(src), in - 1);
+  l1 = fminf(fmaxf(__fsub_rn(src, (float)i0), 0.0f), 1.0f);
+  l0 = __fsub_rn(1.0f, l1);
+  i1 = i0 + (i0 < in - 1 ? 1 : 0);
+}
+// pytorchvideo ShortSideScale(256) + torchvision CenterCrop(224) geometry for an HxW frame.
+__device__ __forceinline__ void ptv_geom(int H, int W, int& nh, int& nw, int& top, int& left) {
+  // python: int(math.floor((float(h) / w) * size)) and int(round((n - crop) / 2.0)), all in double
+  if (W < H) { nw = 256; nh = (int)floor(__dmul_rn(__ddiv_rn((double)H, (double)W), 256.0)); }
+  else { nh = 256; nw = (int)floor(__dmul_rn(__ddiv_rn((double)W, (double)H), 256.0)); }
+  top = (int)rint((double)(nh - S) / 2.0);
+  left = (int)rint((double)(nw - S) / 2.0);
+}
+__device__ __forceinline__ void group_bar(int g) {
+  asm volatile("bar.sync %0, %1;" ::"r"(2 + g), "r"(S) : "memory");
+}
+__device__ __forceinline__ void consumers_bar() {
+  asm volatile("bar.sync 1, %0;" ::"r"(kConsumers) : "memory");
+}
+
+}  // namespace
+
+namespace {
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty = full + kMaxStages;
   StageHdr* hdrs = reinterpret_cast<StageHdr*>(smem + kHdrOff);
   float* lut = reinterpret_cast<float*>(smem + kLutOff);
-  uint8_t* ring = smem + kRingOff;
+  uint8_t* ring = smem + ring_off(MODE);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -139,6 +209,8 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
   }
   if (p.lut)
     for (int i = tid; i < 3 * 256; i += kThreads) lut[i] = p.lut[i];
+  if (MODE == MODE_VIVIT)
+    for (int i = tid; i < S; i += kThreads) reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = pil_tap(i);
   __syncthreads();
 
   if (warp == 0) {
@@ -153,8 +225,18 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
       const lvc_video v = p.videos[b];
       int idx = p.indices[f];
       idx = min(max(idx, 0), v.n_frames - 1);
-      int ox = 0, oy = 0, sw = v.width, sh = v.height;
-      if (p.boxes) {
+      int ox = 0, oy = 0, sw = v.width, sh = v.height;  // source window: origin and size
+      int nh = 0, nw = 0, top = 0, left = 0;
+      float scale_h = 0.f;
+      if (MODE == MODE_PTV) {
+        ptv_geom(v.height, v.width, nh, nw, top, left);
+        scale_h = __fdiv_rn((float)v.height, (float)nh);
+        const float scale_w = __fdiv_rn((float)v.width, (float)nw);
+        int xa, xb, xc, xd; float l0, l1;
+        torch_tap(left, scale_w, v.width, xa, xb, l0, l1);          // first and last tapped columns
+        torch_tap(left + S - 1, scale_w, v.width, xc, xd, l0, l1);
+        ox = xa; sw = xd - xa + 1;
+      } else if (p.boxes) {
         const int4 bx = reinterpret_cast<const int4*>(p.boxes)[f];
         if (bx.x >= 0) {  // numpy half-open slice of the box clipped to the frame, at least 1x1
           ox = min(max(bx.x, 0), v.width - 1);
@@ -163,7 +245,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
           sh = min(max(bx.w, oy + 1), v.height) - oy;
         }
       }
-      const bool area = (sw == 2 * S) && (sh == 2 * S);
+      const bool area = MODE != MODE_PTV && (sw == 2 * S) && (sh == 2 * S);
       const double scale_y = cv_scale(sh);
       const uint64_t row_bytes = (uint64_t)v.width * 3u;
       const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
@@ -181,11 +263,17 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
         uint8_t* stage_base = ring + (size_t)slot * nrows * p.pitch;
         if (lane < nrows) {
           const int r = lane >> 1, oyr = oy_first + r;
-          int sy; float fr;
-          cv_tap(oyr, scale_y, sy, fr);
           int ysrc;
-          if (area) { ysrc = 2 * oyr + (lane & 1); cb = 0; }
-          else {
+          if (MODE == MODE_PTV) {
+            int y0, y1; float l0, l1;
+            torch_tap(oyr + top, scale_h, v.height, y0, y1, l0, l1);
+            ysrc = (lane & 1) ? y1 : y0;
+            cb = __float_as_int((lane & 1) ? l1 : l0);
+          } else if (area) {
+            ysrc = 2 * oyr + (lane & 1);
+          } else {
+            int sy; float fr;
+            cv_tap(oyr, scale_y, sy, fr);
             ysrc = min(max(sy + (lane & 1), 0), sh - 1);
             cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
           }
@@ -213,7 +301,10 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
           rd.off0 = my_off; rd.off1 = off_next; rd.b0 = cb; rd.b1 = cb_next;
           h->rows[lane >> 1] = rd;
         }
-        if (lane == 0) { h->frame = f; h->sw = sw; h->oy0 = oy_first; h->flags = area ? 1 : 0; }
+        if (lane == 0) {
+          h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first; h->flags = area ? 1 : 0;
+          h->ox = ox; h->nw = nw; h->left = left;
+        }
         if (leader && bulk_bytes < my_bytes) {
           // last bytes of the buffer: not a whole 16-byte granule, copy them by hand
           uint8_t* slot_ptr = stage_base + (size_t)lane * p.pitch;
@@ -235,19 +326,37 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
   const int ct = tid - 32;
   const int g = ct / S;
   const int x = ct - g * S;
-  int cached_sw = -1, cached_flags = -1;
+  int cached_sw = -1, cached_flags = -1, cached_ox = -1;
   int xo = 0, d1 = 0, a0 = 0, a1 = 0;
+  float lx0 = 0.f, lx1 = 0.f;
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
   int acc_b = -1;
   uint32_t it = 0;
   const size_t plane = (size_t)S * S;
+  // MODE_VIVIT state: Pillow horizontal taps of this thread's column, row-buffer parity
+  int4 hx = make_int4(0, 0, 0, 0);
+  int parity = 0;
+  uint8_t* inter = smem + kVivitInterOff;
+  if (MODE == MODE_VIVIT) hx = reinterpret_cast<const int4*>(smem + kVivitTapOff)[x];
+
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+    int f = 0;
     for (int st = 0; st < stages_per_item; ++st, ++it) {
       const int slot = it % p.stages;
       mbar_wait(&full[slot], (it / p.stages) & 1u);
       const StageHdr* h = &hdrs[slot];
-      const int f = h->frame, sw = h->sw, flags = h->flags, oy0 = h->oy0;
-      if (sw != cached_sw || flags != cached_flags) {
+      const int sw = h->sw, flags = h->flags, oy0 = h->oy0;
+      f = h->frame;
+      if (MODE == MODE_PTV) {
+        const int hox = h->ox;
+        if (sw != cached_sw || hox != cached_ox) {
+          cached_sw = sw; cached_ox = hox;
+          int x0, x1;
+          torch_tap(x + h->left, __fdiv_rn((float)sw, (float)h->nw), sw, x0, x1, lx0, lx1);
+          xo = 3 * (x0 - hox);
+          d1 = 3 * (x1 - x0);
+        }
+      } else if (sw != cached_sw || flags != cached_flags) {
         cached_sw = sw; cached_flags = flags;
         if (flags & 1) { xo = 6 * x; d1 = 3; a0 = 1; a1 = 1; }
         else {
@@ -262,7 +371,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
         }
       }
       const int b = f / p.T, t = f - b * p.T;
-      if (p.stats && b != acc_b) {
+      if (MODE != MODE_PTV && p.stats && b != acc_b) {
         if (acc_b >= 0) {
 #pragma unroll
           for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -279,6 +388,23 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
         const RowDesc rd = h->rows[r];
         const uint8_t* p0 = ring + rd.off0 + xo;
         const uint8_t* p1 = ring + rd.off1 + xo;
+        const int oyr = oy0 + r;
+        if (MODE == MODE_PTV) {
+          // torch CPU blend order: r = fma(p_x0, lx0, p_x1*lx1) per row, out = fma(r_y0, ly0, r_y1*ly1)
+          const float ly0 = __int_as_float(rd.b0), ly1 = __int_as_float(rd.b1);
+          float* o = reinterpret_cast<float*>(p.out) + base + (size_t)oyr * S + x;
+          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + base + (size_t)oyr * S + x;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const float r0 = __fmaf_rn((float)p0[c], lx0, __fmul_rn((float)p0[c + d1], lx1));
+            const float r1 = __fmaf_rn((float)p1[c], lx0, __fmul_rn((float)p1[c + d1], lx1));
+            const float val = __fmaf_rn(r0, ly0, __fmul_rn(r1, ly1));
+            const float y = __fdiv_rn(__fsub_rn(val, p.mean[c]), p.std[c]);
+            if (p.out_dtype == LVC_DT_F32) __stcs(o + c * cstride, y);
+            else ob[c * cstride] = __float2bfloat16_rn(y);
+          }
+          continue;
+        }
         int v[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -292,7 +418,22 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
           }
         }
         acc += (unsigned)(v[0] + v[1] + v[2]);
-        const int oyr = oy0 + r;
+        if (MODE == MODE_VIVIT) {
+          // Pillow horizontal pass of this row (224 -> cropped 224 of 256), rounded to uint8
+          uint8_t* rb = smem + kVivitRowBufOff + (g * 2 + parity) * kRowBytes;
+          parity ^= 1;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) rb[x * 3 + c] = (uint8_t)v[c];
+          group_bar(g);
+          const uint8_t* tp = rb + hx.x * 3;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            int ss = (1 << 21) + tp[c] * hx.y + tp[3 + c] * hx.z;
+            if (hx.w) ss += tp[6 + c] * hx.w;
+            inter[oyr * kRowBytes + x * 3 + c] = (uint8_t)clip8(ss >> 22);
+          }
+          continue;
+        }
         if (p.out_dtype == LVC_DT_F32) {
           float* o = reinterpret_cast<float*>(p.out) + base + (size_t)oyr * S + x;
 #pragma unroll
@@ -317,8 +458,47 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_cv2_kernel(const __grid_
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
     }
+    if (MODE == MODE_VIVIT) {
+      // the whole frame went through the horizontal pass: Pillow vertical pass + LUT + store
+      consumers_bar();
+      const int b = f / p.T, t = f - b * p.T;
+      size_t base, cstride;
+      if (p.layout == LVC_LAYOUT_BTCHW) { base = (size_t)f * 3 * plane; cstride = plane; }
+      else if (p.layout == LVC_LAYOUT_BCTHW) { base = ((size_t)b * 3 * p.T + t) * plane; cstride = (size_t)p.T * plane; }
+      else { base = (size_t)f * plane * 3; cstride = 1; }
+      const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
+      for (int y = g; y < S; y += kGroups) {
+        const int4 ty = vt[y];
+        const uint8_t* tp = inter + ty.x * kRowBytes + x * 3;
+        int v[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          int ss = (1 << 21) + tp[c] * ty.y + tp[kRowBytes + c] * ty.z;
+          if (ty.w) ss += tp[2 * kRowBytes + c] * ty.w;
+          v[c] = clip8(ss >> 22);
+        }
+        if (p.out_dtype == LVC_DT_F32) {
+          float* o = reinterpret_cast<float*>(p.out) + base + (size_t)y * S + x;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
+        } else if (p.out_dtype == LVC_DT_BF16) {
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + base + (size_t)y * S + x;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(lut[c * 256 + v[c]]);
+        } else if (p.layout == LVC_LAYOUT_BTHWC) {
+          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + base + ((size_t)y * S + x) * 3;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) o[c] = (uint8_t)v[c];
+        } else {
+          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + base + (size_t)y * S + x;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
+        }
+      }
+      consumers_bar();  // the next frame's horizontal pass overwrites the intermediate
+    }
   }
-  if (p.stats && acc_b >= 0) {
+  if (MODE != MODE_PTV && p.stats && acc_b >= 0) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
@@ -353,6 +533,14 @@ const DeviceInfo& device_info() {
   return di;
 }
 
+template <int MODE>
+int launch(const ClipParams& p, int grid, size_t smem, cudaStream_t st) {
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lvc_clip_kernel<MODE><<<grid, kThreads, smem, st>>>(p);
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}
+
 }  // namespace
 
 extern "C" int lvc_clip_launch_count(const lvc_clip_desc* d) { return d ? 1 : 0; }
@@ -366,32 +554,46 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: batch, num_frames and max_width must be positive");
   if (d->layout < LVC_LAYOUT_BTCHW || d->layout > LVC_LAYOUT_BTHWC || d->out_dtype < LVC_DT_F32 || d->out_dtype > LVC_DT_U8)
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: unknown layout or dtype");
+  if (d->resample < LVC_RESAMPLE_CV2 || d->resample > LVC_RESAMPLE_PTV_EVAL)
+    return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: unknown resample mode %d", d->resample);
   if (d->layout == LVC_LAYOUT_BTHWC && d->out_dtype != LVC_DT_U8)
     return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: BTHWC layout is the uint8 Dataset clip only");
-  if (d->out_dtype != LVC_DT_U8 && !lut && d->resample != LVC_RESAMPLE_PTV_EVAL)
+  const bool ptv = d->resample == LVC_RESAMPLE_PTV_EVAL;
+  if (ptv) {
+    if (d->out_dtype == LVC_DT_U8) return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: the pytorchvideo chain is a float pipeline (no uint8 output)");
+    if (boxes) return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: ROI boxes are not defined for the pytorchvideo chain");
+    for (int c = 0; c < 3; ++c)
+      if (d->std[c] == 0.0f) return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: std[%d] is zero", c);
+  } else if (d->out_dtype != LVC_DT_U8 && !lut) {
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: float output needs a LUT (lvc_build_lut)");
-  if (d->resample != LVC_RESAMPLE_CV2)
-    return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: resample mode %d not implemented", d->resample);
+  }
   if (boxes && (reinterpret_cast<uintptr_t>(boxes) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: boxes must be 16-byte aligned");
   if ((int64_t)d->batch * d->num_frames > (1 << 24)) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: too many frames in one call");
 
   const DeviceInfo& di = device_info();
   if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "lvc_clip_forward: no usable CUDA device: %s", cudaGetErrorString(di.err));
 
+  const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
   ClipParams p{};
   p.videos = videos; p.indices = indices; p.boxes = boxes; p.lut = lut; p.out = out;
   p.stats = reinterpret_cast<unsigned long long*>(stats);
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
+  for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
   // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
   p.rps = env_int("LVC_CLIP_RPS", 4);
   if (p.rps < kGroups || p.rps > kMaxRPS || (p.rps % kGroups) || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
-  const int smem_budget = std::min(di.max_smem, env_int("LVC_CLIP_SMEM_KB", 200) * 1024);
+  const int fixed = ring_off(mode);
+  const int smem_budget = std::min(di.max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, fixed + 64 * 1024));
   int stage_bytes = 2 * p.rps * p.pitch;
-  while ((smem_budget - kRingOff) / stage_bytes < 2 && p.rps > kGroups) { p.rps -= kGroups; while (S % p.rps) p.rps -= kGroups; stage_bytes = 2 * p.rps * p.pitch; }
-  p.stages = std::min(kMaxStages, (smem_budget - kRingOff) / stage_bytes);
+  while ((smem_budget - fixed) / stage_bytes < 2 && p.rps > kGroups) {
+    p.rps -= kGroups;
+    while (S % p.rps) p.rps -= kGroups;
+    stage_bytes = 2 * p.rps * p.pitch;
+  }
+  p.stages = std::min(kMaxStages, (smem_budget - fixed) / stage_bytes);
   if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: max_width %d does not fit the shared-memory ring", d->max_width);
-  const size_t smem = (size_t)kRingOff + (size_t)p.stages * stage_bytes;
+  const size_t smem = (size_t)fixed + (size_t)p.stages * stage_bytes;
 
   const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)di.max_smem / (smem + 1024)));
   const int grid_max = di.sms * ctas_per_sm;
@@ -404,12 +606,12 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
     if (rb % p.rps) continue;
     if (forced ? rb == forced : (int64_t)frames * (S / rb) >= 8LL * grid_max) { p.rows_per_band = rb; break; }
   }
+  if (mode == MODE_VIVIT) p.rows_per_band = S;  // the Pillow stage needs the whole frame on chip
   p.bands = S / p.rows_per_band;
   p.total_items = frames * p.bands;
   const int grid = std::min(p.total_items, grid_max);
-
-  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_cv2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lvc_clip_cv2_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
-  LVC_CUDA_TRY(cudaGetLastError());
-  return LVC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (mode == MODE_CV2) return launch<MODE_CV2>(p, grid, smem, st);
+  if (mode == MODE_VIVIT) return launch<MODE_VIVIT>(p, grid, smem, st);
+  return launch<MODE_PTV>(p, grid, smem, st);
 }

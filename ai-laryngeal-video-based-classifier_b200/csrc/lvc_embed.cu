@@ -87,6 +87,54 @@ __global__ void lvc_im2col_kernel(const TIn* __restrict__ x, __nv_bfloat16* __re
   }
 }
 
+// Vectorised variant for the shipped patch shapes (kw = 16 or 4, no padding, 16-byte aligned rows):
+// a thread converts ROWS x KW pixels with 16-byte loads and writes one contiguous bf16 run of A.
+template <typename TIn, int KW, int ROWS>
+__global__ void lvc_im2col_vec_kernel(const TIn* __restrict__ x, __nv_bfloat16* __restrict__ a, EmbedGeom g, int bcthw) {
+  const unsigned dys = g.kh / ROWS;
+  const unsigned runs = (unsigned)g.M * 3u * g.kt * dys;
+  for (unsigned r = blockIdx.x * blockDim.x + threadIdx.x; r < runs; r += gridDim.x * blockDim.x) {
+    unsigned q = r;
+    const unsigned wo = q % g.Wo; q /= g.Wo;
+    const unsigned dyb = q % dys; q /= dys;
+    const unsigned ho = q % g.Ho; q /= g.Ho;
+    const unsigned dt = q % g.kt; q /= g.kt;
+    const unsigned c = q % 3u; q /= 3u;
+    const unsigned to = q % g.To; q /= g.To;
+    const unsigned b = q;
+    const unsigned t = to * g.kt + dt, y = ho * g.kh + dyb * ROWS, x0 = wo * KW;
+    const size_t m = (((size_t)b * g.To + to) * g.Ho + ho) * g.Wo + wo;
+    __nv_bfloat16* dst = a + m * g.K + ((c * g.kt + dt) * g.kh + dyb * ROWS) * KW;
+    const size_t src = bcthw ? ((((size_t)b * 3 + c) * g.T + t) * g.H + y) * g.W + x0
+                             : ((((size_t)b * g.T + t) * 3 + c) * g.H + y) * g.W + x0;
+    uint32_t packed[ROWS * KW / 2];
+#pragma unroll
+    for (int rr = 0; rr < ROWS; ++rr) {
+      const TIn* sp = x + src + (size_t)rr * g.W;
+      if constexpr (sizeof(TIn) == 4) {
+#pragma unroll
+        for (int i = 0; i < KW / 4; ++i) {
+          const float4 f = __ldcs(reinterpret_cast<const float4*>(sp) + i);
+          __nv_bfloat162 lo = __floats2bfloat162_rn(f.x, f.y), hi = __floats2bfloat162_rn(f.z, f.w);
+          packed[rr * KW / 2 + 2 * i] = *reinterpret_cast<uint32_t*>(&lo);
+          packed[rr * KW / 2 + 2 * i + 1] = *reinterpret_cast<uint32_t*>(&hi);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < KW / 4; ++i) {
+          const uint2 u = __ldcs(reinterpret_cast<const uint2*>(sp) + i);
+          packed[rr * KW / 2 + 2 * i] = u.x;
+          packed[rr * KW / 2 + 2 * i + 1] = u.y;
+        }
+      }
+    }
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+    for (int i = 0; i < ROWS * KW / 8; ++i)
+      d4[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+  }
+}
+
 // conv weight (N, 3, kt, kh, kw) fp32 is already [N][K] row-major: packing = bf16 rounding.
 __global__ void lvc_pack_w_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ o, long long n) {
   for (long long i = 1LL * blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 1LL * gridDim.x * blockDim.x)
@@ -198,7 +246,7 @@ struct GemmParams {
   void* out;
 };
 
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kGemmThreads, 2)
 lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                       const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -212,6 +260,12 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   uint64_t* tmem_full = empty + p.stages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);  // N floats, then LayerNorm weight / bias (BN each)
+  float* s_lnw = s_bias + p.N;
+  float* s_lnb = s_lnw + p.BN;
+  for (int i = threadIdx.x; i < p.N; i += kGemmThreads) s_bias[i] = p.bias[i];
+  if (p.do_ln)
+    for (int i = threadIdx.x; i < p.BN; i += kGemmThreads) { s_lnw[i] = p.ln_w[i]; s_lnb[i] = p.ln_b[i]; }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
@@ -283,30 +337,38 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
       const int nchunks = p.BN / 32;
       float mean = 0.f, rstd = 1.f;
       float v[32];
-      if (p.do_ln) {  // LayerNorm over the N = BN columns this thread owns (one token row)
-        float sum = 0.f;
+      const float* sb = s_bias + n_blk * p.BN;
+      if (p.do_ln) {  // LayerNorm over the N = BN columns this thread owns (one token row): one stats pass
+        float sum = 0.f, sq = 0.f;
         for (int ch = 0; ch < nchunks; ++ch) {
           tmem_ld32(taddr + ch * 32, v);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) sum += v[j] + __ldg(p.bias + ch * 32 + j);
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b4 = reinterpret_cast<const float4*>(sb + ch * 32)[j4];
+            const float z0 = v[4 * j4] + b4.x, z1 = v[4 * j4 + 1] + b4.y, z2 = v[4 * j4 + 2] + b4.z, z3 = v[4 * j4 + 3] + b4.w;
+            sum += (z0 + z1) + (z2 + z3);
+            sq = fmaf(z0, z0, fmaf(z1, z1, fmaf(z2, z2, fmaf(z3, z3, sq))));
+          }
         }
         mean = sum / (float)p.N;
-        float sq = 0.f;
-        for (int ch = 0; ch < nchunks; ++ch) {
-          tmem_ld32(taddr + ch * 32, v);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) { const float dlt = v[j] + __ldg(p.bias + ch * 32 + j) - mean; sq += dlt * dlt; }
-        }
-        rstd = rsqrtf(sq / (float)p.N + p.ln_eps);
+        rstd = rsqrtf(fmaxf(sq / (float)p.N - mean * mean, 0.f) + p.ln_eps);
       }
       for (int ch = 0; ch < nchunks; ++ch) {
         tmem_ld32(taddr + ch * 32, v);
         const int n0 = n_blk * p.BN + ch * 32;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float y = v[j] + __ldg(p.bias + n0 + j);
-          if (p.do_ln) y = (y - mean) * rstd * __ldg(p.ln_w + n0 + j) + __ldg(p.ln_b + n0 + j);
-          v[j] = y;
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 b4 = reinterpret_cast<const float4*>(sb + ch * 32)[j4];
+          v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
+          if (p.do_ln) {
+            const float4 g4 = reinterpret_cast<const float4*>(s_lnw + ch * 32)[j4];
+            const float4 o4 = reinterpret_cast<const float4*>(s_lnb + ch * 32)[j4];
+            float tt;
+            tt = rstd * g4.x; v[4 * j4] = fmaf(v[4 * j4], tt, fmaf(-mean, tt, o4.x));
+            tt = rstd * g4.y; v[4 * j4 + 1] = fmaf(v[4 * j4 + 1], tt, fmaf(-mean, tt, o4.y));
+            tt = rstd * g4.z; v[4 * j4 + 2] = fmaf(v[4 * j4 + 2], tt, fmaf(-mean, tt, o4.z));
+            tt = rstd * g4.w; v[4 * j4 + 3] = fmaf(v[4 * j4 + 3], tt, fmaf(-mean, tt, o4.w));
+          }
         }
         if (valid) {
           if (p.out_f32) {
@@ -430,7 +492,19 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
     const long long runs = 1LL * g.M * 3 * g.kt * g.kh;
     const int blocks = (int)std::min<long long>((runs + 255) / 256, (long long)sms * 16);
     const int bcthw = d->x_layout == LVC_LAYOUT_BCTHW;
-    if (d->x_dtype == LVC_DT_F32)
+    const size_t esz = d->x_dtype == LVC_DT_F32 ? 4 : 2;
+    const bool vec_ok = g.T % g.kt == 0 && g.H % g.kh == 0 && g.W % g.kw == 0 && (g.W * esz) % 16 == 0 &&
+                        (reinterpret_cast<uintptr_t>(x) & 15) == 0 && runs < (1LL << 31) && !getenv("LVC_IM2COL_SCALAR");
+    __nv_bfloat16* A = static_cast<__nv_bfloat16*>(workspace);
+    if (vec_ok && g.kw == 16) {
+      const int nb = (int)((runs + 255) / 256);
+      if (d->x_dtype == LVC_DT_F32) lvc_im2col_vec_kernel<float, 16, 1><<<nb, 256, 0, st>>>(static_cast<const float*>(x), A, g, bcthw);
+      else lvc_im2col_vec_kernel<__nv_bfloat16, 16, 1><<<nb, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), A, g, bcthw);
+    } else if (vec_ok && g.kw == 4 && g.kh == 4) {
+      const int nb = (int)((runs / 4 + 255) / 256);
+      if (d->x_dtype == LVC_DT_F32) lvc_im2col_vec_kernel<float, 4, 4><<<nb, 256, 0, st>>>(static_cast<const float*>(x), A, g, bcthw);
+      else lvc_im2col_vec_kernel<__nv_bfloat16, 4, 4><<<nb, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), A, g, bcthw);
+    } else if (d->x_dtype == LVC_DT_F32)
       lvc_im2col_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(workspace), g, bcthw);
     else
       lvc_im2col_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(workspace), g, bcthw);
@@ -453,7 +527,7 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   const int stage_bytes = (BM + p.BN) * p.BK * 2;
   p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (max_smem - 2048) / stage_bytes, std::max(2, p.num_k_blocks * 2)});
   if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "patch_embed: tile does not fit shared memory");
-  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 4) * 8 + 16;
+  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 4) * 8 + 16 + (size_t)(g.N + 2 * p.BN) * 4 + 16;
 
   CUtensorMap map_a, map_b;
   rc = make_map(&map_a, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
@@ -461,7 +535,9 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   rc = make_map(&map_b, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)p.BN);
   if (rc != LVC_OK) return rc;
   LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int grid = std::min(sms, p.m_tiles * p.n_tiles);
+  // two CTAs per SM when shared memory and TMEM (2 x <=256 columns) allow: doubles the epilogue warps
+  const int per_sm = (p.tmem_cols <= 256 && 2 * (smem + 1024) <= (size_t)max_smem) ? 2 : 1;
+  const int grid = std::min(sms * per_sm, p.m_tiles * p.n_tiles);
   lvc_embed_gemm_kernel<<<grid, kGemmThreads, smem, st>>>(map_a, map_b, p);
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;

@@ -181,3 +181,48 @@ def test_full_size_properties_1080p():
     assert torch.equal(cb([small], [list(range(T))])[0], small)
     const = torch.full((2, 1080, 1920, 3), 137, dtype=torch.uint8, device="cuda")
     assert bool((ClipBuilder("dataset_u8", num_frames=2)([const], [[0, 1]]) == 137).all())
+
+
+def test_vivit_preset_fuses_pillow_stage(golden):
+    """cv2 resize -> VivitImageProcessor (Pillow 224->256, crop 224, rescale+offset, normalise) in one kernel."""
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.synth import synth_video
+
+    # golden: the HF processor's own output on 224x224 frames (the cv2 stage is the identity there)
+    g = golden("pixels.npz")
+    fr = synth_video(111, 4, 224, 224)
+    out = ClipBuilder("vivit", num_frames=4)([torch.from_numpy(fr).cuda()], [[0, 1, 2, 3]]).cpu().numpy()
+    assert list(out.shape) == g["vivit_shape"].tolist()
+    assert sha(out) == str(g["vivit_sha"])
+    # general sources, ROI boxes, ragged batch
+    T = 8
+    host, dev = _videos([(51, 10, 720, 1280, "noise"), (52, 9, 480, 640, "ramp"), (53, 8, 100, 150, "noise"),
+                         (54, 8, 1080, 1920, "noise")])
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    out = ClipBuilder("vivit", num_frames=T)(dev, idx).cpu().numpy()
+    for b, v in enumerate(host):
+        want = op.vivit_processor(op.resize_clip_cv2(v[idx[b]]))
+        assert np.abs(out[b] - want).max() <= 1e-5
+        assert (out[b] != want).sum() == 0
+
+
+def test_ptv_eval_preset_matches_torch_chain():
+    """ShortSideScale(256) + CenterCrop(224) + Normalize on 0..255 floats.  Tolerance:
+    values reach 1131, so 1e-5 is read relative to the range: atol 1.1e-2, rtol 1e-5."""
+    from lvc_b200 import ClipBuilder
+
+    T = 4
+    host, dev = _videos([(61, 6, 720, 1280, "noise"), (62, 5, 480, 640, "ramp"), (63, 5, 640, 480, "noise"),
+                         (64, 4, 300, 300, "noise"), (65, 4, 1080, 1920, "noise")])
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    cb = ClipBuilder("ptv_eval", num_frames=T)
+    out = cb(dev, idx).cpu().numpy()
+    assert out.shape == (len(host), 3, T, 224, 224)
+    worst = 0.0
+    for b, v in enumerate(host):
+        want = op.ptv_eval_chain(v[idx[b]])
+        assert np.allclose(out[b], want, atol=1.1e-2, rtol=1e-5)
+        worst = max(worst, float(np.abs(out[b] - want).max()))
+    print("ptv_eval max abs err", worst)
+    with pytest.raises(NotImplementedError):
+        cb(dev, idx, boxes=np.zeros((len(host), T, 4), np.int32))
