@@ -15,4 +15,8 @@ def __getattr__(name):  # torch-dependent parts load lazily
         from . import clips
 
         return getattr(clips, name)
+    if name in ("clips", "datasets", "dataloader", "processors", "patch_embed", "decode", "sharding"):
+        import importlib
+
+        return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

@@ -1,0 +1,138 @@
+"""Drop-in image processors / transforms: the callables the reference's trainers invoke in
+``_process_batch`` (on the CPU, per frame), re-backed by the fused CUDA clip kernel.
+
+  VivitImageProcessor            vivit .../trainers/trainer.py:22-26,62-95; evaluator.py:25,64-67;
+                                 vivit_transformer/inference.py:181-187; data_preprocessing.py:7,16
+  TimesformerImageProcessor      timesformer .../trainers/trainer.py:22-24,91-98 (a VideoMAE-class
+                                 processor forced to size = crop_size = 224)
+  PtvEvalTransform               the pytorchvideo eval chain applied as ``transform({"video": ...})``
+                                 (resnet50-2d-lstm/src/data_config/dataset.py:63-83,204-208)
+
+Call signature and result follow the HF processors: ``proc(images, return_tensors="pt", **kw)`` returns
+a mapping with ``"pixel_values"``: float32 ``(B, T, 3, 224, 224)`` (B = 1 for one video), supporting
+``.keys()``, ``[k]``, ``.items()`` -- but the tensor is already on the GPU, so the caller's ``.to(device)``
+is a no-op.  Frames must be uint8 RGB; any source size is resized with cv2-exact bilinear first (the
+reference always hands over 224x224 frames, where that stage is the identity).
+"""
+import numpy as np
+import torch
+
+from .clips import KINETICS, ClipBuilder
+
+
+class BatchFeature(dict):
+    """Minimal stand-in for transformers.BatchFeature: a dict with ``.to()``."""
+
+    def to(self, *a, **k):
+        return BatchFeature({key: v.to(*a, **k) for key, v in self.items()})
+
+
+def _as_videos(images, device):
+    """Normalise the accepted inputs to a list of CUDA uint8 (T,H,W,3) tensors."""
+    def one(v):
+        t = torch.from_numpy(np.ascontiguousarray(v)) if isinstance(v, np.ndarray) else v
+        if t.dtype != torch.uint8:
+            raise ValueError("frames must be uint8 RGB (the reference casts to uint8 before the processor)")
+        return t.to(device, non_blocking=True).contiguous()
+
+    if isinstance(images, (np.ndarray, torch.Tensor)):
+        if images.ndim == 3:
+            return [one(images)[None]]
+        if images.ndim == 4:
+            return [one(images)]
+        if images.ndim == 5:
+            return [one(v) for v in images]
+        raise ValueError(f"unsupported input shape {tuple(images.shape)}")
+    images = list(images)
+    if not images:
+        raise ValueError("no frames given")
+    if images[0].ndim == 3:  # list of HWC frames = one video
+        if isinstance(images[0], np.ndarray):
+            return [one(np.stack(images))]
+        return [one(torch.stack(list(images)))]
+    return [one(v) for v in images]  # list of (T,H,W,3) videos
+
+
+class _ClipProcessor:
+    preset = None
+
+    def __init__(self, image_mean=None, image_std=None, device=None, **ignored):
+        # the reference passes extra kwargs (num_frames, image_size, patch_size) the HF class ignores
+        self.image_mean, self.image_std = image_mean, image_std
+        self.size = {"height": 224, "width": 224}
+        self.crop_size = {"height": 224, "width": 224}
+        self.device = device
+        self._builders = {}
+
+    def _builder(self, T):
+        if T not in self._builders:
+            self._builders[T] = ClipBuilder(self.preset, num_frames=T, mean=self.image_mean, std=self.image_std,
+                                            device=self.device)
+        return self._builders[T]
+
+    def _check(self, kw):
+        for key in ("size", "crop_size"):
+            v = kw.get(key)
+            if v is not None and (v.get("height", 224) != 224 or v.get("width", 224) != 224):
+                raise NotImplementedError(f"{key}={v}: only 224x224 is supported")
+
+    def __call__(self, images=None, return_tensors="pt", videos=None, **kw):
+        if images is None:
+            images = videos
+        if return_tensors not in ("pt", None):
+            raise ValueError("only return_tensors='pt' is supported")
+        self._check(kw)
+        dev = torch.device(self.device if self.device is not None else f"cuda:{torch.cuda.current_device()}")
+        vids = _as_videos(images, dev)
+        T = vids[0].shape[0]
+        if any(v.shape[0] != T for v in vids):
+            raise ValueError("all videos of a batch must have the same number of frames")
+        idx = np.tile(np.arange(T, dtype=np.int32), (len(vids), 1))
+        return BatchFeature(pixel_values=self._builder(T)(vids, idx))
+
+    preprocess = __call__
+
+
+class VivitImageProcessor(_ClipProcessor):
+    """VivitImageProcessor defaults: shortest_edge 256 (Pillow bilinear), centre crop 224,
+    ``x/127.5 - 1``, mean/std 0.5 -> values in [-3, 1]."""
+
+    preset = "vivit"
+
+    def _check(self, kw):
+        super()._check(kw)
+        if kw.get("size") not in (None, {"shortest_edge": 256}) and "height" not in (kw.get("size") or {}):
+            raise NotImplementedError("only the default shortest_edge=256 geometry is fused")
+
+
+class TimesformerImageProcessor(_ClipProcessor):
+    """VideoMAE-class processor at size = crop_size = 224: ``x/255`` then ``(x - mean)/std``.  The
+    checkpoint's mean/std are not available offline: pass them, default 0.45/0.225."""
+
+    preset = "timesformer"
+
+    def __init__(self, image_mean=None, image_std=None, **kw):
+        super().__init__(image_mean if image_mean is not None else KINETICS[0],
+                         image_std if image_std is not None else KINETICS[1], **kw)
+
+
+class PtvEvalTransform:
+    """``transform({"video": float (C,T,H,W) 0..255, ...})`` -> same dict with "video" replaced by the
+    (C,T,224,224) result of UniformTemporalSubsample(T) -> ShortSideScale(256) -> CenterCrop(224) ->
+    Normalize(mean, std).  A uint8 (T,H,W,3) tensor under "video" skips the float round trip."""
+
+    def __init__(self, num_frames, mean=KINETICS[0], std=KINETICS[1], device=None):
+        self.num_frames = num_frames
+        self.builder = ClipBuilder("ptv_eval", num_frames=num_frames, mean=mean, std=std, device=device)
+
+    def __call__(self, sample):
+        from .sampling import uniform_temporal_subsample
+
+        v = sample["video"]
+        if v.dtype != torch.uint8:  # (C,T,H,W) float holding decoded integers
+            v = v.permute(1, 2, 3, 0).round().clamp(0, 255).to(torch.uint8)
+        v = v.to(self.builder.device).contiguous()
+        idx = uniform_temporal_subsample(v.shape[0], self.num_frames)
+        out = dict(sample)
+        out["video"] = self.builder([v], [idx])[0]
+        return out
