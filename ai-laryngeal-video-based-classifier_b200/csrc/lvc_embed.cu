@@ -246,11 +246,65 @@ struct GemmParams {
   void* out;
 };
 
+// Coalesced epilogue store: every thread owns one output row (TMEM lane); its `row_bytes` (64 or 128)
+// of packed results go through a warp-private, XOR-swizzled shared-memory tile so that the global
+// stores cover whole 128-byte lines (8 lanes x 16 B per row) instead of 32 scattered 16-byte pieces.
+__device__ __forceinline__ void stage_store_rows(uint8_t* stg, const uint32_t* pk, int lane, uint8_t* gbase,
+                                                 size_t row_stride, int rows_valid, int row_bytes) {
+  const int cpr = row_bytes >> 4;  // 16-byte chunks per row: 4 or 8
+  __syncwarp();
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < cpr)
+      *reinterpret_cast<uint4*>(stg + lane * row_bytes + ((j ^ (lane & (cpr - 1))) << 4)) =
+          make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  __syncwarp();
+  const int rpi = 32 / cpr;  // rows covered by one warp-wide store
+  const int c = lane % cpr, r0 = lane / cpr;
+#pragma unroll
+  for (int it = 0; it < 8; ++it)
+    if (it < cpr) {
+      const int row = it * rpi + r0;
+      const uint4 val = *reinterpret_cast<const uint4*>(stg + row * row_bytes + ((c ^ (row & (cpr - 1))) << 4));
+      if (row < rows_valid) *reinterpret_cast<uint4*>(gbase + (size_t)row * row_stride + (c << 4)) = val;
+    }
+}
+// Packs 32 fp32 accumulator columns into the thread's staging words: bf16 -> 16 words at pk[half*16],
+// fp32 -> 32 words.
+template <int HALF>
+__device__ __forceinline__ void pack_bf16(const float* v, uint32_t* pk) {
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    pk[HALF * 16 + j] = *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+// Emits chunk `ch` (32 columns starting at n0) of this thread's row; flushes a full 128-byte staging
+// row (two bf16 chunks or one fp32 chunk) or the trailing 64-byte half row.
+__device__ __forceinline__ void emit_chunk(const float* v, uint32_t* pk, const GemmParams& p, uint8_t* stg, int lane,
+                                           long long m_warp0, int n0, int ch, int nchunks) {
+  const int rows_valid = (int)max(0LL, min(32LL, (long long)p.M - m_warp0));
+  const size_t esz = p.out_f32 ? 4 : 2;
+  const size_t stride = (size_t)p.N * esz;
+  uint8_t* rowbase = reinterpret_cast<uint8_t*>(p.out) + (size_t)m_warp0 * stride;
+  if (p.out_f32) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) pk[j] = __float_as_uint(v[j]);
+    stage_store_rows(stg, pk, lane, rowbase + (size_t)n0 * 4, stride, rows_valid, 128);
+  } else if (ch & 1) {
+    pack_bf16<1>(v, pk);
+    stage_store_rows(stg, pk, lane, rowbase + (size_t)(n0 - 32) * 2, stride, rows_valid, 128);
+  } else {
+    pack_bf16<0>(v, pk);
+    if (ch == nchunks - 1) stage_store_rows(stg, pk, lane, rowbase + (size_t)n0 * 2, stride, rows_valid, 64);
+  }
+}
+
 __global__ void __launch_bounds__(kGemmThreads, 2)
 lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                       const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);  // 1024-aligned, stays in the shared window
   const int span = p.BK * 2;                       // bytes per tile row = swizzle span
   const uint32_t a_bytes = BM * span, b_bytes = p.BN * span;
   uint8_t* smem_a = smem;
@@ -263,6 +317,7 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);  // N floats, then LayerNorm weight / bias (BN each)
   float* s_lnw = s_bias + p.N;
   float* s_lnb = s_lnw + p.BN;
+  uint8_t* stg = reinterpret_cast<uint8_t*>(s_lnb + p.BN) + (size_t)(threadIdx.x >> 5 & 3) * 4096;  // per epilogue warp
   for (int i = threadIdx.x; i < p.N; i += kGemmThreads) s_bias[i] = p.bias[i];
   if (p.do_ln)
     for (int i = threadIdx.x; i < p.BN; i += kGemmThreads) { s_lnw[i] = p.ln_w[i]; s_lnb[i] = p.ln_b[i]; }
@@ -324,7 +379,6 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   } else {
     // ===================== epilogue: 4 warps, warp%4 selects its TMEM lane quarter =====================
     const int q = warp & 3;
-    const int row = q * 32 + lane;
     uint32_t local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int m_blk = tile / p.n_tiles, n_blk = tile - m_blk * p.n_tiles;
@@ -332,9 +386,10 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
       mb_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)p.BN;
-      const long long m = (long long)m_blk * BM + row;
-      const bool valid = m < p.M;
+      const long long m_warp0 = (long long)m_blk * BM + q * 32;
       const int nchunks = p.BN / 32;
+      const int NCH = nchunks;
+      uint32_t pk[32];
       float mean = 0.f, rstd = 1.f;
       float v[32];
       const float* sb = s_bias + n_blk * p.BN;
@@ -370,26 +425,7 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
             tt = rstd * g4.w; v[4 * j4 + 3] = fmaf(v[4 * j4 + 3], tt, fmaf(-mean, tt, o4.w));
           }
         }
-        if (valid) {
-          if (p.out_f32) {
-            float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + m * p.N + n0);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-          } else {
-            uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + m * p.N + n0);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * j], v[8 * j + 1]);
-              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
-              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
-              uint4 u;
-              u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
-              u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
-              o[j] = u;
-            }
-          }
-        }
+        emit_chunk(v, pk, p, stg, lane, m_warp0, n0, ch, NCH);
       }
       tc_fence_before();
       __syncwarp();
@@ -401,6 +437,175 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- 2-CTA (cta_group::2) GEMM ----
+// CTA pairs (cluster 2x1x1) cooperate on a 256 x BN tile: each CTA stages its own 128 rows of A and
+// HALF of the B tile, the leader CTA issues tcgen05.mma.cta_group::2 (M = 256) which reads both
+// halves, and each CTA's TMEM receives its 128 accumulator rows.  Per k-block a CTA pulls
+// (128 + BN/2) x 64 bf16 = 32 KB from L2 instead of 48 KB: the 1-CTA kernel is L2->SM feed-bound
+// (MMA issuer stalls on the `full` barriers), this cuts the feed by a third and deepens the ring.
+namespace {
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `p` (a local shared address) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mb_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* map, int c0, int c1, uint32_t bar_cluster_addr) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(s32(dst)), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(slot)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive (once the MMAs issued so far completed) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(s32(bar)), "h"((uint16_t)3) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                       const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);  // 1024-aligned, stays in the shared window
+  const int span = p.BK * 2;
+  const int half_n = p.BN / 2;
+  const uint32_t a_bytes = BM * span, b_bytes = half_n * span;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + (size_t)p.stages * a_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_b + (size_t)p.stages * b_bytes);
+  uint64_t* empty = full + p.stages;
+  uint64_t* tmem_full = empty + p.stages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);
+  for (int i = threadIdx.x; i < p.N; i += kGemmThreads) s_bias[i] = p.bias[i];
+  uint8_t* stg = reinterpret_cast<uint8_t*>(s_bias + p.N) + (size_t)(threadIdx.x >> 5 & 3) * 4096;  // per epilogue warp
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_rank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int num_units = p.m_tiles * p.n_tiles;  // m_tiles counts 256-row pair tiles here
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc_2sm(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // peer barriers are initialised before any remote signal
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs; bytes are counted on the LEADER's full barrier) =====
+    if (elect_one()) {
+      uint32_t it = 0;
+      for (int u = pair; u < num_units; u += num_pairs) {
+        const int m_pair = u / p.n_tiles, n_blk = u - m_pair * p.n_tiles;
+        const int row_a = m_pair * 2 * BM + (int)rank * BM;
+        const int row_b = n_blk * p.BN + (int)rank * half_n;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+          const int s = it % p.stages;
+          mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
+          if (leader) mb_expect_tx(&full[s], 2u * (a_bytes + b_bytes));
+          const uint32_t bar = mapa(s32(&full[s]), 0);
+          tma_load_2d_2sm(smem_a + (size_t)s * a_bytes, &map_a, kb * p.BK, row_a, bar);
+          tma_load_2d_2sm(smem_b + (size_t)s * b_bytes, &map_b, kb * p.BK, row_b, bar);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && elect_one()) {
+      const uint32_t idesc = make_idesc(2 * BM, p.BN);
+      uint32_t it = 0, local = 0;
+      for (int u = pair; u < num_units; u += num_pairs, ++local) {
+        const uint32_t acc = local & 1u, acc_phase = (local >> 1) & 1u;
+        mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.BN;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+          const int s = it % p.stages;
+          mb_wait(&full[s], (it / p.stages) & 1u);
+          tc_fence_after();
+          const uint64_t adesc = make_smem_desc(s32(smem_a + (size_t)s * a_bytes), span);
+          const uint64_t bdesc = make_smem_desc(s32(smem_b + (size_t)s * b_bytes), span);
+          for (int k = 0; k < p.BK / 16; ++k)
+            umma_bf16_2sm(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+          umma_commit_2sm(&empty[s]);
+        }
+        umma_commit_2sm(&tmem_full[acc]);
+      }
+    }
+  } else {
+    // ===================== epilogue (both CTAs, own 128 rows) =====================
+    const int q = warp & 3;
+    const uint32_t leader_tmem_empty0 = mapa(s32(&tmem_empty[0]), 0);
+    uint32_t local = 0;
+    for (int u = pair; u < num_units; u += num_pairs, ++local) {
+      const int m_pair = u / p.n_tiles, n_blk = u - m_pair * p.n_tiles;
+      const uint32_t acc = local & 1u, acc_phase = (local >> 1) & 1u;
+      mb_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)p.BN;
+      const long long m_warp0 = (long long)m_pair * 2 * BM + (long long)rank * BM + q * 32;
+      const float* sb = s_bias + n_blk * p.BN;
+      const int NCH = p.BN / 32;
+      float v[32];
+      uint32_t pk[32];
+      for (int ch = 0; ch < NCH; ++ch) {
+        tmem_ld32(taddr + ch * 32, v);
+        const int n0 = n_blk * p.BN + ch * 32;
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 b4 = reinterpret_cast<const float4*>(sb + ch * 32)[j4];
+          v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
+        }
+        emit_chunk(v, pk, p, stg, lane, m_warp0, n0, ch, NCH);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mb_arrive_cluster(leader_tmem_empty0 + acc * 8u);  // the MMA issuer lives in the leader
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // nobody exits while the peer may still signal its barriers
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, p.tmem_cols);
   }
 }
 
@@ -525,18 +730,44 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   p.out_f32 = d->out_dtype == LVC_DT_F32;
   p.out = out;
   const int stage_bytes = (BM + p.BN) * p.BK * 2;
-  p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (max_smem - 2048) / stage_bytes, std::max(2, p.num_k_blocks * 2)});
+  const int fixed_bytes = 1024 + 2048 + (g.N + 2 * p.BN) * 4 + 16384;  // alignment, barriers, params, store staging
+  // two CTAs per SM when TMEM (2 x <=256 columns) and shared memory allow: doubles the epilogue warps,
+  // which is what bounds the HBM-bound Swin shape
+  int per_sm = (p.tmem_cols <= 256 && !getenv("LVC_GEMM_ONE_PER_SM")) ? 2 : 1;
+  int sm_smem = 0;
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+  for (;; per_sm = 1) {
+    const int budget = per_sm == 2 ? std::min(max_smem, sm_smem / 2 - 1024) : max_smem;
+    p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (budget - fixed_bytes) / stage_bytes, std::max(2, p.num_k_blocks * 2)});
+    if (per_sm == 1 || p.stages >= std::min(3, p.num_k_blocks + 1)) break;
+  }
   if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "patch_embed: tile does not fit shared memory");
-  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 4) * 8 + 16 + (size_t)(g.N + 2 * p.BN) * 4 + 16;
+  const size_t smem = (size_t)fixed_bytes + (size_t)p.stages * stage_bytes;
 
+  // tensor-bound shapes (no LayerNorm, 128B-swizzle K blocks, even tile split): CTA-pair kernel
+  const bool two_cta = !p.do_ln && p.BK == 64 && p.BN % 64 == 0 && p.BN >= 64 && !getenv("LVC_GEMM_1CTA") && sms >= 2;
+  if (two_cta) {
+    const int stage2 = (BM + p.BN / 2) * p.BK * 2;
+    p.m_tiles = (g.M + 2 * BM - 1) / (2 * BM);
+    p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (max_smem - 2048 - g.N * 4 - 16384) / stage2, std::max(2, p.num_k_blocks * 2)});
+    const size_t smem2 = 1024 + (size_t)p.stages * stage2 + (2 * p.stages + 4) * 8 + 16 + (size_t)g.N * 4 + 16 + 16384;
+    CUtensorMap ma, mb;
+    rc = make_map(&ma, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
+    if (rc != LVC_OK) return rc;
+    rc = make_map(&mb, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)(p.BN / 2));
+    if (rc != LVC_OK) return rc;
+    LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    const int pairs = std::min(sms / 2, p.m_tiles * p.n_tiles);
+    lvc_embed_gemm2_kernel<<<2 * pairs, kGemmThreads, smem2, st>>>(ma, mb, p);
+    LVC_CUDA_TRY(cudaGetLastError());
+    return LVC_OK;
+  }
   CUtensorMap map_a, map_b;
   rc = make_map(&map_a, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
   if (rc != LVC_OK) return rc;
   rc = make_map(&map_b, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)p.BN);
   if (rc != LVC_OK) return rc;
   LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // two CTAs per SM when shared memory and TMEM (2 x <=256 columns) allow: doubles the epilogue warps
-  const int per_sm = (p.tmem_cols <= 256 && 2 * (smem + 1024) <= (size_t)max_smem) ? 2 : 1;
   const int grid = std::min(sms * per_sm, p.m_tiles * p.n_tiles);
   lvc_embed_gemm_kernel<<<grid, kGemmThreads, smem, st>>>(map_a, map_b, p);
   LVC_CUDA_TRY(cudaGetLastError());
