@@ -14,7 +14,7 @@ SAMPLE = {"uniform": 0, "random_window": 1, "random": 2}
 VARIANT_DATASET, VARIANT_CLAMPED, VARIANT_NUMPY_INFER = 0, 1, 2
 LUT_DIV, LUT_MUL64 = 0, 1
 RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL = 0, 1, 2
-LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC = 0, 1, 2
+LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC, LAYOUT_TOKENS = 0, 1, 2, 3
 DT_F32, DT_BF16, DT_U8 = 0, 1, 2
 EMBED_VIVIT, EMBED_TIMESFORMER, EMBED_SWIN = 0, 1, 2
 
@@ -31,7 +31,7 @@ class Video(C.Structure):
 class ClipDesc(C.Structure):
     _fields_ = [("resample", C.c_int32), ("layout", C.c_int32), ("out_dtype", C.c_int32),
                 ("out_size", C.c_int32), ("batch", C.c_int32), ("num_frames", C.c_int32),
-                ("max_width", C.c_int32), ("reserved", C.c_int32),
+                ("max_width", C.c_int32), ("tok_kt", C.c_int32), ("tok_kh", C.c_int32), ("tok_kw", C.c_int32),
                 ("mean", C.c_float * 3), ("std", C.c_float * 3)]
 
 

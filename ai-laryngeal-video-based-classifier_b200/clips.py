@@ -20,7 +20,8 @@ from . import _lib
 IMAGENET_STANDARD = ((0.5, 0.5, 0.5), (0.5, 0.5, 0.5))
 KINETICS = ((0.45, 0.45, 0.45), (0.225, 0.225, 0.225))
 
-_LAYOUTS = {"BTCHW": _lib.LAYOUT_BTCHW, "BCTHW": _lib.LAYOUT_BCTHW, "BTHWC": _lib.LAYOUT_BTHWC}
+_LAYOUTS = {"BTCHW": _lib.LAYOUT_BTCHW, "BCTHW": _lib.LAYOUT_BCTHW, "BTHWC": _lib.LAYOUT_BTHWC,
+            "TOKENS": _lib.LAYOUT_TOKENS}
 _DTYPES = {torch.float32: _lib.DT_F32, torch.bfloat16: _lib.DT_BF16, torch.uint8: _lib.DT_U8}
 
 # name -> (resample, lut kind, lut scale, offset, (mean, std), layout, dtype)
@@ -60,7 +61,10 @@ def tapped_row_bytes(videos, indices, boxes, T, S=224):
     return int(total)
 
 
-def _shape(layout, B, T, S=224):
+def _shape(layout, B, T, S=224, patch=None):
+    if layout == "TOKENS":
+        kt, kh, kw = patch
+        return (B * (T // kt) * (S // kh) * (S // kw), 3 * kt * kh * kw)
     return {"BTCHW": (B, T, 3, S, S), "BCTHW": (B, 3, T, S, S), "BTHWC": (B, T, S, S, 3)}[layout]
 
 
@@ -73,7 +77,7 @@ class ClipBuilder:
     """
 
     def __init__(self, preset="resnet_infer", num_frames=32, mean=None, std=None, layout=None, dtype=None,
-                 device=None):
+                 device=None, patch=None):
         if preset not in PRESETS:
             raise ValueError(f"unknown preset {preset!r}; choose from {sorted(PRESETS)}")
         if not torch.cuda.is_available():
@@ -84,6 +88,12 @@ class ClipBuilder:
         self.std = tuple(float(v) for v in (std if std is not None else s))
         self.layout = layout or lay
         self.dtype = dtype or dt
+        # layout="TOKENS": write the bf16 patch matrix A[M][K] of a (kt,kh,kw) patch embedding directly
+        self.patch = tuple(int(v) for v in patch) if patch is not None else (0, 0, 0)
+        if self.layout == "TOKENS":
+            if patch is None:
+                raise ValueError("layout='TOKENS' needs patch=(kt, kh, kw)")
+            self.dtype = torch.bfloat16
         if self.layout not in _LAYOUTS or self.dtype not in _DTYPES:
             raise ValueError(f"unsupported layout/dtype {self.layout}/{self.dtype}")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -129,9 +139,10 @@ class ClipBuilder:
         and return a ``ClipBatch`` that ``run`` can launch any number of times."""
         B, T = len(videos), self.num_frames
         tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes)
-        d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, 0,
+        d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, *self.patch,
                           (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std))
-        return ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos), _shape(self.layout, B, T))
+        return ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
+                         _shape(self.layout, B, T, patch=self.patch))
 
     def run(self, batch, out=None, stats=None):
         """Enqueue the fused kernel for a prepared batch on the current stream (no synchronisation)."""
@@ -153,7 +164,8 @@ class ClipBuilder:
         output; stats: optional CUDA int64 (B,) checksum accumulator.  Returns the clip tensor
         (enqueued on the current stream, not synchronised)."""
         if len(videos) == 0:
-            return torch.empty(_shape(self.layout, 0, self.num_frames), dtype=self.dtype, device=self.device)
+            return torch.empty(_shape(self.layout, 0, self.num_frames, patch=self.patch), dtype=self.dtype,
+                               device=self.device)
         batch = self.prepare(videos, indices, boxes)
         out = self.run(batch, out, stats)
         batch.tables.record_stream(torch.cuda.current_stream(self.device))

@@ -59,6 +59,7 @@ struct ClipParams {
   int total_items;           // B*T*bands
   int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
   float mean[3], std[3];     // PTV normalisation
+  int kt, kh, kw;            // LVC_LAYOUT_TOKENS: patch size; output is the GEMM operand A[M][K] (bf16)
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------
@@ -186,6 +187,29 @@ __device__ __forceinline__ void consumers_bar() {
 }  // namespace
 
 namespace {
+
+// Element offset of output sample (frame f = b*T + t, channel 0, row y, column 0) and the channel
+// stride, for every layout; the per-thread column term comes from col_offset().  LVC_LAYOUT_TOKENS
+// writes the patch-embedding operand A[m][k] directly: m = ((b*To + t/kt)*Ho + y/kh)*Wo + x/kw,
+// k = ((c*kt + t%kt)*kh + y%kh)*kw + x%kw (token order of the reference modules).
+__device__ __forceinline__ size_t row_offset(const ClipParams& p, int f, int b, int t, int y, size_t& cstride) {
+  const size_t plane = (size_t)S * S;
+  switch (p.layout) {
+    case LVC_LAYOUT_BTCHW: cstride = plane; return (size_t)f * 3 * plane + (size_t)y * S;
+    case LVC_LAYOUT_BCTHW: cstride = (size_t)p.T * plane; return ((size_t)b * 3 * p.T + t) * plane + (size_t)y * S;
+    case LVC_LAYOUT_BTHWC: cstride = 1; return (size_t)f * plane * 3 + (size_t)y * S * 3;
+    default: {
+      const int To = p.T / p.kt, Ho = S / p.kh, Wo = S / p.kw, K = 3 * p.kt * p.kh * p.kw;
+      cstride = (size_t)p.kt * p.kh * p.kw;
+      return (((size_t)b * To + t / p.kt) * Ho + y / p.kh) * Wo * K + (size_t)((t % p.kt) * p.kh + y % p.kh) * p.kw;
+    }
+  }
+}
+__device__ __forceinline__ size_t col_offset(const ClipParams& p, int x) {
+  if (p.layout == LVC_LAYOUT_BTHWC) return (size_t)x * 3;
+  if (p.layout == LVC_LAYOUT_TOKENS) return (size_t)(x / p.kw) * (3 * p.kt * p.kh * p.kw) + x % p.kw;
+  return (size_t)x;
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
@@ -332,7 +356,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
   int acc_b = -1;
   uint32_t it = 0;
-  const size_t plane = (size_t)S * S;
+  const size_t xoff = col_offset(p, x);
   // MODE_VIVIT state: Pillow horizontal taps of this thread's column, row-buffer parity
   int4 hx = make_int4(0, 0, 0, 0);
   int parity = 0;
@@ -379,21 +403,18 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
         acc = 0; acc_b = b;
       }
-      // element offsets of channel 0 of this frame and the channel stride
-      size_t base, cstride;
-      if (p.layout == LVC_LAYOUT_BTCHW) { base = (size_t)f * 3 * plane; cstride = plane; }
-      else if (p.layout == LVC_LAYOUT_BCTHW) { base = ((size_t)b * 3 * p.T + t) * plane; cstride = (size_t)p.T * plane; }
-      else { base = (size_t)f * plane * 3; cstride = 1; }
       for (int r = g; r < p.rps; r += kGroups) {
         const RowDesc rd = h->rows[r];
         const uint8_t* p0 = ring + rd.off0 + xo;
         const uint8_t* p1 = ring + rd.off1 + xo;
         const int oyr = oy0 + r;
+        size_t cstride;
+        const size_t eoff = row_offset(p, f, b, t, oyr, cstride) + xoff;  // element offset of channel 0
         if (MODE == MODE_PTV) {
           // torch CPU blend order: r = fma(p_x0, lx0, p_x1*lx1) per row, out = fma(r_y0, ly0, r_y1*ly1)
           const float ly0 = __int_as_float(rd.b0), ly1 = __int_as_float(rd.b1);
-          float* o = reinterpret_cast<float*>(p.out) + base + (size_t)oyr * S + x;
-          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + base + (size_t)oyr * S + x;
+          float* o = reinterpret_cast<float*>(p.out) + eoff;
+          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
             const float r0 = __fmaf_rn((float)p0[c], lx0, __fmul_rn((float)p0[c + d1], lx1));
@@ -435,24 +456,17 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           continue;
         }
         if (p.out_dtype == LVC_DT_F32) {
-          float* o = reinterpret_cast<float*>(p.out) + base + (size_t)oyr * S + x;
+          float* o = reinterpret_cast<float*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
         } else if (p.out_dtype == LVC_DT_BF16) {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + base + (size_t)oyr * S + x;
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(lut[c * 256 + v[c]]);
         } else {
-          uint8_t* o = reinterpret_cast<uint8_t*>(p.out);
-          if (p.layout == LVC_LAYOUT_BTHWC) {
-            o += base + ((size_t)oyr * S + x) * 3;
+          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
 #pragma unroll
-            for (int c = 0; c < 3; ++c) o[c] = (uint8_t)v[c];
-          } else {
-            o += base + (size_t)oyr * S + x;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
-          }
+          for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
         }
       }
       __syncwarp();
@@ -462,12 +476,10 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       // the whole frame went through the horizontal pass: Pillow vertical pass + LUT + store
       consumers_bar();
       const int b = f / p.T, t = f - b * p.T;
-      size_t base, cstride;
-      if (p.layout == LVC_LAYOUT_BTCHW) { base = (size_t)f * 3 * plane; cstride = plane; }
-      else if (p.layout == LVC_LAYOUT_BCTHW) { base = ((size_t)b * 3 * p.T + t) * plane; cstride = (size_t)p.T * plane; }
-      else { base = (size_t)f * plane * 3; cstride = 1; }
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
       for (int y = g; y < S; y += kGroups) {
+        size_t cstride;
+        const size_t eoff = row_offset(p, f, b, t, y, cstride) + xoff;
         const int4 ty = vt[y];
         const uint8_t* tp = inter + ty.x * kRowBytes + x * 3;
         int v[3];
@@ -478,19 +490,15 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           v[c] = clip8(ss >> 22);
         }
         if (p.out_dtype == LVC_DT_F32) {
-          float* o = reinterpret_cast<float*>(p.out) + base + (size_t)y * S + x;
+          float* o = reinterpret_cast<float*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
         } else if (p.out_dtype == LVC_DT_BF16) {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + base + (size_t)y * S + x;
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(lut[c * 256 + v[c]]);
-        } else if (p.layout == LVC_LAYOUT_BTHWC) {
-          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + base + ((size_t)y * S + x) * 3;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) o[c] = (uint8_t)v[c];
         } else {
-          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + base + (size_t)y * S + x;
+          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
         }
@@ -552,8 +560,13 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
   if (d->out_size != S) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: out_size %d unsupported (224 only)", d->out_size);
   if (d->batch <= 0 || d->num_frames <= 0 || d->max_width <= 0)
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: batch, num_frames and max_width must be positive");
-  if (d->layout < LVC_LAYOUT_BTCHW || d->layout > LVC_LAYOUT_BTHWC || d->out_dtype < LVC_DT_F32 || d->out_dtype > LVC_DT_U8)
+  if (d->layout < LVC_LAYOUT_BTCHW || d->layout > LVC_LAYOUT_TOKENS || d->out_dtype < LVC_DT_F32 || d->out_dtype > LVC_DT_U8)
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: unknown layout or dtype");
+  if (d->layout == LVC_LAYOUT_TOKENS) {
+    if (d->out_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: the token layout is the bf16 GEMM operand");
+    if (d->tok_kt <= 0 || d->tok_kh <= 0 || d->tok_kw <= 0 || d->num_frames % d->tok_kt || S % d->tok_kh || S % d->tok_kw)
+      return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: patch (%d,%d,%d) must divide (T,224,224)", d->tok_kt, d->tok_kh, d->tok_kw);
+  }
   if (d->resample < LVC_RESAMPLE_CV2 || d->resample > LVC_RESAMPLE_PTV_EVAL)
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: unknown resample mode %d", d->resample);
   if (d->layout == LVC_LAYOUT_BTHWC && d->out_dtype != LVC_DT_U8)
@@ -579,6 +592,7 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
   p.stats = reinterpret_cast<unsigned long long*>(stats);
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
   for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
+  p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
   // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
   p.rps = env_int("LVC_CLIP_RPS", 4);

@@ -658,7 +658,7 @@ extern "C" int64_t lvc_patch_embed_workspace(const lvc_embed_desc* d) {
   return ((int64_t)g.M * g.K * 2 + 255) / 256 * 256;
 }
 
-extern "C" int lvc_patch_embed_launch_count(const lvc_embed_desc* d) { return d ? 2 : 0; }
+extern "C" int lvc_patch_embed_launch_count(const lvc_embed_desc* d) { return d ? (d->x_layout == LVC_LAYOUT_TOKENS ? 1 : 2) : 0; }
 
 extern "C" int lvc_patch_embed_pack_weights(const lvc_embed_desc* d, const float* w_f32, void* w_packed, void* stream) {
   EmbedGeom g;
@@ -677,11 +677,18 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   EmbedGeom g;
   int rc = make_geom(d, &g);
   if (rc != LVC_OK) return rc;
-  if (!x || !w_packed || !bias || !out || !workspace) return lvc_fail(LVC_E_INVAL, "patch_embed: NULL pointer");
+  if (!x || !w_packed || !bias || !out || (!workspace && d->x_layout != LVC_LAYOUT_TOKENS)) return lvc_fail(LVC_E_INVAL, "patch_embed: NULL pointer");
   if (d->kind == LVC_EMBED_SWIN && (!ln_w || !ln_b)) return lvc_fail(LVC_E_INVAL, "patch_embed: Swin needs LayerNorm weight and bias");
   if (d->x_dtype != LVC_DT_F32 && d->x_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "patch_embed: x_dtype must be f32 or bf16");
   if (d->out_dtype != LVC_DT_F32 && d->out_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "patch_embed: out_dtype must be f32 or bf16");
-  if (d->x_layout != LVC_LAYOUT_BTCHW && d->x_layout != LVC_LAYOUT_BCTHW) return lvc_fail(LVC_E_INVAL, "patch_embed: x_layout must be BTCHW or BCTHW");
+  const bool tokens_in = d->x_layout == LVC_LAYOUT_TOKENS;
+  if (d->x_layout != LVC_LAYOUT_BTCHW && d->x_layout != LVC_LAYOUT_BCTHW && !tokens_in) return lvc_fail(LVC_E_INVAL, "patch_embed: x_layout must be BTCHW, BCTHW or TOKENS");
+  if (tokens_in) {
+    if (d->x_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "patch_embed: token input must be bf16");
+    if (reinterpret_cast<uintptr_t>(x) & 127) return lvc_fail(LVC_E_ALIGN, "patch_embed: token input needs 128-byte alignment");
+    if (g.T % g.kt || g.H % g.kh || g.W % g.kw) return lvc_fail(LVC_E_SHAPE, "patch_embed: token input cannot carry padding");
+    workspace = const_cast<void*>(x);  // the GEMM reads A straight from the clip kernel's output
+  }
   if ((reinterpret_cast<uintptr_t>(workspace) & 127) || (reinterpret_cast<uintptr_t>(w_packed) & 127) || (reinterpret_cast<uintptr_t>(out) & 15))
     return lvc_fail(LVC_E_ALIGN, "patch_embed: workspace / packed weights need 128-byte, out 16-byte alignment");
   if (g.N % 32) return lvc_fail(LVC_E_SHAPE, "patch_embed: embed_dim %d must be a multiple of 32", g.N);
@@ -692,8 +699,8 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   LVC_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   LVC_CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
 
-  // 1) im2col: x -> A[M][K] bf16
-  {
+  // 1) im2col: x -> A[M][K] bf16 (skipped when the clip kernel already wrote the tokens)
+  if (!tokens_in) {
     const long long runs = 1LL * g.M * 3 * g.kt * g.kh;
     const int blocks = (int)std::min<long long>((runs + 255) / 256, (long long)sms * 16);
     const int bcthw = d->x_layout == LVC_LAYOUT_BCTHW;

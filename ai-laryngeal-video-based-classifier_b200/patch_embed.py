@@ -47,7 +47,17 @@ class _EmbedBase(nn.Module):
         return _lib.EmbedDesc(self.kind, _DT[x.dtype], self.x_layout, _DT[self.out_dtype], B, T, H, W,
                               kt, kh, kw, conv.out_channels, float(self._ln()[2]), 0)
 
-    def _run(self, x, B, T, H, W, out_shape):
+    def forward_tokens(self, tokens, batch, frames, height=224, width=224):
+        """Embedding of a clip batch the fused clip kernel already wrote as the bf16 patch matrix
+        ``A[M][K]`` (``ClipBuilder(..., layout="TOKENS", patch=(kt,kh,kw))``): no im2col pass, one
+        launch.  Returns the flat ``(M, N)`` result; callers reshape to the module's output shape."""
+        conv = self._conv()
+        M = tokens.shape[0]
+        if tokens.dtype != torch.bfloat16 or tokens.dim() != 2 or not tokens.is_contiguous():
+            raise ValueError("tokens must be a contiguous bf16 (M, K) matrix")
+        return self._run(tokens, batch, frames, height, width, (M, conv.out_channels), layout=_lib.LAYOUT_TOKENS)
+
+    def _run(self, x, B, T, H, W, out_shape, layout=None):
         if not x.is_cuda:
             raise RuntimeError(f"{type(self).__name__}: input must be on a CUDA device (no CPU fallback)")
         if x.dtype not in _DT:
@@ -59,6 +69,8 @@ class _EmbedBase(nn.Module):
             raise RuntimeError("module parameters and input are on different devices")
         lib = _lib.lib()
         d = self._desc(x, B, T, H, W)
+        if layout is not None:
+            d.x_layout = layout
         stream = torch.cuda.current_stream(x.device).cuda_stream
         key = (w.data_ptr(), w._version, tuple(w.shape))
         if self._packed is None or self._packed_key != key:
@@ -70,8 +82,10 @@ class _EmbedBase(nn.Module):
         need = lib.lvc_patch_embed_workspace(C.byref(d))
         if need < 0:
             _lib.check(_lib.E_SHAPE, type(self).__name__)
+        if layout == _lib.LAYOUT_TOKENS:
+            need = 0
         if self._ws is None or self._ws.numel() < need or self._ws.device != x.device:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=x.device)
+            self._ws = torch.empty(max(need, 256), dtype=torch.uint8, device=x.device)
         out = torch.empty(out_shape, dtype=self.out_dtype, device=x.device)
         if bias is None:
             bias = torch.zeros(conv.out_channels, device=x.device)

@@ -117,7 +117,14 @@ enum {
    * (videoswintransformer/.../dataset.py:164-172).  Uses mean/std, not the LUT. */
   LVC_RESAMPLE_PTV_EVAL = 2
 };
-enum { LVC_LAYOUT_BTCHW = 0, LVC_LAYOUT_BCTHW = 1, LVC_LAYOUT_BTHWC = 2 };
+enum {
+  LVC_LAYOUT_BTCHW = 0,
+  LVC_LAYOUT_BCTHW = 1,
+  LVC_LAYOUT_BTHWC = 2,
+  /* the clip kernel writes the patch-embedding GEMM operand A[M][K] (bf16, token-major, K ordered
+   * (c,kt,kh,kw)) directly, so lvc_patch_embed can skip its im2col pass */
+  LVC_LAYOUT_TOKENS = 3
+};
 enum { LVC_DT_F32 = 0, LVC_DT_BF16 = 1, LVC_DT_U8 = 2 };
 
 typedef struct {
@@ -131,7 +138,7 @@ typedef struct {
   int32_t max_width;  /* largest frame width (pixels) among the B videos: sizes the shared-memory
                          row slots.  A wider video in `videos` is a contract violation (the kernel
                          traps). */
-  int32_t reserved;
+  int32_t tok_kt, tok_kh, tok_kw; /* LVC_LAYOUT_TOKENS: patch size, e.g. (2,16,16); else ignored */
   float mean[3];      /* PTV_EVAL only */
   float std[3];
 } lvc_clip_desc;
@@ -166,7 +173,8 @@ enum {
 typedef struct {
   int32_t kind;      /* LVC_EMBED_* */
   int32_t x_dtype;   /* LVC_DT_F32 or LVC_DT_BF16 */
-  int32_t x_layout;  /* LVC_LAYOUT_BTCHW (HF models) or LVC_LAYOUT_BCTHW (torchvision swin) */
+  int32_t x_layout;  /* LVC_LAYOUT_BTCHW (HF models), LVC_LAYOUT_BCTHW (torchvision swin), or
+                        LVC_LAYOUT_TOKENS: x already is A[M][K] bf16 from lvc_clip_forward */
   int32_t out_dtype; /* LVC_DT_BF16 or LVC_DT_F32 */
   int32_t batch, frames, height, width; /* B, T, H, W of x; channels are 3 */
   int32_t kt, kh, kw; /* patch size: (2,16,16) / (1,16,16) / (2,4,4) */

@@ -129,3 +129,33 @@ def test_clip_kernel_feeds_patch_embed():
     ref, _, _ = ope.timesformer_patch_embed(torch.from_numpy(want_clip), t.projection.weight.detach().cpu(),
                                             t.projection.bias.detach().cpu())
     check(emb, ref)
+
+
+@pytest.mark.parametrize("preset,kind", [("vivit", "vivit"), ("timesformer", "timesformer"), ("resnet_infer", "swin")])
+def test_fused_token_layout_skips_im2col(preset, kind):
+    """The clip kernel writes the bf16 patch matrix A[M][K] itself (layout TOKENS); the GEMM then runs
+    alone.  Must equal: clip kernel (bf16, planar) -> module forward (im2col + GEMM) bit for bit."""
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.patch_embed import TimesformerPatchEmbeddings, VivitTubeletEmbeddings
+    from lvc_b200.synth import synth_video
+    from oracle import samplers as osm
+
+    T = 8
+    host = [synth_video(70 + i, 12, 180, 320) for i in range(3)]
+    dev = [torch.from_numpy(v).cuda() for v in host]
+    idx = [osm.dataset_indices("uniform", 12, T) for _ in host]
+    if kind == "vivit":
+        m, patch, lay = _vivit(224, T), (2, 16, 16), "BTCHW"
+    elif kind == "timesformer":
+        m, patch, lay = TimesformerPatchEmbeddings().cuda(), (1, 16, 16), "BTCHW"
+    else:
+        m, patch, lay = _swin(128), (2, 4, 4), "BCTHW"
+    planar = ClipBuilder(preset, num_frames=T, layout=lay, dtype=torch.bfloat16)(dev, idx)
+    want = m(planar)
+    want = want[0] if isinstance(want, tuple) else want
+    tokens = ClipBuilder(preset, num_frames=T, layout="TOKENS", patch=patch)(dev, idx)
+    assert tokens.dtype == torch.bfloat16 and tokens.shape[1] == 3 * patch[0] * patch[1] * patch[2]
+    launches = m.launches
+    got = m.forward_tokens(tokens, len(host), T)
+    assert m.launches - launches == 1
+    assert torch.equal(got.reshape(want.shape), want)

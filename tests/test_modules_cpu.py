@@ -51,7 +51,7 @@ def test_no_cpu_fallback():
         ClipBuilder("resnet_infer")
     with pytest.raises(RuntimeError):
         pe.VivitTubeletEmbeddings()(torch.zeros(1, 32, 3, 224, 224))
-    d = _lib.ClipDesc(0, 0, 0, 224, 1, 1, 8, 0, (C.c_float * 3)(), (C.c_float * 3)())
+    d = _lib.ClipDesc(0, 0, 0, 224, 1, 1, 8, 0, 0, 0, (C.c_float * 3)(), (C.c_float * 3)())
     rc = _lib.lib().lvc_clip_forward(C.byref(d), 1, 1, None, 1, 1, None, None)
     assert rc == _lib.E_CUDA
     with pytest.raises(RuntimeError):
@@ -60,7 +60,7 @@ def test_no_cpu_fallback():
 
 def test_argument_validation_without_gpu():
     lib = _lib.lib()
-    d = _lib.ClipDesc(0, 0, 0, 200, 1, 1, 8, 0, (C.c_float * 3)(), (C.c_float * 3)())
+    d = _lib.ClipDesc(0, 0, 0, 200, 1, 1, 8, 0, 0, 0, (C.c_float * 3)(), (C.c_float * 3)())
     assert lib.lvc_clip_forward(C.byref(d), 1, 1, None, 1, 1, None, None) == _lib.E_SHAPE
     assert lib.lvc_clip_forward(None, 1, 1, None, 1, 1, None, None) == _lib.E_INVAL
     e = _lib.EmbedDesc(_lib.EMBED_VIVIT, 0, 0, 1, 8, 32, 224, 224, 2, 16, 16, 768, 0.0, 0)
