@@ -192,18 +192,32 @@ namespace {
 // stride, for every layout; the per-thread column term comes from col_offset().  LVC_LAYOUT_TOKENS
 // writes the patch-embedding operand A[m][k] directly: m = ((b*To + t/kt)*Ho + y/kh)*Wo + x/kw,
 // k = ((c*kt + t%kt)*kh + y%kh)*kw + x%kw (token order of the reference modules).
-__device__ __forceinline__ size_t row_offset(const ClipParams& p, int f, int b, int t, int y, size_t& cstride) {
+struct FrameOut {   // per-frame part of the output addressing, computed once per stage
+  size_t base;      // element offset of (channel 0, row 0, column 0) -- tokens: of patch row 0
+  size_t cstride;   // channel stride in elements
+  unsigned rowmul;  // planar layouts: elements per output row; tokens: Wo*K (per patch row)
+};
+__device__ __forceinline__ FrameOut frame_out(const ClipParams& p, int f, int b, int t) {
   const size_t plane = (size_t)S * S;
+  FrameOut o;
   switch (p.layout) {
-    case LVC_LAYOUT_BTCHW: cstride = plane; return (size_t)f * 3 * plane + (size_t)y * S;
-    case LVC_LAYOUT_BCTHW: cstride = (size_t)p.T * plane; return ((size_t)b * 3 * p.T + t) * plane + (size_t)y * S;
-    case LVC_LAYOUT_BTHWC: cstride = 1; return (size_t)f * plane * 3 + (size_t)y * S * 3;
+    case LVC_LAYOUT_BTCHW: o.cstride = plane; o.base = (size_t)f * 3 * plane; o.rowmul = S; break;
+    case LVC_LAYOUT_BCTHW: o.cstride = (size_t)p.T * plane; o.base = ((size_t)b * 3 * p.T + t) * plane; o.rowmul = S; break;
+    case LVC_LAYOUT_BTHWC: o.cstride = 1; o.base = (size_t)f * plane * 3; o.rowmul = S * 3; break;
     default: {
-      const int To = p.T / p.kt, Ho = S / p.kh, Wo = S / p.kw, K = 3 * p.kt * p.kh * p.kw;
-      cstride = (size_t)p.kt * p.kh * p.kw;
-      return (((size_t)b * To + t / p.kt) * Ho + y / p.kh) * Wo * K + (size_t)((t % p.kt) * p.kh + y % p.kh) * p.kw;
+      const unsigned To = p.T / p.kt, Ho = S / p.kh, Wo = S / p.kw, K = 3 * p.kt * p.kh * p.kw;
+      const unsigned to = (unsigned)t / (unsigned)p.kt, dt = (unsigned)t - to * p.kt;
+      o.cstride = (size_t)p.kt * p.kh * p.kw;
+      o.rowmul = Wo * K;
+      o.base = ((size_t)b * To + to) * Ho * o.rowmul + (size_t)dt * p.kh * p.kw;
     }
   }
+  return o;
+}
+__device__ __forceinline__ size_t row_offset(const ClipParams& p, const FrameOut& o, int y) {
+  if (p.layout != LVC_LAYOUT_TOKENS) return o.base + (size_t)y * o.rowmul;
+  const unsigned ho = (unsigned)y / (unsigned)p.kh, dy = (unsigned)y - ho * p.kh;
+  return o.base + (size_t)ho * o.rowmul + dy * p.kw;
 }
 __device__ __forceinline__ size_t col_offset(const ClipParams& p, int x) {
   if (p.layout == LVC_LAYOUT_BTHWC) return (size_t)x * 3;
@@ -403,13 +417,14 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
         acc = 0; acc_b = b;
       }
+      const FrameOut fo = frame_out(p, f, b, t);
       for (int r = g; r < p.rps; r += kGroups) {
         const RowDesc rd = h->rows[r];
         const uint8_t* p0 = ring + rd.off0 + xo;
         const uint8_t* p1 = ring + rd.off1 + xo;
         const int oyr = oy0 + r;
-        size_t cstride;
-        const size_t eoff = row_offset(p, f, b, t, oyr, cstride) + xoff;  // element offset of channel 0
+        const size_t cstride = fo.cstride;
+        const size_t eoff = row_offset(p, fo, oyr) + xoff;  // element offset of channel 0
         if (MODE == MODE_PTV) {
           // torch CPU blend order: r = fma(p_x0, lx0, p_x1*lx1) per row, out = fma(r_y0, ly0, r_y1*ly1)
           const float ly0 = __int_as_float(rd.b0), ly1 = __int_as_float(rd.b1);
@@ -427,15 +442,26 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           continue;
         }
         int v[3];
+        {
+          // 6 source bytes (2 pixels x RGB) per row come from three aligned 32-bit shared loads and a
+          // funnel shift instead of six byte loads (halves the bank-conflicted wavefronts); the
+          // horizontal pass a0*p0 + a1*p1 is one PRMT + one DP2A per channel.  At a clamped right
+          // edge a1 == 0, so the bytes read at +3 (still inside the slot's slack) do not matter.
+          const uint32_t o0 = (uint32_t)(rd.off0 + xo), o1 = (uint32_t)(rd.off1 + xo);
+          const uint32_t* w0 = reinterpret_cast<const uint32_t*>(ring + (o0 & ~3u));
+          const uint32_t* w1 = reinterpret_cast<const uint32_t*>(ring + (o1 & ~3u));
+          const uint32_t a = w0[0], bq = w0[1], cq = w0[2], d = w1[0], e = w1[1], fq = w1[2];
+          const uint32_t sh0 = (o0 & 3u) * 8u, sh1 = (o1 & 3u) * 8u;
+          const uint32_t lo0 = __funnelshift_r(a, bq, sh0), hi0 = __funnelshift_r(bq, cq, sh0);
+          const uint32_t lo1 = __funnelshift_r(d, e, sh1), hi1 = __funnelshift_r(e, fq, sh1);
+          const uint32_t a01 = (uint32_t)a0 | ((uint32_t)a1 << 16);
+          const uint32_t sel[3] = {0x4430u, 0x4441u, 0x4452u};  // (R0,R1), (G0,G1), (B0,B1) of the 8 bytes
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const int p00 = p0[c], p01 = p0[c + d1], p10 = p1[c], p11 = p1[c + d1];
-          if (flags & 1) {
-            v[c] = (p00 + p01 + p10 + p11 + 2) >> 2;
-          } else {
-            const int s0 = a0 * p00 + a1 * p01;
-            const int s1 = a0 * p10 + a1 * p11;
-            v[c] = (((rd.b0 * (s0 >> 4)) >> 16) + ((rd.b1 * (s1 >> 4)) >> 16) + 2) >> 2;
+          for (int c = 0; c < 3; ++c) {
+            const int s0 = (int)__dp2a_lo(a01, __byte_perm(lo0, hi0, sel[c]), 0u);
+            const int s1 = (int)__dp2a_lo(a01, __byte_perm(lo1, hi1, sel[c]), 0u);
+            v[c] = (flags & 1) ? ((s0 + s1 + 2) >> 2)
+                               : ((((rd.b0 * (s0 >> 4)) >> 16) + ((rd.b1 * (s1 >> 4)) >> 16) + 2) >> 2);
           }
         }
         acc += (unsigned)(v[0] + v[1] + v[2]);
@@ -477,9 +503,10 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       consumers_bar();
       const int b = f / p.T, t = f - b * p.T;
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
+      const FrameOut fo = frame_out(p, f, b, t);
       for (int y = g; y < S; y += kGroups) {
-        size_t cstride;
-        const size_t eoff = row_offset(p, f, b, t, y, cstride) + xoff;
+        const size_t cstride = fo.cstride;
+        const size_t eoff = row_offset(p, fo, y) + xoff;
         const int4 ty = vt[y];
         const uint8_t* tp = inter + ty.x * kRowBytes + x * 3;
         int v[3];

@@ -307,10 +307,16 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host->device leg (profiling runs only)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the configs[1..3] clip+embed pipelines")
+    ap.add_argument("--secondary-only", action="store_true", help="run only the configs[1..3] pipelines (profiling)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         return run_reference(args, wl)
+    if args.secondary_only:
+        import torch
+
+        print(json.dumps({"secondary": run_secondary(torch.device("cuda", 0), iters=3)}), flush=True)
+        return
 
     r = run_b200(args, wl)
     import torch
