@@ -60,6 +60,7 @@ struct ClipParams {
   int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
   float mean[3], std[3];     // PTV normalisation
   int kt, kh, kw;            // LVC_LAYOUT_TOKENS: patch size; output is the GEMM operand A[M][K] (bf16)
+  int kh_shift;              // log2(kh) when kh is a power of two, else -1
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------
@@ -216,7 +217,8 @@ __device__ __forceinline__ FrameOut frame_out(const ClipParams& p, int f, int b,
 }
 __device__ __forceinline__ size_t row_offset(const ClipParams& p, const FrameOut& o, int y) {
   if (p.layout != LVC_LAYOUT_TOKENS) return o.base + (size_t)y * o.rowmul;
-  const unsigned ho = (unsigned)y / (unsigned)p.kh, dy = (unsigned)y - ho * p.kh;
+  const unsigned ho = p.kh_shift >= 0 ? ((unsigned)y >> p.kh_shift) : ((unsigned)y / (unsigned)p.kh);
+  const unsigned dy = (unsigned)y - ho * p.kh;
   return o.base + (size_t)ho * o.rowmul + dy * p.kw;
 }
 __device__ __forceinline__ size_t col_offset(const ClipParams& p, int x) {
@@ -364,7 +366,8 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   const int ct = tid - 32;
   const int g = ct / S;
   const int x = ct - g * S;
-  int cached_sw = -1, cached_flags = -1, cached_ox = -1;
+  int cached_sw = -1, cached_flags = -1, cached_ox = -1, cached_f = -1, cur_b = 0, cur_t = 0;
+  FrameOut fo = {0, 0, 0};
   int xo = 0, d1 = 0, a0 = 0, a1 = 0;
   float lx0 = 0.f, lx1 = 0.f;
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
@@ -408,7 +411,13 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           d1 = (sx + 1 <= sw - 1) ? 3 : 0;
         }
       }
-      const int b = f / p.T, t = f - b * p.T;
+      if (f != cached_f) {
+        cached_f = f;
+        cur_b = f / p.T;
+        cur_t = f - cur_b * p.T;
+        fo = frame_out(p, f, cur_b, cur_t);
+      }
+      const int b = cur_b;
       if (MODE != MODE_PTV && p.stats && b != acc_b) {
         if (acc_b >= 0) {
 #pragma unroll
@@ -417,7 +426,6 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
         acc = 0; acc_b = b;
       }
-      const FrameOut fo = frame_out(p, f, b, t);
       for (int r = g; r < p.rps; r += kGroups) {
         const RowDesc rd = h->rows[r];
         const uint8_t* p0 = ring + rd.off0 + xo;
@@ -501,9 +509,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
     if (MODE == MODE_VIVIT) {
       // the whole frame went through the horizontal pass: Pillow vertical pass + LUT + store
       consumers_bar();
-      const int b = f / p.T, t = f - b * p.T;
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
-      const FrameOut fo = frame_out(p, f, b, t);
       for (int y = g; y < S; y += kGroups) {
         const size_t cstride = fo.cstride;
         const size_t eoff = row_offset(p, fo, y) + xoff;
@@ -620,9 +626,17 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
   for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
   p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
+  p.kh_shift = -1;
+  for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
   // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
-  p.rps = env_int("LVC_CLIP_RPS", 4);
+  // 8 output rows per stage amortise the per-stage bookkeeping when the row slots are small enough
+  // to keep >= 3 stages in flight; wide sources (1080p) use 4 rows per stage and a deeper ring
+  p.rps = env_int("LVC_CLIP_RPS", 0);
+  if (p.rps == 0) {
+    const int budget0 = std::min(di.max_smem, 200 * 1024) - ring_off(mode);
+    p.rps = (budget0 / (16 * p.pitch) >= 3) ? 8 : 4;
+  }
   if (p.rps < kGroups || p.rps > kMaxRPS || (p.rps % kGroups) || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
   const int fixed = ring_off(mode);
   const int smem_budget = std::min(di.max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, fixed + 64 * 1024));
