@@ -211,6 +211,41 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+
+// Asynchronous variant: the 32 destination registers are valid only after tmem_wait_dep(v), whose
+// "+r" operands give the compiler a true dependency (nothing that reads v can move above the wait).
+__device__ __forceinline__ void tmem_ld32_async(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_wait_dep(float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                 "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :: "memory");
+}
+// 2-D tiled TMA store (SASS: UTMASTG) of a swizzled shared-memory tile; rows/columns beyond the
+// tensor's extents are clipped by the hardware.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(s32(src)), "r"(c0), "r"(c1) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 // Shared-memory matrix descriptor for a K-major bf16 tile whose rows are one swizzle span wide
 // (BK*2 = 128 B -> SWIZZLE_128B, 64 B -> SWIZZLE_64B): 8-row groups are `span*8` bytes apart (SBO);
 // LBO is unused for swizzled K-major operands; bits 46-47 = descriptor version 1 (sm_100).
@@ -243,6 +278,7 @@ struct GemmParams {
   const float* ln_b;
   float ln_eps;
   int do_ln, out_f32;
+  int diag;            // LVC_GEMM_DIAG (profiling only): 1 = no output stores, 2 = no MMAs, 4 = no TMA loads
   void* out;
 };
 
@@ -489,24 +525,26 @@ __device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
                ::"r"(s32(bar)), "h"((uint16_t)3) : "memory");
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+constexpr int kGemm2Threads = 320;  // producer warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemm2Threads, 1)
 lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                       const __grid_constant__ GemmParams p) {
+                       const __grid_constant__ CUtensorMap map_o, const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
+  if (p.diag & 8) return;
   uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);  // 1024-aligned, stays in the shared window
   const int span = p.BK * 2;
   const int half_n = p.BN / 2;
   const uint32_t a_bytes = BM * span, b_bytes = half_n * span;
-  uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + (size_t)p.stages * a_bytes;
+  // staging tiles of the TMA stores first (128B-swizzled boxes need 1024-byte alignment): 8 warps x 4 KB
+  uint8_t* stg = smem + (size_t)((threadIdx.x >> 5) - 2 & 7) * 4096;
+  uint8_t* smem_a = smem + 8 * 4096;
+  uint8_t* smem_b = smem_a + (size_t)p.stages * a_bytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_b + (size_t)p.stages * b_bytes);
   uint64_t* empty = full + p.stages;
   uint64_t* tmem_full = empty + p.stages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);
-  for (int i = threadIdx.x; i < p.N; i += kGemmThreads) s_bias[i] = p.bias[i];
-  uint8_t* stg = reinterpret_cast<uint8_t*>(s_bias + p.N) + (size_t)(threadIdx.x >> 5 & 3) * 4096;  // per epilogue warp
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_rank();
@@ -518,7 +556,8 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 8); }
+    tma_prefetch_desc(&map_o);
+    for (int a = 0; a < 2; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 16); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc_2sm(tmem_slot, p.tmem_cols);
@@ -539,6 +578,7 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
           const int s = it % p.stages;
           mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
+          if (p.diag & 4) { if (leader) mb_arrive(&full[s]); continue; }
           if (leader) mb_expect_tx(&full[s], 2u * (a_bytes + b_bytes));
           const uint32_t bar = mapa(s32(&full[s]), 0);
           tma_load_2d_2sm(smem_a + (size_t)s * a_bytes, &map_a, kb * p.BK, row_a, bar);
@@ -562,7 +602,7 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
           tc_fence_after();
           const uint64_t adesc = make_smem_desc(s32(smem_a + (size_t)s * a_bytes), span);
           const uint64_t bdesc = make_smem_desc(s32(smem_b + (size_t)s * b_bytes), span);
-          for (int k = 0; k < p.BK / 16; ++k)
+          for (int k = 0; k < p.BK / 16 && !(p.diag & 2); ++k)
             umma_bf16_2sm(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
           umma_commit_2sm(&empty[s]);
         }
@@ -570,35 +610,74 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
       }
     }
   } else {
-    // ===================== epilogue (both CTAs, own 128 rows) =====================
-    const int q = warp & 3;
+    // ===================== epilogue (both CTAs, own 128 rows; 8 warps) =====================
+    // warp%4 selects the TMEM lane quarter (hardware rule), (warp-2)/4 the column half of the tile.
+    // Per 128-byte fill: two TMEM loads are in flight while the previous fill is packed, written to
+    // the warp's swizzled staging tile and handed to the TMA store engine.
+    const int q = warp & 3, half = (warp - 2) >> 2;
     const uint32_t leader_tmem_empty0 = mapa(s32(&tmem_empty[0]), 0);
+    const int cpf = p.out_f32 ? 32 : 64;      // columns per fill (128 bytes of output)
+    const int nfill = half_n / cpf;
     uint32_t local = 0;
     for (int u = pair; u < num_units; u += num_pairs, ++local) {
       const int m_pair = u / p.n_tiles, n_blk = u - m_pair * p.n_tiles;
       const uint32_t acc = local & 1u, acc_phase = (local >> 1) & 1u;
       mb_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)p.BN;
-      const long long m_warp0 = (long long)m_pair * 2 * BM + (long long)rank * BM + q * 32;
-      const float* sb = s_bias + n_blk * p.BN;
-      const int NCH = p.BN / 32;
-      float v[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)p.BN + (uint32_t)(half * half_n);
+      const int m_warp0 = m_pair * 2 * BM + (int)rank * BM + q * 32;
+      const int n_base = n_blk * p.BN + half * half_n;
+      float va[32], vb[32];
       uint32_t pk[32];
-      for (int ch = 0; ch < NCH; ++ch) {
-        tmem_ld32(taddr + ch * 32, v);
-        const int n0 = n_blk * p.BN + ch * 32;
+      if (p.diag & 16) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mb_arrive_cluster(leader_tmem_empty0 + acc * 8u);
+        continue;
+      }
+      tmem_ld32_async(taddr, va);
+      if (!p.out_f32) tmem_ld32_async(taddr + 32, vb);
+      for (int f = 0; f < nfill; ++f) {
+        const int n0 = n_base + f * cpf;
+        tmem_wait_dep(va);
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 b4 = reinterpret_cast<const float4*>(sb + ch * 32)[j4];
-          v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0) + j4);
+          va[4 * j4] += b4.x; va[4 * j4 + 1] += b4.y; va[4 * j4 + 2] += b4.z; va[4 * j4 + 3] += b4.w;
         }
-        emit_chunk(v, pk, p, stg, lane, m_warp0, n0, ch, NCH);
+        if (p.out_f32) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) pk[j] = __float_as_uint(va[j]);
+        } else {
+          tmem_wait_dep(vb);
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 32) + j4);
+            vb[4 * j4] += b4.x; vb[4 * j4 + 1] += b4.y; vb[4 * j4 + 2] += b4.z; vb[4 * j4 + 3] += b4.w;
+          }
+          pack_bf16<0>(va, pk);
+          pack_bf16<1>(vb, pk);
+        }
+        if (f + 1 < nfill) {   // next fill's accumulator columns travel while this one is stored
+          tmem_ld32_async(taddr + (uint32_t)((f + 1) * cpf), va);
+          if (!p.out_f32) tmem_ld32_async(taddr + (uint32_t)((f + 1) * cpf + 32), vb);
+        } else {               // accumulator fully read: hand the TMEM buffer back to the MMA issuer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mb_arrive_cluster(leader_tmem_empty0 + acc * 8u);
+        }
+        if (lane == 0) tma_store_wait_read();   // the previous store has finished reading the tile
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+              make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0 && !(p.diag & 1)) tma_store_2d(&map_o, stg, n0, m_warp0);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mb_arrive_cluster(leader_tmem_empty0 + acc * 8u);  // the MMA issuer lives in the leader
     }
+    if (lane == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -606,6 +685,188 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------- short-K GEMM + LayerNorm (Video Swin) ----
+// PatchEmbed3d is HBM-bound (K = 96, N = 128: 55 FLOP/B), so this kernel is organised around the
+// byte streams, not the MMAs: the whole weight matrix B[N][K] is loaded ONCE per CTA and stays in
+// shared memory; A tiles (128 tokens x K) stream through a TMA ring, one mbarrier per tile; two
+// epilogue warpgroups own one TMEM accumulator each and alternate tiles.  A thread holds its token's
+// full row (N fp32 values) in registers: bias, two-pass LayerNorm statistics and the affine are done
+// without re-reading TMEM, and rows leave through 128-byte-swizzled staging tiles and TMA stores.
+namespace {
+
+constexpr int kSwinThreads = 320;
+
+template <int NCH, bool OUT_F32>  // N = 32 * NCH columns
+__global__ void __launch_bounds__(kSwinThreads, 1)
+lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                      const __grid_constant__ CUtensorMap map_o, const __grid_constant__ GemmParams p) {
+  constexpr int N = 32 * NCH;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
+  const int span = p.BK * 2;
+  const uint32_t a_sub = BM * span, b_sub = N * span;          // one k-block of A / of B
+  const uint32_t a_bytes = a_sub * p.num_k_blocks, b_bytes = b_sub * p.num_k_blocks;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* stg = smem + (size_t)((warp - 2) & 7) * 8192;       // 2 x 4 KB store tiles per epilogue warp
+  uint8_t* smem_b = smem + 8 * 8192;
+  uint8_t* smem_a = smem_b + b_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_a + (size_t)p.stages * a_bytes);
+  uint64_t* empty = full + p.stages;
+  uint64_t* tmem_full = empty + p.stages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint64_t* b_full = tmem_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
+  // parameters after the barriers, 16-byte aligned for float4 reads (barrier block is < 512 bytes)
+  float* s_bias = reinterpret_cast<float*>(smem_a + (size_t)p.stages * a_bytes + 512);
+  float* s_lnw = s_bias + N;
+  float* s_lnb = s_lnw + N;
+  for (int i = threadIdx.x; i < N; i += kSwinThreads) {
+    s_bias[i] = p.bias[i];
+    s_lnw[i] = p.do_ln ? p.ln_w[i] : 1.f;
+    s_lnb[i] = p.do_ln ? p.ln_b[i] : 0.f;
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_o);
+    for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
+    mb_init(b_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_tiles = p.m_tiles;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      mb_expect_tx(b_full, b_bytes);
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) tma_load_2d(smem_b + (size_t)kb * b_sub, &map_b, kb * p.BK, 0, b_full);
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int s = it % p.stages;
+        mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
+        if (p.diag & 4) { mb_arrive(&full[s]); continue; }
+        mb_expect_tx(&full[s], a_bytes);
+        for (int kb = 0; kb < p.num_k_blocks; ++kb)
+          tma_load_2d(smem_a + (size_t)s * a_bytes + (size_t)kb * a_sub, &map_a, kb * p.BK, tile * BM, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc(BM, N);
+      mb_wait(b_full, 0);
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const uint32_t acc = it & 1u, acc_phase = (it >> 1) & 1u;
+        const int s = it % p.stages;
+        mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
+        mb_wait(&full[s], (it / p.stages) & 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * (uint32_t)N;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          const uint64_t adesc = make_smem_desc(s32(smem_a + (size_t)s * a_bytes + (size_t)kb * a_sub), span);
+          const uint64_t bdesc = make_smem_desc(s32(smem_b + (size_t)kb * b_sub), span);
+          for (int k = 0; k < p.BK / 16 && !(p.diag & 2); ++k)
+            umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+        }
+        umma_commit(&empty[s]);
+        umma_commit(&tmem_full[acc]);
+      }
+    }
+  } else {
+    // ===================== epilogue: warpgroup g = (warp-2)/4 owns accumulator g =====================
+    const int q = warp & 3, grp = (warp - 2) >> 2;
+    const float inv_n = 1.f / (float)N;
+    uint32_t it = 0, fill = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      if ((int)(it & 1u) != grp) continue;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      mb_wait(&tmem_full[grp], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * N);
+      float v[NCH][32];
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) tmem_ld32_async(taddr + c * 32, v[c]);
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) tmem_wait_dep(v[c]);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mb_arrive(&tmem_empty[grp]);   // the row lives in registers now
+      if (p.diag & 16) continue;
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};   // four independent chains (a dependent FADD/FFMA issues every 4 cycles)
+#pragma unroll
+      for (int c = 0; c < NCH; ++c)
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 b4 = reinterpret_cast<const float4*>(s_bias + c * 32)[j4];
+          v[c][4 * j4] += b4.x; v[c][4 * j4 + 1] += b4.y; v[c][4 * j4 + 2] += b4.z; v[c][4 * j4 + 3] += b4.w;
+          s4[j4 & 3] += (v[c][4 * j4] + v[c][4 * j4 + 1]) + (v[c][4 * j4 + 2] + v[c][4 * j4 + 3]);
+        }
+      float mean = 0.f, rstd = 1.f;
+      if (p.do_ln && !(p.diag & 32)) {
+        mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) * inv_n;
+        float q4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < NCH; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { v[c][j] -= mean; q4[j & 3] = fmaf(v[c][j], v[c][j], q4[j & 3]); }
+        rstd = rsqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) * inv_n + p.ln_eps);
+      }
+      const int m0 = tile * BM + q * 32;
+      constexpr int CPF = OUT_F32 ? 1 : 2;  // 32-column chunks per 128-byte fill
+#pragma unroll
+      for (int c0 = 0; c0 < NCH; c0 += CPF) {
+        uint32_t pk[32];
+#pragma unroll
+        for (int cc = 0; cc < CPF; ++cc) {
+          const int c = c0 + cc;
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 g4 = reinterpret_cast<const float4*>(s_lnw + c * 32)[j4];
+            const float4 o4 = reinterpret_cast<const float4*>(s_lnb + c * 32)[j4];
+            const float y0 = fmaf(v[c][4 * j4], rstd * g4.x, o4.x), y1 = fmaf(v[c][4 * j4 + 1], rstd * g4.y, o4.y);
+            const float y2 = fmaf(v[c][4 * j4 + 2], rstd * g4.z, o4.z), y3 = fmaf(v[c][4 * j4 + 3], rstd * g4.w, o4.w);
+            if (OUT_F32) {
+              pk[4 * j4] = __float_as_uint(y0); pk[4 * j4 + 1] = __float_as_uint(y1);
+              pk[4 * j4 + 2] = __float_as_uint(y2); pk[4 * j4 + 3] = __float_as_uint(y3);
+            } else {
+              __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
+              pk[cc * 16 + 2 * j4] = *reinterpret_cast<uint32_t*>(&lo);
+              pk[cc * 16 + 2 * j4 + 1] = *reinterpret_cast<uint32_t*>(&hi);
+            }
+          }
+        }
+        uint8_t* tile_s = stg + (fill & 1u) * 4096;
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // slot's previous store was read
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(tile_s + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+              make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        if (!(p.diag & 64)) fence_async_smem();
+        __syncwarp();
+        if (lane == 0 && !(p.diag & 1)) tma_store_2d(&map_o, tile_s, c0 * 32, m0);
+        ++fill;
+      }
+    }
+    if (lane == 0) tma_store_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
@@ -642,6 +903,22 @@ int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t K, uint
                   CU_TENSOR_MAP_INTERLEAVE_NONE, BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return lvc_fail(LVC_E_CUDA, "patch_embed: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return LVC_OK;
+}
+
+// out[M][N] (bf16 or fp32) row-major, box = 128 bytes x 32 rows, SWIZZLE_128B: the epilogue's store tile
+int make_out_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t N, bool f32) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return lvc_fail(LVC_E_CUDA, "patch_embed: cuTensorMapEncodeTiled is not available from the driver");
+  const uint64_t esz = f32 ? 4 : 2;
+  cuuint64_t dims[2] = {N, rows};
+  cuuint64_t strides[1] = {N * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esz), 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return lvc_fail(LVC_E_CUDA, "patch_embed: cuTensorMapEncodeTiled(out) failed with CUresult %d", (int)r);
   return LVC_OK;
 }
 
@@ -736,6 +1013,7 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   p.do_ln = d->kind == LVC_EMBED_SWIN;
   p.out_f32 = d->out_dtype == LVC_DT_F32;
   p.out = out;
+  p.diag = env_i("LVC_GEMM_DIAG", 0);
   const int stage_bytes = (BM + p.BN) * p.BK * 2;
   const int fixed_bytes = 1024 + 2048 + (g.N + 2 * p.BN) * 4 + 16384;  // alignment, barriers, params, store staging
   // two CTAs per SM when TMEM (2 x <=256 columns) and shared memory allow: doubles the epilogue warps,
@@ -752,22 +1030,52 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   const size_t smem = (size_t)fixed_bytes + (size_t)p.stages * stage_bytes;
 
   // tensor-bound shapes (no LayerNorm, 128B-swizzle K blocks, even tile split): CTA-pair kernel
-  const bool two_cta = !p.do_ln && p.BK == 64 && p.BN % 64 == 0 && p.BN >= 64 && !getenv("LVC_GEMM_1CTA") && sms >= 2;
+  const bool two_cta = !p.do_ln && p.BK == 64 && p.BN % 128 == 0 && !getenv("LVC_GEMM_1CTA") && sms >= 2;
   if (two_cta) {
     const int stage2 = (BM + p.BN / 2) * p.BK * 2;
+    const int fixed2 = 1024 + 8 * 4096 + 512;  // alignment slack, 8 store tiles, barriers + TMEM slot
     p.m_tiles = (g.M + 2 * BM - 1) / (2 * BM);
-    p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (max_smem - 2048 - g.N * 4 - 16384) / stage2, std::max(2, p.num_k_blocks * 2)});
-    const size_t smem2 = 1024 + (size_t)p.stages * stage2 + (2 * p.stages + 4) * 8 + 16 + (size_t)g.N * 4 + 16 + 16384;
-    CUtensorMap ma, mb;
+    p.stages = std::min({env_i("LVC_GEMM_STAGES", 8), (max_smem - fixed2) / stage2, std::max(2, p.num_k_blocks * 2)});
+    if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "patch_embed: tile does not fit shared memory");
+    const size_t smem2 = (size_t)fixed2 + (size_t)p.stages * stage2;
+    CUtensorMap ma, mb, mo;
     rc = make_map(&ma, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
     if (rc != LVC_OK) return rc;
     rc = make_map(&mb, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)(p.BN / 2));
     if (rc != LVC_OK) return rc;
+    rc = make_out_map(&mo, out, (uint64_t)g.M, (uint64_t)g.N, p.out_f32 != 0);
+    if (rc != LVC_OK) return rc;
     LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     const int pairs = std::min(sms / 2, p.m_tiles * p.n_tiles);
-    lvc_embed_gemm2_kernel<<<2 * pairs, kGemmThreads, smem2, st>>>(ma, mb, p);
+    lvc_embed_gemm2_kernel<<<2 * pairs, kGemm2Threads, smem2, st>>>(ma, mb, mo, p);
     LVC_CUDA_TRY(cudaGetLastError());
     return LVC_OK;
+  }
+  // short-K shapes with N = 128 (Video Swin-B): weights resident in shared memory, row-in-registers LayerNorm
+  if (g.N == 128 && g.K <= 256 && !getenv("LVC_GEMM_GENERIC")) {
+    const int a_tile = BM * g.K * 2, b_all = g.N * g.K * 2;
+    const int fixed3 = 1024 + 8 * 8192 + b_all + 512 + 3 * g.N * 4 + 64;
+    p.stages = std::min(env_i("LVC_GEMM_STAGES", 8), (max_smem - fixed3) / a_tile);
+    if (p.stages >= 2) {
+      const size_t smem3 = (size_t)fixed3 + (size_t)p.stages * a_tile;
+      CUtensorMap ma, mb, mo;
+      rc = make_map(&ma, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
+      if (rc != LVC_OK) return rc;
+      rc = make_map(&mb, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)g.N);
+      if (rc != LVC_OK) return rc;
+      rc = make_out_map(&mo, out, (uint64_t)g.M, (uint64_t)g.N, p.out_f32 != 0);
+      if (rc != LVC_OK) return rc;
+      const int grid3 = std::min(sms, p.m_tiles);
+      if (p.out_f32) {
+        LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+        lvc_embed_swin_kernel<4, true><<<grid3, kSwinThreads, smem3, st>>>(ma, mb, mo, p);
+      } else {
+        LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+        lvc_embed_swin_kernel<4, false><<<grid3, kSwinThreads, smem3, st>>>(ma, mb, mo, p);
+      }
+      LVC_CUDA_TRY(cudaGetLastError());
+      return LVC_OK;
+    }
   }
   CUtensorMap map_a, map_b;
   rc = make_map(&map_a, workspace, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);

@@ -283,6 +283,9 @@ def run_secondary(dev, iters=10):
             for _ in range(3 + iters):
                 if flush_l2:
                     flush.zero_()
+                # keep the device busy ~0.2 ms so the host-side call (Python + ctypes) is fully enqueued
+                # before e0 fires: the interval then holds device time only, no launch gap
+                torch.cuda._sleep(400000)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 fn()

@@ -30,6 +30,7 @@ def run(name, iters=20):
     ts = []
     for _ in range(iters):
         flush.zero_()  # > L2
+        torch.cuda._sleep(400000)  # host call fully enqueued before e0 fires
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         m(x)
