@@ -163,6 +163,17 @@ __device__ __forceinline__ void mb_wait(uint64_t* b, uint32_t parity) {
                  : "=r"(done) : "r"(s32(b)), "r"(parity) : "memory");
   } while (!done);
 }
+// wait with back-off: for warps that idle for long stretches next to busy warps of the same SM
+// sub-partition (a bare try_wait spin competes with them for issue slots)
+__device__ __forceinline__ void mb_wait_backoff(uint64_t* b, uint32_t parity) {
+  uint32_t done;
+  for (;;) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(s32(b)), "r"(parity), "r"(2000u) : "memory");
+    if (done) break;
+    __nanosleep(100);
+  }
+}
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
@@ -246,6 +257,25 @@ __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.b
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Packed fp32x2 arithmetic (SASS FFMA2 / FADD2): two lanes per instruction, halves the issue slots of
+// the LayerNorm epilogue.
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
 // Shared-memory matrix descriptor for a K-major bf16 tile whose rows are one swizzle span wide
 // (BK*2 = 128 B -> SWIZZLE_128B, 64 B -> SWIZZLE_64B): 8-row groups are `span*8` bytes apart (SBO);
 // LBO is unused for swizzled K-major operands; bits 46-47 = descriptor version 1 (sm_100).
@@ -278,6 +308,7 @@ struct GemmParams {
   const float* ln_b;
   float ln_eps;
   int do_ln, out_f32;
+  const void* diag_a;  // A base pointer for the linear-copy experiment
   int diag;            // LVC_GEMM_DIAG (profiling only): 1 = no output stores, 2 = no MMAs, 4 = no TMA loads
   void* out;
 };
@@ -699,43 +730,62 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
 // without re-reading TMEM, and rows leave through 128-byte-swizzled staging tiles and TMA stores.
 namespace {
 
-constexpr int kSwinThreads = 320;
+constexpr int kSwinGroups = 4;                           // epilogue warpgroups = TMEM accumulators
+constexpr int kSwinThreads = 64 + kSwinGroups * 128;     // producer warp, MMA warp, 16 epilogue warps
 
-template <int NCH, bool OUT_F32>  // N = 32 * NCH columns
+template <int NCH, bool OUT_F32>  // N = 32 * NCH columns, kSwinGroups * N <= 512 TMEM columns
 __global__ void __launch_bounds__(kSwinThreads, 1)
 lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                       const __grid_constant__ CUtensorMap map_o, const __grid_constant__ GemmParams p) {
   constexpr int N = 32 * NCH;
+  constexpr int NG = kSwinGroups;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
   const int span = p.BK * 2;
   const uint32_t a_sub = BM * span, b_sub = N * span;          // one k-block of A / of B
   const uint32_t a_bytes = a_sub * p.num_k_blocks, b_bytes = b_sub * p.num_k_blocks;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint8_t* stg = smem + (size_t)((warp - 2) & 7) * 8192;       // 2 x 4 KB store tiles per epilogue warp
-  uint8_t* smem_b = smem + 8 * 8192;
-  uint8_t* smem_a = smem_b + b_bytes;
+  uint8_t* stg = smem + (size_t)((warp - 2) & (4 * NG - 1)) * 4096;   // one 4 KB store tile per epilogue warp
+  uint8_t* smem_b = smem + 4 * NG * 4096;
+  // bias rides in the MMA as one extra K=16 step: D += ONES[128 x 16] . BIASPARTS[N x 16]^T, where the three
+  // leading K entries of row n hold a bf16 hi/mid/lo split of bias[n] (their fp32 sum is bias[n] to ~2^-24)
+  uint8_t* smem_ones = smem_b + b_bytes;                 // 128 rows x 64 B, every element bf16 1.0
+  uint8_t* smem_bias = smem_ones + BM * 64;              // N rows x 64 B, 64B-swizzled
+  uint8_t* smem_a = smem_bias + N * 64;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_a + (size_t)p.stages * a_bytes);
   uint64_t* empty = full + p.stages;
   uint64_t* tmem_full = empty + p.stages;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint64_t* b_full = tmem_empty + 2;
+  uint64_t* tmem_empty = tmem_full + NG;
+  uint64_t* b_full = tmem_empty + NG;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
   // parameters after the barriers, 16-byte aligned for float4 reads (barrier block is < 512 bytes)
   float* s_bias = reinterpret_cast<float*>(smem_a + (size_t)p.stages * a_bytes + 512);
   float* s_lnw = s_bias + N;
   float* s_lnb = s_lnw + N;
   for (int i = threadIdx.x; i < N; i += kSwinThreads) {
-    s_bias[i] = p.bias[i];
     s_lnw[i] = p.do_ln ? p.ln_w[i] : 1.f;
     s_lnb[i] = p.do_ln ? p.ln_b[i] : 0.f;
+    const float b = p.bias[i];
+    const __nv_bfloat16 hi = __float2bfloat16_rn(b);
+    const float r1 = b - __bfloat162float(hi);
+    const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
+    const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
+    uint4* row = reinterpret_cast<uint4*>(smem_bias + i * 64);
+    const int c0 = (i >> 1) & 3;   // SWIZZLE_64B: 16-byte chunk c of row i lives at chunk c ^ ((i >> 1) & 3)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) row[c] = make_uint4(0u, 0u, 0u, 0u);
+    row[c0] = make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(mid) << 16),
+                         (uint32_t)__bfloat16_as_ushort(lo), 0u, 0u);
   }
+  for (int i = threadIdx.x; i < BM * 64 / 16; i += kSwinThreads)
+    reinterpret_cast<uint4*>(smem_ones)[i] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+  fence_async_smem();   // generic-proxy writes above are read by the tensor core (async proxy)
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
     for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
+    for (int a = 0; a < NG; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
     mb_init(b_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -757,6 +807,12 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
         if (p.diag & 4) { mb_arrive(&full[s]); continue; }
         mb_expect_tx(&full[s], a_bytes);
+        if (p.diag & 128) {  // timing experiment: the tile as ONE linear bulk copy (layout is wrong for the MMA)
+          const uint8_t* src = reinterpret_cast<const uint8_t*>(p.diag_a) + (size_t)tile * a_bytes;
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(s32(smem_a + (size_t)s * a_bytes)), "l"(src), "r"(a_bytes), "r"(s32(&full[s])) : "memory");
+          continue;
+        }
         for (int kb = 0; kb < p.num_k_blocks; ++kb)
           tma_load_2d(smem_a + (size_t)s * a_bytes + (size_t)kb * a_sub, &map_a, kb * p.BK, tile * BM, &full[s]);
       }
@@ -768,7 +824,7 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
       mb_wait(b_full, 0);
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const uint32_t acc = it & 1u, acc_phase = (it >> 1) & 1u;
+        const uint32_t acc = it % NG, acc_phase = (it / NG) & 1u;
         const int s = it % p.stages;
         mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
         mb_wait(&full[s], (it / p.stages) & 1u);
@@ -781,83 +837,98 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
             umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
         }
         umma_commit(&empty[s]);
+        umma_bf16(d_tmem, make_smem_desc(s32(smem_ones), 64), make_smem_desc(s32(smem_bias), 64), idesc, 1u);  // + bias
         umma_commit(&tmem_full[acc]);
       }
     }
   } else {
     // ===================== epilogue: warpgroup g = (warp-2)/4 owns accumulator g =====================
+    // A thread owns one token row.  Pass 1 over TMEM: bias + sum / sum of squares (four independent
+    // chains each); pass 2: normalise, affine, pack, 128-byte fills through the warp's swizzled store
+    // tile.  The next chunk's tcgen05.ld is always in flight while the current one is processed.
     const int q = warp & 3, grp = (warp - 2) >> 2;
     const float inv_n = 1.f / (float)N;
-    uint32_t it = 0, fill = 0;
+    constexpr int CPF = OUT_F32 ? 1 : 2;  // 32-column chunks per 128-byte fill
+    uint32_t it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      if ((int)(it & 1u) != grp) continue;
-      const uint32_t acc_phase = (it >> 1) & 1u;
-      mb_wait(&tmem_full[grp], acc_phase);
+      if ((int)(it % NG) != grp) continue;
+      if (p.diag & 256) mb_wait(&tmem_full[grp], (it / NG) & 1u); else mb_wait_backoff(&tmem_full[grp], (it / NG) & 1u);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * N);
-      float v[NCH][32];
-#pragma unroll
-      for (int c = 0; c < NCH; ++c) tmem_ld32_async(taddr + c * 32, v[c]);
-#pragma unroll
-      for (int c = 0; c < NCH; ++c) tmem_wait_dep(v[c]);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mb_arrive(&tmem_empty[grp]);   // the row lives in registers now
-      if (p.diag & 16) continue;
-      float s4[4] = {0.f, 0.f, 0.f, 0.f};   // four independent chains (a dependent FADD/FFMA issues every 4 cycles)
-#pragma unroll
-      for (int c = 0; c < NCH; ++c)
-#pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 b4 = reinterpret_cast<const float4*>(s_bias + c * 32)[j4];
-          v[c][4 * j4] += b4.x; v[c][4 * j4 + 1] += b4.y; v[c][4 * j4 + 2] += b4.z; v[c][4 * j4 + 3] += b4.w;
-          s4[j4 & 3] += (v[c][4 * j4] + v[c][4 * j4 + 1]) + (v[c][4 * j4 + 2] + v[c][4 * j4 + 3]);
-        }
+      if (p.diag & 16) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mb_arrive(&tmem_empty[grp]);
+        continue;
+      }
+      float v[2][32];
       float mean = 0.f, rstd = 1.f;
       if (p.do_ln && !(p.diag & 32)) {
-        mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) * inv_n;
-        float q4[4] = {0.f, 0.f, 0.f, 0.f};
+        // pass 1: sum and sum of squares, two packed chains each (4 scalar chains)
+        uint64_t s2[2] = {0ull, 0ull}, q2[2] = {0ull, 0ull};
+        tmem_ld32_async(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < NCH; ++c)
+        for (int c = 0; c < NCH; ++c) {
+          tmem_wait_dep(v[c & 1]);
+          if (c + 1 < NCH) tmem_ld32_async(taddr + (c + 1) * 32, v[(c + 1) & 1]);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) { v[c][j] -= mean; q4[j & 3] = fmaf(v[c][j], v[c][j], q4[j & 3]); }
-        rstd = rsqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) * inv_n + p.ln_eps);
-      }
-      const int m0 = tile * BM + q * 32;
-      constexpr int CPF = OUT_F32 ? 1 : 2;  // 32-column chunks per 128-byte fill
-#pragma unroll
-      for (int c0 = 0; c0 < NCH; c0 += CPF) {
-        uint32_t pk[32];
-#pragma unroll
-        for (int cc = 0; cc < CPF; ++cc) {
-          const int c = c0 + cc;
-#pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 g4 = reinterpret_cast<const float4*>(s_lnw + c * 32)[j4];
-            const float4 o4 = reinterpret_cast<const float4*>(s_lnb + c * 32)[j4];
-            const float y0 = fmaf(v[c][4 * j4], rstd * g4.x, o4.x), y1 = fmaf(v[c][4 * j4 + 1], rstd * g4.y, o4.y);
-            const float y2 = fmaf(v[c][4 * j4 + 2], rstd * g4.z, o4.z), y3 = fmaf(v[c][4 * j4 + 3], rstd * g4.w, o4.w);
-            if (OUT_F32) {
-              pk[4 * j4] = __float_as_uint(y0); pk[4 * j4 + 1] = __float_as_uint(y1);
-              pk[4 * j4 + 2] = __float_as_uint(y2); pk[4 * j4 + 3] = __float_as_uint(y3);
-            } else {
-              __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
-              pk[cc * 16 + 2 * j4] = *reinterpret_cast<uint32_t*>(&lo);
-              pk[cc * 16 + 2 * j4 + 1] = *reinterpret_cast<uint32_t*>(&hi);
-            }
+          for (int j = 0; j < 16; ++j) {
+            const uint64_t z = pack2(v[c & 1][2 * j], v[c & 1][2 * j + 1]);
+            s2[j & 1] = add2(s2[j & 1], z);
+            q2[j & 1] = fma2(z, z, q2[j & 1]);
           }
         }
-        uint8_t* tile_s = stg + (fill & 1u) * 4096;
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // slot's previous store was read
-        __syncwarp();
+        float sa, sb, qa, qb;
+        unpack2(add2(s2[0], s2[1]), sa, sb);
+        unpack2(add2(q2[0], q2[1]), qa, qb);
+        mean = (sa + sb) * inv_n;
+        rstd = rsqrtf(fmaxf((qa + qb) * inv_n - mean * mean, 0.f) + p.ln_eps);
+      }
+      const int m0 = tile * BM + q * 32;
+      const uint64_t rstd2 = pack2(rstd, rstd), nmr2 = pack2(-mean * rstd, -mean * rstd);
+      uint32_t pk[32];
+      tmem_ld32_async(taddr, v[0]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(tile_s + lane * 128 + ((j ^ (lane & 7)) << 4)) =
-              make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        if (!(p.diag & 64)) fence_async_smem();
-        __syncwarp();
-        if (lane == 0 && !(p.diag & 1)) tma_store_2d(&map_o, tile_s, c0 * 32, m0);
-        ++fill;
+      for (int c = 0; c < NCH; ++c) {
+        tmem_wait_dep(v[c & 1]);
+        if (c + 1 < NCH) {
+          tmem_ld32_async(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+        } else {   // accumulator fully read: the MMA issuer may overwrite it
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mb_arrive(&tmem_empty[grp]);
+        }
+        const int cc = c % CPF;
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 g4 = reinterpret_cast<const float4*>(s_lnw + c * 32)[j4];
+          const float4 o4 = reinterpret_cast<const float4*>(s_lnb + c * 32)[j4];
+          // (z - mean) * rstd * gamma + beta  ==  fma(fma(z, rstd, -mean*rstd), gamma, beta), z = acc (bias included)
+          const uint64_t ya = fma2(fma2(pack2(v[c & 1][4 * j4], v[c & 1][4 * j4 + 1]), rstd2, nmr2), pack2(g4.x, g4.y), pack2(o4.x, o4.y));
+          const uint64_t yb = fma2(fma2(pack2(v[c & 1][4 * j4 + 2], v[c & 1][4 * j4 + 3]), rstd2, nmr2), pack2(g4.z, g4.w), pack2(o4.z, o4.w));
+          float y0, y1, y2, y3;
+          unpack2(ya, y0, y1);
+          unpack2(yb, y2, y3);
+          if (OUT_F32) {
+            pk[4 * j4] = __float_as_uint(y0); pk[4 * j4 + 1] = __float_as_uint(y1);
+            pk[4 * j4 + 2] = __float_as_uint(y2); pk[4 * j4 + 3] = __float_as_uint(y3);
+          } else {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
+            pk[cc * 16 + 2 * j4] = *reinterpret_cast<uint32_t*>(&lo);
+            pk[cc * 16 + 2 * j4 + 1] = *reinterpret_cast<uint32_t*>(&hi);
+          }
+        }
+        if (cc == CPF - 1) {   // a 128-byte fill is complete
+          if (lane == 0) tma_store_wait_read();   // the tile's previous store has been read out
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0 && !(p.diag & 1)) tma_store_2d(&map_o, stg, (c + 1 - CPF) * 32, m0);
+        }
       }
     }
     if (lane == 0) tma_store_wait_all();
@@ -1014,6 +1085,7 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   p.out_f32 = d->out_dtype == LVC_DT_F32;
   p.out = out;
   p.diag = env_i("LVC_GEMM_DIAG", 0);
+  p.diag_a = workspace;
   const int stage_bytes = (BM + p.BN) * p.BK * 2;
   const int fixed_bytes = 1024 + 2048 + (g.N + 2 * p.BN) * 4 + 16384;  // alignment, barriers, params, store staging
   // two CTAs per SM when TMEM (2 x <=256 columns) and shared memory allow: doubles the epilogue warps,
@@ -1054,7 +1126,7 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   // short-K shapes with N = 128 (Video Swin-B): weights resident in shared memory, row-in-registers LayerNorm
   if (g.N == 128 && g.K <= 256 && !getenv("LVC_GEMM_GENERIC")) {
     const int a_tile = BM * g.K * 2, b_all = g.N * g.K * 2;
-    const int fixed3 = 1024 + 8 * 8192 + b_all + 512 + 3 * g.N * 4 + 64;
+    const int fixed3 = 1024 + 4 * kSwinGroups * 4096 + b_all + (BM + g.N) * 64 + 512 + 3 * g.N * 4 + 64;
     p.stages = std::min(env_i("LVC_GEMM_STAGES", 8), (max_smem - fixed3) / a_tile);
     if (p.stages >= 2) {
       const size_t smem3 = (size_t)fixed3 + (size_t)p.stages * a_tile;
@@ -1066,6 +1138,7 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
       rc = make_out_map(&mo, out, (uint64_t)g.M, (uint64_t)g.N, p.out_f32 != 0);
       if (rc != LVC_OK) return rc;
       const int grid3 = std::min(sms, p.m_tiles);
+      p.tmem_cols = 512;  // kSwinGroups accumulators of N columns
       if (p.out_f32) {
         LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
         lvc_embed_swin_kernel<4, true><<<grid3, kSwinThreads, smem3, st>>>(ma, mb, mo, p);
