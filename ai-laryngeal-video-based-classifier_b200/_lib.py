@@ -16,6 +16,7 @@ LUT_DIV, LUT_MUL64 = 0, 1
 RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL = 0, 1, 2
 LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC, LAYOUT_TOKENS = 0, 1, 2, 3
 DT_F32, DT_BF16, DT_U8 = 0, 1, 2
+SRC_RGB, SRC_BGR = 0, 1
 EMBED_VIVIT, EMBED_TIMESFORMER, EMBED_SWIN = 0, 1, 2
 
 
@@ -32,7 +33,7 @@ class ClipDesc(C.Structure):
     _fields_ = [("resample", C.c_int32), ("layout", C.c_int32), ("out_dtype", C.c_int32),
                 ("out_size", C.c_int32), ("batch", C.c_int32), ("num_frames", C.c_int32),
                 ("max_width", C.c_int32), ("tok_kt", C.c_int32), ("tok_kh", C.c_int32), ("tok_kw", C.c_int32),
-                ("mean", C.c_float * 3), ("std", C.c_float * 3)]
+                ("mean", C.c_float * 3), ("std", C.c_float * 3), ("src_order", C.c_int32), ("reserved", C.c_int32)]
 
 
 class EmbedDesc(C.Structure):

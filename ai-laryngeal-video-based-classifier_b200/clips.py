@@ -77,7 +77,7 @@ class ClipBuilder:
     """
 
     def __init__(self, preset="resnet_infer", num_frames=32, mean=None, std=None, layout=None, dtype=None,
-                 device=None, patch=None):
+                 device=None, patch=None, src_order="RGB"):
         if preset not in PRESETS:
             raise ValueError(f"unknown preset {preset!r}; choose from {sorted(PRESETS)}")
         if not torch.cuda.is_available():
@@ -88,6 +88,11 @@ class ClipBuilder:
         self.std = tuple(float(v) for v in (std if std is not None else s))
         self.layout = layout or lay
         self.dtype = dtype or dt
+        # "BGR": frames exactly as cv2.VideoCapture.read() returns them; the kernel's gather swaps the
+        # channels (replaces the reference's cv2.cvtColor(frame, COLOR_BGR2RGB) pass on the host)
+        if src_order not in ("RGB", "BGR"):
+            raise ValueError("src_order must be 'RGB' or 'BGR'")
+        self.src_order = _lib.SRC_BGR if src_order == "BGR" else _lib.SRC_RGB
         # layout="TOKENS": write the bf16 patch matrix A[M][K] of a (kt,kh,kw) patch embedding directly
         self.patch = tuple(int(v) for v in patch) if patch is not None else (0, 0, 0)
         if self.layout == "TOKENS":
@@ -140,7 +145,7 @@ class ClipBuilder:
         B, T = len(videos), self.num_frames
         tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes)
         d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, *self.patch,
-                          (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std))
+                          (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std), self.src_order, 0)
         return ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
                          _shape(self.layout, B, T, patch=self.patch))
 

@@ -61,6 +61,7 @@ struct ClipParams {
   float mean[3], std[3];     // PTV normalisation
   int kt, kh, kw;            // LVC_LAYOUT_TOKENS: patch size; output is the GEMM operand A[M][K] (bf16)
   int kh_shift;              // log2(kh) when kh is a power of two, else -1
+  int bgr;                   // source frames are BGR (cv2.VideoCapture order): swap channels in the gather
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------
@@ -440,8 +441,9 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
-            const float r0 = __fmaf_rn((float)p0[c], lx0, __fmul_rn((float)p0[c + d1], lx1));
-            const float r1 = __fmaf_rn((float)p1[c], lx0, __fmul_rn((float)p1[c + d1], lx1));
+            const int sc = p.bgr ? 2 - c : c;
+            const float r0 = __fmaf_rn((float)p0[sc], lx0, __fmul_rn((float)p0[sc + d1], lx1));
+            const float r1 = __fmaf_rn((float)p1[sc], lx0, __fmul_rn((float)p1[sc + d1], lx1));
             const float val = __fmaf_rn(r0, ly0, __fmul_rn(r1, ly1));
             const float y = __fdiv_rn(__fsub_rn(val, p.mean[c]), p.std[c]);
             if (p.out_dtype == LVC_DT_F32) __stcs(o + c * cstride, y);
@@ -463,7 +465,8 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           const uint32_t lo0 = __funnelshift_r(a, bq, sh0), hi0 = __funnelshift_r(bq, cq, sh0);
           const uint32_t lo1 = __funnelshift_r(d, e, sh1), hi1 = __funnelshift_r(e, fq, sh1);
           const uint32_t a01 = (uint32_t)a0 | ((uint32_t)a1 << 16);
-          const uint32_t sel[3] = {0x4430u, 0x4441u, 0x4452u};  // (R0,R1), (G0,G1), (B0,B1) of the 8 bytes
+          // byte pairs (c of pixel 0, c of pixel 1) of the 8 source bytes; a BGR source swaps ends
+          const uint32_t sel[3] = {p.bgr ? 0x4452u : 0x4430u, 0x4441u, p.bgr ? 0x4430u : 0x4452u};
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
             const int s0 = (int)__dp2a_lo(a01, __byte_perm(lo0, hi0, sel[c]), 0u);
@@ -626,6 +629,7 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
   for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
   p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
+  p.bgr = d->src_order == LVC_SRC_BGR;
   p.kh_shift = -1;
   for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
   // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)

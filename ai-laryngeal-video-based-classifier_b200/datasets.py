@@ -33,6 +33,7 @@ class FrameSource:
 
     video_paths = ()
     labels = ()
+    channel_order = "RGB"  # "BGR": frames as cv2 decodes them; the clip kernel swaps channels in its gather
 
     def frames(self, i):
         raise NotImplementedError
@@ -105,6 +106,7 @@ class _BaseDataset(torch.utils.data.Dataset):
         self.labels = list(frame_source.labels)
         # the reference seeds the global streams once in __init__ (vivit .../dataset.py:39-40)
         self.rng = sampling.SamplerRng(42, "py")
+        builder_kw.setdefault("src_order", getattr(frame_source, "channel_order", "RGB"))
         self.builder = ClipBuilder(preset, num_frames=self.num_frames, **builder_kw)
 
     def __len__(self):

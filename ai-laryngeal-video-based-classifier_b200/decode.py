@@ -1,8 +1,9 @@
 """Decoded-frame ingest from real files (the step BEFORE the accelerated path).
 
-Decode itself stays on the host with the reference's own calls -- ``cv2.VideoCapture`` read +
-``cv2.cvtColor(BGR2RGB)`` (vivit .../dataset.py:317-350, resnet50-2d-lstm/inference.py:55-72) -- and the
-frames are uploaded once and kept resident in HBM for the fused clip kernel."""
+Decode itself stays on the host with the reference's own call -- ``cv2.VideoCapture.read()`` (vivit
+.../dataset.py:317-350, resnet50-2d-lstm/inference.py:55-72).  The reference's per-frame
+``cv2.cvtColor(frame, COLOR_BGR2RGB)`` pass is NOT run on the host: frames are uploaded as decoded (BGR),
+kept resident in HBM, and the fused clip kernel swaps the channels in its gather (``src_order="BGR"``)."""
 import numpy as np
 import torch
 
@@ -10,7 +11,9 @@ from .datasets import FrameSource
 
 
 class OpenCVFrameSource(FrameSource):
-    def __init__(self, paths, labels=None, device="cuda", cache=True):
+    def __init__(self, paths, labels=None, device="cuda", cache=True, bgr=True):
+        # bgr=True: keep cv2's channel order and let the kernel swap; False: cvtColor on the host
+        self.channel_order = "BGR" if bgr else "RGB"
         self.video_paths = [str(p) for p in paths]
         self.labels = list(labels) if labels is not None else [0] * len(self.video_paths)
         self.device, self._cache, self._do_cache, self._fps = device, {}, cache, {}
@@ -27,7 +30,7 @@ class OpenCVFrameSource(FrameSource):
             ok, fr = cap.read()
             if not ok:
                 break
-            frames.append(cv2.cvtColor(fr, cv2.COLOR_BGR2RGB))
+            frames.append(fr if self.channel_order == "BGR" else cv2.cvtColor(fr, cv2.COLOR_BGR2RGB))
         cap.release()
         if not frames:
             raise ValueError(f"Invalid video: {self.video_paths[i]} - no frames")

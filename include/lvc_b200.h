@@ -126,6 +126,7 @@ enum {
   LVC_LAYOUT_TOKENS = 3
 };
 enum { LVC_DT_F32 = 0, LVC_DT_BF16 = 1, LVC_DT_U8 = 2 };
+enum { LVC_SRC_RGB = 0, LVC_SRC_BGR = 1 };
 
 typedef struct {
   int32_t resample;   /* LVC_RESAMPLE_* */
@@ -141,6 +142,10 @@ typedef struct {
   int32_t tok_kt, tok_kh, tok_kw; /* LVC_LAYOUT_TOKENS: patch size, e.g. (2,16,16); else ignored */
   float mean[3];      /* PTV_EVAL only */
   float std[3];
+  int32_t src_order;  /* LVC_SRC_RGB, or LVC_SRC_BGR: frames as cv2.VideoCapture.read() returns them; the
+                         kernel's gather swaps the channels, replacing cv2.cvtColor(frame, COLOR_BGR2RGB)
+                         (vivit .../dataset.py:336, resnet50-2d-lstm/inference.py:66) */
+  int32_t reserved;
 } lvc_clip_desc;
 
 /* Replaces, for a batch of B videos: the gather (vivit .../dataset.py:246-268), the per-frame

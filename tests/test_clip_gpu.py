@@ -226,3 +226,27 @@ def test_ptv_eval_preset_matches_torch_chain():
     print("ptv_eval max abs err", worst)
     with pytest.raises(NotImplementedError):
         cb(dev, idx, boxes=np.zeros((len(host), T, 4), np.int32))
+
+
+@pytest.mark.parametrize("preset", ["resnet_infer", "vivit", "dataset_u8", "ptv_eval"])
+def test_bgr_source_swaps_channels_in_the_gather(preset):
+    """Row f1: frames as cv2.VideoCapture.read() returns them (BGR).  src_order="BGR" must give exactly what the
+    RGB path gives on cv2.cvtColor(frame, COLOR_BGR2RGB) input (vivit .../dataset.py:336), incl. the checksum."""
+    from lvc_b200 import ClipBuilder
+
+    T = 4
+    host, dev = _videos([(71, 6, 360, 640, "noise"), (72, 5, 100, 150, "ramp"), (73, 4, 448, 448, "noise")])
+    bgr = [torch.from_numpy(np.ascontiguousarray(v[..., ::-1])).cuda() for v in host]
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    a = ClipBuilder(preset, num_frames=T)
+    b = ClipBuilder(preset, num_frames=T, src_order="BGR")
+    sa = torch.zeros(len(host), dtype=torch.int64, device="cuda")
+    sb = torch.zeros_like(sa)
+    if preset == "ptv_eval":
+        oa, ob = a(dev, idx), b(bgr, idx)
+    else:
+        oa, ob = a(dev, idx, stats=sa), b(bgr, idx, stats=sb)
+    assert torch.equal(oa, ob)
+    assert torch.equal(sa, sb)
+    with pytest.raises(ValueError):
+        ClipBuilder(preset, num_frames=T, src_order="GBR")
