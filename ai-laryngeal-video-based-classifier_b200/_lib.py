@@ -62,6 +62,12 @@ _SIGS = {
     "lvc_clip_forward": (C.c_int, [C.POINTER(ClipDesc), C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_clip_launch_count": (C.c_int, [C.POINTER(ClipDesc)]),
+    "lvc_clip_forward_aug": (C.c_int, [C.POINTER(ClipDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lvc_torch_randint": (C.c_int, [C.POINTER(Rng), C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
+    "lvc_torch_rand": (C.c_float, [C.POINTER(Rng)]),
+    "lvc_train_aug_draw": (C.c_int, [C.POINTER(Rng), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double,
+                                     C.POINTER(C.c_int32)]),
 }
 # entry points added by later translation units; bound when the library exports them
 _OPTIONAL_SIGS = {

@@ -111,14 +111,16 @@ class ClipBuilder:
         self.last_h2d_bytes = 0
 
     # -- host-side packing of the small per-batch tables into ONE pinned upload ------------------
-    def _tables(self, videos, indices, boxes):
+    def _tables(self, videos, indices, boxes, aug=None):
         B, T = len(videos), self.num_frames
         idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int32).reshape(B, T))
         nb = 0 if boxes is None else B * T * 16
         vt_bytes = B * C.sizeof(_lib.Video)
         off_idx = (vt_bytes + 15) // 16 * 16
         off_box = (off_idx + idx.nbytes + 15) // 16 * 16
-        host = torch.empty(off_box + nb, dtype=torch.uint8).pin_memory()
+        off_aug = (off_box + nb + 15) // 16 * 16
+        na = 0 if aug is None else B * 16
+        host = torch.empty(off_aug + na, dtype=torch.uint8).pin_memory()
         hv = host.numpy()
         vt = (_lib.Video * B).from_buffer(hv)  # writes straight into the pinned buffer
         max_w = 0
@@ -135,19 +137,31 @@ class ClipBuilder:
         if boxes is not None:
             bx = np.ascontiguousarray(np.asarray(boxes, dtype=np.int32).reshape(B, T, 4))
             hv[off_box:off_box + nb] = bx.view(np.uint8).reshape(-1)
+        if aug is not None:
+            ag = np.ascontiguousarray(np.asarray(aug, dtype=np.int32).reshape(B, 4))
+            if (ag[:, 0] < 224).any():
+                raise ValueError("aug: short-side size must be >= 224")
+            hv[off_aug:off_aug + na] = ag.view(np.uint8).reshape(-1)
         dev = host.to(self.device, non_blocking=True)
         p = dev.data_ptr()
+        self._p_aug = p + off_aug if aug is not None else None
         return dev, host, p, p + off_idx, (p + off_box if boxes is not None else None), max_w
 
-    def prepare(self, videos, indices, boxes=None):
-        """Upload the per-batch tables (video descriptors, indices, boxes: a few KB, one pinned copy)
-        and return a ``ClipBatch`` that ``run`` can launch any number of times."""
+    def prepare(self, videos, indices, boxes=None, aug=None):
+        """Upload the per-batch tables (video descriptors, indices, boxes, augmentation draws: a few KB,
+        one pinned copy) and return a ``ClipBatch`` that ``run`` can launch any number of times.
+        ``aug``: (B, 4) int {short-side size, crop top, crop left, flip} per clip -- the train chain of the
+        pytorchvideo datasets (preset ``ptv_eval`` only; see ``sampling.train_aug_params``)."""
         B, T = len(videos), self.num_frames
-        tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes)
+        if aug is not None and self.resample != _lib.RESAMPLE_PTV_EVAL:
+            raise ValueError("aug belongs to the pytorchvideo chain (preset 'ptv_eval')")
+        tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes, aug)
         d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, *self.patch,
                           (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std), self.src_order, 0)
-        return ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
-                         _shape(self.layout, B, T, patch=self.patch))
+        cb = ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
+                       _shape(self.layout, B, T, patch=self.patch))
+        cb.p_aug = self._p_aug
+        return cb
 
     def run(self, batch, out=None, stats=None):
         """Enqueue the fused kernel for a prepared batch on the current stream (no synchronisation)."""
@@ -156,14 +170,15 @@ class ClipBuilder:
         elif tuple(out.shape) != batch.shape or out.dtype != self.dtype or not out.is_contiguous():
             raise ValueError("out has the wrong shape, dtype or strides")
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        st = _lib.lib().lvc_clip_forward(C.byref(batch.desc), batch.p_vid, batch.p_idx, batch.p_box,
-                                         self.lut.data_ptr() if self.lut is not None else None,
-                                         out.data_ptr(), stats.data_ptr() if stats is not None else None, stream)
+        st = _lib.lib().lvc_clip_forward_aug(C.byref(batch.desc), batch.p_vid, batch.p_idx, batch.p_box,
+                                             getattr(batch, "p_aug", None),
+                                             self.lut.data_ptr() if self.lut is not None else None,
+                                             out.data_ptr(), stats.data_ptr() if stats is not None else None, stream)
         _lib.check(st, "lvc_clip_forward")
         self.launches += _lib.lib().lvc_clip_launch_count(C.byref(batch.desc))
         return out
 
-    def __call__(self, videos, indices, boxes=None, out=None, stats=None):
+    def __call__(self, videos, indices, boxes=None, out=None, stats=None, aug=None):
         """videos: list of B CUDA uint8 (N,H,W,3) tensors; indices: (B,T) ints; boxes: (B,T,4) int
         xyxy or None (a box with x1 < 0 = no detection = full frame); out: optional preallocated
         output; stats: optional CUDA int64 (B,) checksum accumulator.  Returns the clip tensor
@@ -171,7 +186,7 @@ class ClipBuilder:
         if len(videos) == 0:
             return torch.empty(_shape(self.layout, 0, self.num_frames, patch=self.patch), dtype=self.dtype,
                                device=self.device)
-        batch = self.prepare(videos, indices, boxes)
+        batch = self.prepare(videos, indices, boxes, aug)
         out = self.run(batch, out, stats)
         batch.tables.record_stream(torch.cuda.current_stream(self.device))
         self._keep = batch  # staging buffers must outlive the enqueued work

@@ -50,6 +50,7 @@ struct ClipParams {
   const lvc_video* videos;
   const int32_t* indices;
   const int32_t* boxes;
+  const int32_t* aug;        // PTV: per-clip {short side, crop top, crop left, flip} or NULL (eval chain)
   const float* lut;
   void* out;
   unsigned long long* stats;
@@ -171,14 +172,14 @@ __device__ __forceinline__ void torch_tap(int dst, float scale, int in, int& i0,
   l0 = __fsub_rn(1.0f, l1);
   i1 = i0 + (i0 < in - 1 ? 1 : 0);
 }
-// pytorchvideo ShortSideScale(256) + torchvision CenterCrop(224) geometry for an HxW frame.
-__device__ __forceinline__ void ptv_geom(int H, int W, int& nh, int& nw, int& top, int& left) {
-  // python: int(math.floor((float(h) / w) * size)) and int(round((n - crop) / 2.0)), all in double
-  if (W < H) { nw = 256; nh = (int)floor(__dmul_rn(__ddiv_rn((double)H, (double)W), 256.0)); }
-  else { nh = 256; nw = (int)floor(__dmul_rn(__ddiv_rn((double)W, (double)H), 256.0)); }
-  top = (int)rint((double)(nh - S) / 2.0);
-  left = (int)rint((double)(nw - S) / 2.0);
+// pytorchvideo ShortSideScale(size) geometry for an HxW frame, then the crop origin: torchvision
+// CenterCrop(224) when `aug` is absent (eval chain), else the drawn RandomCrop origin (train chain).
+__device__ __forceinline__ void ptv_geom(int H, int W, int size, int& nh, int& nw) {
+  // python: int(math.floor((float(h) / w) * size)), in double
+  if (W < H) { nw = size; nh = (int)floor(__dmul_rn(__ddiv_rn((double)H, (double)W), (double)size)); }
+  else { nh = size; nw = (int)floor(__dmul_rn(__ddiv_rn((double)W, (double)H), (double)size)); }
 }
+__device__ __forceinline__ int center_crop_origin(int n) { return (int)rint((double)(n - S) / 2.0); }
 __device__ __forceinline__ void group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(2 + g), "r"(S) : "memory");
 }
@@ -269,8 +270,19 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       int ox = 0, oy = 0, sw = v.width, sh = v.height;  // source window: origin and size
       int nh = 0, nw = 0, top = 0, left = 0;
       float scale_h = 0.f;
+      int flip = 0;
       if (MODE == MODE_PTV) {
-        ptv_geom(v.height, v.width, nh, nw, top, left);
+        if (p.aug) {   // train chain: RandomShortSideScale size, RandomCrop origin, RandomHorizontalFlip (per clip)
+          const int4 a = reinterpret_cast<const int4*>(p.aug)[b];
+          ptv_geom(v.height, v.width, max(a.x, S), nh, nw);
+          top = min(max(a.y, 0), nh - S);
+          left = min(max(a.z, 0), nw - S);
+          flip = a.w != 0;
+        } else {
+          ptv_geom(v.height, v.width, 256, nh, nw);
+          top = center_crop_origin(nh);
+          left = center_crop_origin(nw);
+        }
         scale_h = __fdiv_rn((float)v.height, (float)nh);
         const float scale_w = __fdiv_rn((float)v.width, (float)nw);
         int xa, xb, xc, xd; float l0, l1;
@@ -343,7 +355,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           h->rows[lane >> 1] = rd;
         }
         if (lane == 0) {
-          h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first; h->flags = area ? 1 : 0;
+          h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first; h->flags = (area ? 1 : 0) | (flip << 1);
           h->ox = ox; h->nw = nw; h->left = left;
         }
         if (leader && bulk_bytes < my_bytes) {
@@ -391,10 +403,12 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       f = h->frame;
       if (MODE == MODE_PTV) {
         const int hox = h->ox;
-        if (sw != cached_sw || hox != cached_ox) {
-          cached_sw = sw; cached_ox = hox;
+        const int geo = h->nw | (h->left << 12) | ((flags & 2) << 28);   // nw, left < 4096
+        if (sw != cached_sw || hox != cached_ox || geo != cached_flags) {
+          cached_sw = sw; cached_ox = hox; cached_flags = geo;
           int x0, x1;
-          torch_tap(x + h->left, __fdiv_rn((float)sw, (float)h->nw), sw, x0, x1, lx0, lx1);
+          const int xs = (flags & 2) ? S - 1 - x : x;   // hflip: output column x shows crop column 223 - x
+          torch_tap(xs + h->left, __fdiv_rn((float)sw, (float)h->nw), sw, x0, x1, lx0, lx1);
           xo = 3 * (x0 - hox);
           d1 = 3 * (x1 - x0);
         }
@@ -592,6 +606,12 @@ extern "C" int lvc_clip_launch_count(const lvc_clip_desc* d) { return d ? 1 : 0;
 extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
                                 const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
                                 void* stream) {
+  return lvc_clip_forward_aug(d, videos, indices, boxes, nullptr, lut, out, stats, stream);
+}
+
+extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
+                                    const int32_t* boxes, const int32_t* aug, const float* lut, void* out,
+                                    uint64_t* stats, void* stream) {
   if (!d || !videos || !indices || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: NULL argument");
   if (d->out_size != S) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: out_size %d unsupported (224 only)", d->out_size);
   if (d->batch <= 0 || d->num_frames <= 0 || d->max_width <= 0)
@@ -617,6 +637,8 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: float output needs a LUT (lvc_build_lut)");
   }
   if (boxes && (reinterpret_cast<uintptr_t>(boxes) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: boxes must be 16-byte aligned");
+  if (aug && !ptv) return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: the augmentation table belongs to the pytorchvideo chain (LVC_RESAMPLE_PTV_EVAL)");
+  if (aug && (reinterpret_cast<uintptr_t>(aug) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: aug must be 16-byte aligned");
   if ((int64_t)d->batch * d->num_frames > (1 << 24)) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: too many frames in one call");
 
   const DeviceInfo& di = device_info();
@@ -624,7 +646,7 @@ extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos,
 
   const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
   ClipParams p{};
-  p.videos = videos; p.indices = indices; p.boxes = boxes; p.lut = lut; p.out = out;
+  p.videos = videos; p.indices = indices; p.boxes = boxes; p.aug = aug; p.lut = lut; p.out = out;
   p.stats = reinterpret_cast<unsigned long long*>(stats);
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
   for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }

@@ -138,6 +138,40 @@ int lvc_rng_seed_np(lvc_rng* st, uint32_t seed) {
 double lvc_rng_random(lvc_rng* st) { return py_random(st); }
 uint32_t lvc_rng_u32(lvc_rng* st) { return next_u32(st); }
 
+// ---- torch CPU generator stream (at::mt19937 seeded by torch.manual_seed) -------------------
+// torch.randint(low, high, (1,)): ATen random_from_to -> uniform_int_from_to(random(), range, base)
+// = uint32 draw % range + base for range < 2^32.
+int lvc_torch_randint(lvc_rng* st, int64_t low, int64_t high, int64_t* out) {
+  if (!st || !out) return lvc_fail(LVC_E_INVAL, "lvc_torch_randint: NULL argument");
+  if (high <= low || (uint64_t)(high - low) >= (1ull << 32)) return lvc_fail(LVC_E_INVAL, "lvc_torch_randint: need 0 < high - low < 2^32");
+  *out = (int64_t)((uint64_t)next_u32(st) % (uint64_t)(high - low)) + low;
+  return LVC_OK;
+}
+// torch.rand(1) (float32): uniform_real(random(), 0, 1) = (uint32 draw & (2^24 - 1)) * 2^-24.
+float lvc_torch_rand(lvc_rng* st) { return st ? (float)(next_u32(st) & ((1u << 24) - 1u)) * (1.0f / 16777216.0f) : -1.0f; }
+
+// One clip's draws of the train chain in the reference's order (videoswintransformer/.../dataset.py:156-161):
+// RandomShortSideScale: size = randint(min, max+1); RandomCrop.get_params on the scaled (nh, nw): if it is
+// already 224x224 no draw, else top = randint(0, nh-224+1), left = randint(0, nw-224+1);
+// RandomHorizontalFlip: flip = rand(1) < p.   out = {size, top, left, flip}.
+int lvc_train_aug_draw(lvc_rng* st, int32_t height, int32_t width, int32_t min_size, int32_t max_size,
+                       double flip_p, int32_t* out) {
+  if (!st || !out) return lvc_fail(LVC_E_INVAL, "lvc_train_aug_draw: NULL argument");
+  if (height <= 0 || width <= 0 || min_size < 224 || max_size < min_size) return lvc_fail(LVC_E_INVAL, "lvc_train_aug_draw: need positive extents and 224 <= min_size <= max_size");
+  int64_t size = 0, top = 0, left = 0;
+  lvc_torch_randint(st, min_size, (int64_t)max_size + 1, &size);
+  int64_t nh, nw;
+  if (width < height) { nw = size; nh = (int64_t)std::floor(((double)height / (double)width) * (double)size); }
+  else { nh = size; nw = (int64_t)std::floor(((double)width / (double)height) * (double)size); }
+  if (!(nh == 224 && nw == 224)) {
+    lvc_torch_randint(st, 0, nh - 224 + 1, &top);
+    lvc_torch_randint(st, 0, nw - 224 + 1, &left);
+  }
+  const float u = lvc_torch_rand(st);
+  out[0] = (int32_t)size; out[1] = (int32_t)top; out[2] = (int32_t)left; out[3] = (u < (float)flip_p) ? 1 : 0;
+  return LVC_OK;
+}
+
 double lvc_dynamic_fps(int64_t total_frames, int32_t num_frames, double original_fps) {
   if (total_frames >= num_frames) return std::numeric_limits<double>::quiet_NaN();
   if (original_fps <= 0) original_fps = 30.0;

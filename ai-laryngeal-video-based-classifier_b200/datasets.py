@@ -160,9 +160,15 @@ class SwinVideoDataset(_BaseDataset):
     transform chain (ShortSideScale 256, CenterCrop 224, Normalize 0.45/0.225 on 0..255 values)."""
 
     def __init__(self, root_dir=None, mode="train", sampling_method="uniform", num_frames=32, fps=30, stride=0.5,
-                 logger=None, log_dir=None, frame_source=None):
+                 logger=None, log_dir=None, frame_source=None, augment=None, aug_seed=0):
         self.mode, self.fps, self.stride = mode, fps, stride
         self._setup(root_dir, mode, sampling_method, num_frames, logger, frame_source, "ptv_eval")
+        # mode == 'train' uses RandomShortSideScale(256,320) + RandomCrop(224) + RandomHorizontalFlip(0.5)
+        # (videoswintransformer/.../dataset.py:153-162); the draws come from an explicit torch-compatible
+        # stream (sampling.TorchRng(aug_seed) == torch.manual_seed(aug_seed)), one draw per clip in item order
+        self.augment = (mode == "train") if augment is None else bool(augment)
+        self.aug_rng = sampling.TorchRng(aug_seed)
+        self.last_aug = None
 
     def get_sampling_indices(self, video_path, total_frames):
         i = self.video_paths.index(video_path) if video_path in self.video_paths else 0
@@ -171,7 +177,11 @@ class SwinVideoDataset(_BaseDataset):
     def get_batch(self, indices):
         vids = [self.source.frames(i) for i in indices]
         fidx = [window_subsample(self._indices(v.shape[0]), self.num_frames) for v in vids]
-        clips = self.builder(vids, fidx)  # (B, C, T, 224, 224)
+        aug = None
+        if self.augment:
+            aug = [sampling.train_aug_params(v.shape[1], v.shape[2], self.aug_rng) for v in vids]
+        self.last_aug = aug
+        clips = self.builder(vids, fidx, aug=aug)  # (B, C, T, 224, 224)
         return clips.unsqueeze(1), torch.tensor([[self.labels[i]] for i in indices], dtype=torch.long)
 
     def __getitem__(self, idx):
@@ -186,16 +196,24 @@ class LstmVideoDataset(_BaseDataset):
     reseed_each_call = True
 
     def __init__(self, root_dir=None, split="train", sampling_method="uniform", sequence_length=32, transform=None,
-                 logger=None, frame_source=None):
+                 logger=None, frame_source=None, augment=None, aug_seed=0):
         if transform is not None:
             raise NotImplementedError("custom transforms are not supported; the eval chain is fused in the kernel")
         self.split, self.sequence_length = split, sequence_length
         self._setup(root_dir, split, sampling_method, sequence_length, logger, frame_source, "ptv_eval")
+        # split == 'train': the same random chain as the Swin dataset (resnet50-2d-lstm/.../dataset.py:63-72)
+        self.augment = (split == "train") if augment is None else bool(augment)
+        self.aug_rng = sampling.TorchRng(aug_seed)
+        self.last_aug = None
 
     def get_batch(self, indices):
         vids = [self.source.frames(i) for i in indices]
         fidx = [window_subsample(self._indices(v.shape[0]), self.num_frames) for v in vids]
-        return self.builder(vids, fidx), torch.tensor([self.labels[i] for i in indices], dtype=torch.float32)
+        aug = None
+        if self.augment:
+            aug = [sampling.train_aug_params(v.shape[1], v.shape[2], self.aug_rng) for v in vids]
+        self.last_aug = aug
+        return self.builder(vids, fidx, aug=aug), torch.tensor([self.labels[i] for i in indices], dtype=torch.float32)
 
     def __getitem__(self, idx):
         clips, labels = self.get_batch([idx])

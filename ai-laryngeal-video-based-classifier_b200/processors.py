@@ -136,3 +136,33 @@ class PtvEvalTransform:
         out = dict(sample)
         out["video"] = self.builder([v], [idx])[0]
         return out
+
+
+class PtvTrainTransform(PtvEvalTransform):
+    """Train-mode chain of the pytorchvideo datasets (videoswintransformer/.../dataset.py:153-162):
+    UniformTemporalSubsample(T) -> RandomShortSideScale(256, 320) -> RandomCrop(224) ->
+    RandomHorizontalFlip(0.5) -> Normalize, one draw per clip.  The draws come from ``rng`` (a
+    ``sampling.TorchRng``: the stream ``torch.manual_seed(seed)`` gives the reference), so a seeded run is
+    reproducible and comparable with the reference; geometry, flip and normalisation run in the fused kernel."""
+
+    def __init__(self, num_frames, mean=KINETICS[0], std=KINETICS[1], device=None, rng=None, min_size=256,
+                 max_size=320, flip_p=0.5):
+        super().__init__(num_frames, mean, std, device)
+        from .sampling import TorchRng
+
+        self.rng = rng if rng is not None else TorchRng(0)
+        self.min_size, self.max_size, self.flip_p = min_size, max_size, flip_p
+        self.last_params = None
+
+    def __call__(self, sample):
+        from .sampling import train_aug_params, uniform_temporal_subsample
+
+        v = sample["video"]
+        if v.dtype != torch.uint8:
+            v = v.permute(1, 2, 3, 0).round().clamp(0, 255).to(torch.uint8)
+        v = v.to(self.builder.device).contiguous()
+        idx = uniform_temporal_subsample(v.shape[0], self.num_frames)
+        self.last_params = train_aug_params(v.shape[1], v.shape[2], self.rng, self.min_size, self.max_size, self.flip_p)
+        out = dict(sample)
+        out["video"] = self.builder([v], [idx], aug=[self.last_params])[0]
+        return out

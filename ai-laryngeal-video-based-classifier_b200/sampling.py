@@ -104,3 +104,33 @@ def random_window_sampling(total_frames, num_frames, rng=None, numpy_stream=Fals
         return get_sampling_indices("random_window", total_frames, num_frames, SamplerRng(42, "np"),
                                     _lib.VARIANT_NUMPY_INFER)
     return get_sampling_indices("random_window", total_frames, num_frames, rng, _lib.VARIANT_CLAMPED)
+
+
+class TorchRng:
+    """The torch CPU generator stream after ``torch.manual_seed(seed)`` (at::mt19937), emulated in the C
+    library: ``randint(lo, hi)`` == ``torch.randint(lo, hi, (1,)).item()``, ``rand()`` == ``torch.rand(1).item()``.
+    The explicit, reproducible RNG contract of the train-time augmentation chain."""
+
+    def __init__(self, seed=0):
+        self.state = _lib.Rng()
+        self.seed(seed)
+
+    def seed(self, seed):
+        _lib.check(_lib.lib().lvc_rng_seed_np(C.byref(self.state), int(seed) & 0xFFFFFFFF), "rng_seed")
+
+    def randint(self, low, high):
+        o = C.c_int64()
+        _lib.check(_lib.lib().lvc_torch_randint(C.byref(self.state), int(low), int(high), C.byref(o)), "torch_randint")
+        return int(o.value)
+
+    def rand(self):
+        return float(_lib.lib().lvc_torch_rand(C.byref(self.state)))
+
+
+def train_aug_params(height, width, rng, min_size=256, max_size=320, flip_p=0.5):
+    """One clip's draws of RandomShortSideScale(min,max) -> RandomCrop(224) -> RandomHorizontalFlip(p)
+    in the reference's order (videoswintransformer/.../dataset.py:156-161) -> [size, top, left, flip]."""
+    out = (C.c_int32 * 4)()
+    _lib.check(_lib.lib().lvc_train_aug_draw(C.byref(rng.state), int(height), int(width), int(min_size), int(max_size),
+                                             float(flip_p), out), "train_aug_draw")
+    return [int(v) for v in out]

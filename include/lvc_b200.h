@@ -76,6 +76,16 @@ int lvc_uniform_temporal_subsample(int64_t t, int32_t num_samples, int64_t* out)
 /* Swin copy's second return value (videoswintransformer/.../dataset.py:104-121); NaN = None. */
 double lvc_dynamic_fps(int64_t total_frames, int32_t num_frames, double original_fps);
 
+/* torch CPU generator stream: after lvc_rng_seed_np(st, seed) the state equals torch.manual_seed(seed)'s
+ * at::mt19937.  lvc_torch_randint = torch.randint(low, high, (1,)).item(); lvc_torch_rand = torch.rand(1).item(). */
+int lvc_torch_randint(lvc_rng* st, int64_t low, int64_t high, int64_t* out);
+float lvc_torch_rand(lvc_rng* st);
+/* The train chain's per-clip draws in the reference's order -- RandomShortSideScale(min,max), RandomCrop(224),
+ * RandomHorizontalFlip(p) (videoswintransformer/.../dataset.py:156-161) -- for a (height, width) video.
+ * out = {short-side size, crop top, crop left, flip}: one row of lvc_clip_forward_aug's `aug` table. */
+int lvc_train_aug_draw(lvc_rng* st, int32_t height, int32_t width, int32_t min_size, int32_t max_size,
+                       double flip_p, int32_t* out);
+
 /* -------------------------------------------------- normalisation look-up table (host) ---- */
 
 enum {
@@ -163,6 +173,17 @@ typedef struct {
 int lvc_clip_forward(const lvc_clip_desc* desc, const lvc_video* videos, const int32_t* indices,
                      const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
                      void* stream);
+
+/* Train-time chain of the pytorchvideo datasets (videoswintransformer/.../dataset.py:153-162,
+ * resnet50-3d-video/.../dataset.py:173-182, resnet50-2d-lstm/.../dataset.py:63-72): RandomShortSideScale(256,320)
+ * -> RandomCrop(224) -> RandomHorizontalFlip(0.5) -> Normalize, drawn ONCE per clip like the reference's
+ * clip-level transforms.  Same as lvc_clip_forward with resample = LVC_RESAMPLE_PTV_EVAL plus
+ *   aug      device  int32[B*4]  per clip {short-side size, crop top, crop left, flip}; the draws themselves are
+ *                    made on the host on a torch-compatible MT19937 stream (lvc_torch_randint / lvc_torch_rand)
+ *                    so that a seeded run reproduces the reference's torch.manual_seed stream.  NULL = eval chain. */
+int lvc_clip_forward_aug(const lvc_clip_desc* desc, const lvc_video* videos, const int32_t* indices,
+                         const int32_t* boxes, const int32_t* aug, const float* lut, void* out,
+                         uint64_t* stats, void* stream);
 
 /* Number of kernel launches lvc_clip_forward enqueues for this descriptor (for accounting). */
 int lvc_clip_launch_count(const lvc_clip_desc* desc);

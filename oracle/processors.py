@@ -119,3 +119,44 @@ def ptv_eval_chain(frames, mean=(0.45, 0.45, 0.45), std=(0.225, 0.225, 0.225)):
     m = torch.tensor(mean, dtype=torch.float32).view(3, 1, 1, 1)
     s = torch.tensor(std, dtype=torch.float32).view(3, 1, 1, 1)
     return ((x - m) / s).contiguous().numpy()
+
+
+def ptv_train_chain(frames, seed=None, mean=(0.45, 0.45, 0.45), std=(0.225, 0.225, 0.225), min_size=256,
+                    max_size=320, flip_p=0.5, generator_seeded=False):
+    """f2 train chain -- videoswintransformer/.../dataset.py:153-162 (= resnet50-2d-lstm/.../dataset.py:63-72,
+    resnet50-3d-video/.../dataset.py:173-182): RandomShortSideScale(256, 320) -> transforms.RandomCrop(224)
+    -> transforms.RandomHorizontalFlip(0.5) -> Normalize, applied to the whole (C,T,H,W) clip.
+    RandomCrop / RandomHorizontalFlip are torchvision's own classes (installed); RandomShortSideScale is
+    restated from pytorchvideo's published definition (``size = torch.randint(min, max + 1, (1,)).item()``
+    then short_side_scale, package absent -> PARITY UNPINNED for that step).  All draws come from torch's
+    global CPU generator: ``seed`` calls torch.manual_seed first (unless the caller already seeded it).
+    Returns (out (C,T,224,224) float32, [size, top, left, flip])."""
+    import math
+
+    import torch
+    import torch.nn.functional as F
+    from torchvision import transforms
+
+    if seed is not None and not generator_seeded:
+        torch.manual_seed(seed)
+    x = torch.from_numpy(np.asarray(frames)).permute(3, 0, 1, 2).float()  # (C,T,H,W)
+    H, W = x.shape[2:]
+    size = int(torch.randint(min_size, max_size + 1, (1,)).item())
+    if W < H:
+        nh, nw = int(math.floor((float(H) / W) * size)), size
+    else:
+        nh, nw = size, int(math.floor((float(W) / H) * size))
+    x = F.interpolate(x, size=(nh, nw), mode="bilinear", align_corners=False)
+    # record what the torchvision classes are about to draw, from a cloned generator state
+    state = torch.get_rng_state()
+    top, left = 0, 0
+    if not (nh == 224 and nw == 224):
+        top = int(torch.randint(0, nh - 224 + 1, size=(1,)).item())
+        left = int(torch.randint(0, nw - 224 + 1, size=(1,)).item())
+    flip = int(bool(torch.rand(1) < flip_p))
+    torch.set_rng_state(state)
+    x = transforms.RandomCrop(224)(x)
+    x = transforms.RandomHorizontalFlip(p=flip_p)(x)
+    m = torch.tensor(mean, dtype=torch.float32).view(3, 1, 1, 1)
+    s = torch.tensor(std, dtype=torch.float32).view(3, 1, 1, 1)
+    return ((x - m) / s).contiguous().numpy(), [size, top, left, flip]

@@ -250,3 +250,53 @@ def test_bgr_source_swaps_channels_in_the_gather(preset):
     assert torch.equal(sa, sb)
     with pytest.raises(ValueError):
         ClipBuilder(preset, num_frames=T, src_order="GBR")
+
+
+def test_ptv_train_chain_matches_torchvision_under_seed():
+    """Row f2: RandomShortSideScale(256,320) + RandomCrop(224) + RandomHorizontalFlip(0.5) + Normalize, one draw
+    per clip on the torch-compatible stream.  Oracle = torch CPU + torchvision's own RandomCrop / RandomHorizontalFlip
+    under torch.manual_seed (RandomShortSideScale restated, pytorchvideo absent).  Same tolerance as the eval chain."""
+    from lvc_b200 import ClipBuilder, sampling
+
+    T = 4
+    host, dev = _videos([(81, 6, 720, 1280, "noise"), (82, 5, 480, 640, "ramp"), (83, 5, 640, 480, "noise"),
+                         (84, 4, 300, 300, "noise"), (85, 4, 224, 224, "noise"), (86, 4, 1080, 1920, "noise")])
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    for seed in (0, 3):
+        rng = sampling.TorchRng(seed)
+        aug = [sampling.train_aug_params(v.shape[1], v.shape[2], rng) for v in host]
+        out = ClipBuilder("ptv_eval", num_frames=T)(dev, idx, aug=aug).cpu().numpy()
+        torch.manual_seed(seed)
+        worst, flips = 0.0, 0
+        for b, v in enumerate(host):
+            want, params = op.ptv_train_chain(v[idx[b]], seed=None)
+            assert params == aug[b]
+            flips += params[3]
+            assert np.allclose(out[b], want, atol=1.1e-2, rtol=1e-5)
+            worst = max(worst, float(np.abs(out[b] - want).max()))
+        print("ptv_train seed", seed, "max abs err", worst, "flips", flips)
+    with pytest.raises(ValueError):
+        ClipBuilder("resnet_infer", num_frames=T)(dev, idx, aug=aug)
+    with pytest.raises(ValueError):
+        ClipBuilder("ptv_eval", num_frames=T)(dev, idx, aug=[[100, 0, 0, 0]] * len(host))
+
+
+def test_swin_dataset_train_mode_draws_per_clip():
+    from lvc_b200.datasets import SwinVideoDataset, TensorFrameSource
+
+    host, _ = _videos([(91, 40, 240, 320, "noise"), (92, 36, 320, 240, "ramp")])
+    src = TensorFrameSource(host, labels=[0, 1])
+    ds = SwinVideoDataset(mode="train", num_frames=8, frame_source=src, aug_seed=11)
+    ev = SwinVideoDataset(mode="val", num_frames=8, frame_source=src)
+    clips, labels = ds.get_batch([0, 1])
+    assert clips.shape == (2, 1, 3, 8, 224, 224) and labels.tolist() == [[0], [1]]
+    assert ds.last_aug is not None and ev.augment is False
+    torch.manual_seed(11)
+    for b in range(2):
+        fidx = ds.get_sampling_indices(ds.video_paths[b], host[b].shape[0])[0]
+        lo, hi = min(fidx), max(fidx)
+        from lvc_b200.sampling import uniform_temporal_subsample
+        pick = [lo + k for k in uniform_temporal_subsample(hi - lo + 1, 8)]
+        want, params = op.ptv_train_chain(host[b][pick], seed=None)
+        assert params == ds.last_aug[b]
+        assert np.allclose(clips[b, 0].cpu().numpy(), want, atol=1.1e-2, rtol=1e-5)
