@@ -33,7 +33,7 @@ class ClipDesc(C.Structure):
     _fields_ = [("resample", C.c_int32), ("layout", C.c_int32), ("out_dtype", C.c_int32),
                 ("out_size", C.c_int32), ("batch", C.c_int32), ("num_frames", C.c_int32),
                 ("max_width", C.c_int32), ("tok_kt", C.c_int32), ("tok_kh", C.c_int32), ("tok_kw", C.c_int32),
-                ("mean", C.c_float * 3), ("std", C.c_float * 3), ("src_order", C.c_int32), ("reserved", C.c_int32)]
+                ("mean", C.c_float * 3), ("std", C.c_float * 3), ("src_order", C.c_int32), ("src_float", C.c_int32)]
 
 
 class EmbedDesc(C.Structure):

@@ -77,7 +77,7 @@ class ClipBuilder:
     """
 
     def __init__(self, preset="resnet_infer", num_frames=32, mean=None, std=None, layout=None, dtype=None,
-                 device=None, patch=None, src_order="RGB"):
+                 device=None, patch=None, src_order="RGB", float_frames=False):
         if preset not in PRESETS:
             raise ValueError(f"unknown preset {preset!r}; choose from {sorted(PRESETS)}")
         if not torch.cuda.is_available():
@@ -93,6 +93,11 @@ class ClipBuilder:
         if src_order not in ("RGB", "BGR"):
             raise ValueError("src_order must be 'RGB' or 'BGR'")
         self.src_order = _lib.SRC_BGR if src_order == "BGR" else _lib.SRC_RGB
+        # float_frames: resize as the reference's primary Dataset branch does (pytorchvideo decode gives float32
+        # frames, vivit .../dataset.py:244-284): cv2.resize in float, then truncation to uint8
+        self.float_frames = bool(float_frames)
+        if self.float_frames and rs == _lib.RESAMPLE_PTV_EVAL:
+            raise ValueError("float_frames applies to the cv2.resize presets only")
         # layout="TOKENS": write the bf16 patch matrix A[M][K] of a (kt,kh,kw) patch embedding directly
         self.patch = tuple(int(v) for v in patch) if patch is not None else (0, 0, 0)
         if self.layout == "TOKENS":
@@ -157,7 +162,7 @@ class ClipBuilder:
             raise ValueError("aug belongs to the pytorchvideo chain (preset 'ptv_eval')")
         tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes, aug)
         d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, *self.patch,
-                          (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std), self.src_order, 0)
+                          (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std), self.src_order, int(self.float_frames))
         cb = ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
                        _shape(self.layout, B, T, patch=self.patch))
         cb.p_aug = self._p_aug

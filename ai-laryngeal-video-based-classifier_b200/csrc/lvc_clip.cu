@@ -62,6 +62,7 @@ struct ClipParams {
   float mean[3], std[3];     // PTV normalisation
   int kt, kh, kw;            // LVC_LAYOUT_TOKENS: patch size; output is the GEMM operand A[M][K] (bf16)
   int kh_shift;              // log2(kh) when kh is a power of two, else -1
+  int f32src;                // cv2.resize as the reference runs it on FLOAT frames, result truncated to uint8
   int bgr;                   // source frames are BGR (cv2.VideoCapture order): swap channels in the gather
 };
 
@@ -113,6 +114,14 @@ __device__ __forceinline__ void cv_tap(int d, double scale, int& s, float& fr) {
   float fl = floorf(f);
   s = (int)fl;
   fr = __fsub_rn(f, fl);
+}
+// Float-frame variant (cv2.resize on float32 input, vivit .../dataset.py:244-284): the fraction keeps
+// double precision until the final cast, which reproduces the installed OpenCV to 1 float32 ulp.
+__device__ __forceinline__ void cv_tap64(int d, double scale, int& s, float& fr) {
+  const double f = __dadd_rn(__dmul_rn((double)d + 0.5, scale), -0.5);
+  const double fl = floor(f);
+  s = (int)fl;
+  fr = (float)__dsub_rn(f, fl);
 }
 __device__ __forceinline__ double cv_scale(int src) {
   double inv = __ddiv_rn((double)S, (double)src);
@@ -326,9 +335,10 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             ysrc = 2 * oyr + (lane & 1);
           } else {
             int sy; float fr;
-            cv_tap(oyr, scale_y, sy, fr);
+            if (p.f32src) cv_tap64(oyr, scale_y, sy, fr); else cv_tap(oyr, scale_y, sy, fr);
             ysrc = min(max(sy + (lane & 1), 0), sh - 1);
-            cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
+            if (p.f32src) cb = __float_as_int((lane & 1) ? fr : __fsub_rn(1.0f, fr));
+            else cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
           }
           const uint64_t addr = frame_base + (uint64_t)(oy + ysrc) * row_bytes + (uint64_t)ox * 3u;
           a = addr & ~(uint64_t)15;
@@ -417,11 +427,12 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         if (flags & 1) { xo = 6 * x; d1 = 3; a0 = 1; a1 = 1; }
         else {
           int sx; float fr;
-          cv_tap(x, cv_scale(sw), sx, fr);
+          if (p.f32src) cv_tap64(x, cv_scale(sw), sx, fr); else cv_tap(x, cv_scale(sw), sx, fr);
           if (sx < 0) { sx = 0; fr = 0.f; }
           if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }
           a0 = coef(__fsub_rn(1.0f, fr));
           a1 = coef(fr);
+          lx0 = __fsub_rn(1.0f, fr); lx1 = fr;
           xo = 3 * sx;
           d1 = (sx + 1 <= sw - 1) ? 3 : 0;
         }
@@ -481,12 +492,29 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           const uint32_t a01 = (uint32_t)a0 | ((uint32_t)a1 << 16);
           // byte pairs (c of pixel 0, c of pixel 1) of the 8 source bytes; a BGR source swaps ends
           const uint32_t sel[3] = {p.bgr ? 0x4452u : 0x4430u, 0x4441u, p.bgr ? 0x4430u : 0x4452u};
+          if (p.f32src) {
+            // float frames: two float products and an add per pass (no FMA contraction), truncation to uint8;
+            // the exact 2x2 case is INTER_AREA = sum * 0.25f, truncated
+            const float by0 = __int_as_float(rd.b0), by1 = __int_as_float(rd.b1);
 #pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            const int s0 = (int)__dp2a_lo(a01, __byte_perm(lo0, hi0, sel[c]), 0u);
-            const int s1 = (int)__dp2a_lo(a01, __byte_perm(lo1, hi1, sel[c]), 0u);
-            v[c] = (flags & 1) ? ((s0 + s1 + 2) >> 2)
-                               : ((((rd.b0 * (s0 >> 4)) >> 16) + ((rd.b1 * (s1 >> 4)) >> 16) + 2) >> 2);
+            for (int c = 0; c < 3; ++c) {
+              const uint32_t w0c = __byte_perm(lo0, hi0, sel[c]), w1c = __byte_perm(lo1, hi1, sel[c]);
+              if (flags & 1) {
+                v[c] = (int)((w0c & 0xffu) + ((w0c >> 8) & 0xffu) + (w1c & 0xffu) + ((w1c >> 8) & 0xffu)) >> 2;
+              } else {
+                const float r0 = __fadd_rn(__fmul_rn((float)(w0c & 0xffu), lx0), __fmul_rn((float)((w0c >> 8) & 0xffu), lx1));
+                const float r1 = __fadd_rn(__fmul_rn((float)(w1c & 0xffu), lx0), __fmul_rn((float)((w1c >> 8) & 0xffu), lx1));
+                v[c] = (int)__fadd_rn(__fmul_rn(r0, by0), __fmul_rn(r1, by1));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const int s0 = (int)__dp2a_lo(a01, __byte_perm(lo0, hi0, sel[c]), 0u);
+              const int s1 = (int)__dp2a_lo(a01, __byte_perm(lo1, hi1, sel[c]), 0u);
+              v[c] = (flags & 1) ? ((s0 + s1 + 2) >> 2)
+                                 : ((((rd.b0 * (s0 >> 4)) >> 16) + ((rd.b1 * (s1 >> 4)) >> 16) + 2) >> 2);
+            }
           }
         }
         acc += (unsigned)(v[0] + v[1] + v[2]);
@@ -652,6 +680,7 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
   p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
   p.bgr = d->src_order == LVC_SRC_BGR;
+  p.f32src = d->src_float != 0 && !ptv;
   p.kh_shift = -1;
   for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
   // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)

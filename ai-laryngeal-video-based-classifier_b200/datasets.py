@@ -125,9 +125,13 @@ class VivitVideoDataset(_BaseDataset):
     """``VideoDataset(root_dir, mode='train', sampling_method='uniform', num_frames=32, logger=None)``."""
 
     def __init__(self, root_dir=None, mode="train", sampling_method="uniform", num_frames=32, logger=None,
-                 frame_source=None):
+                 frame_source=None, float_frames=False):
+        # float_frames=True reproduces the reference's PRIMARY branch (pytorchvideo decode -> float32 frames ->
+        # cv2.resize in float -> astype(uint8), vivit .../dataset.py:244-284); False its OpenCV fallback
+        # (uint8 frames, :317-350), which is also what the cv2-based ingest of this package decodes
         self.mode = mode
-        self._setup(root_dir, mode, sampling_method, num_frames, logger, frame_source, "dataset_u8")
+        self._setup(root_dir, mode, sampling_method, num_frames, logger, frame_source, "dataset_u8",
+                    float_frames=float_frames)
 
     def get_batch(self, indices):
         vids = [self.source.frames(i) for i in indices]

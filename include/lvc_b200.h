@@ -155,7 +155,10 @@ typedef struct {
   int32_t src_order;  /* LVC_SRC_RGB, or LVC_SRC_BGR: frames as cv2.VideoCapture.read() returns them; the
                          kernel's gather swaps the channels, replacing cv2.cvtColor(frame, COLOR_BGR2RGB)
                          (vivit .../dataset.py:336, resnet50-2d-lstm/inference.py:66) */
-  int32_t reserved;
+  int32_t src_float;  /* CV2 / CV2_PIL256 only.  1: resize like the reference's PRIMARY Dataset branch, where
+                         pytorchvideo hands over float32 frames (vivit .../dataset.py:244, :271-284): cv2.resize
+                         computes in float and `.astype(np.uint8)` truncates.  Differs from the uint8 path by
+                         0/+1 LSB on ~37 % of pixels.  Frames are still stored as uint8 (they hold integers). */
 } lvc_clip_desc;
 
 /* Replaces, for a batch of B videos: the gather (vivit .../dataset.py:246-268), the per-frame

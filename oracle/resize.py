@@ -155,3 +155,40 @@ def pil_resize_bilinear_u8(img, out_h, out_w):
     if out_h != img.shape[0]:
         out = _pil_pass(out, out_h, 0)
     return out.copy() if out is img else out
+
+
+def cv2_resize_linear_f32_trunc(img, out_h=224, out_w=224):
+    """a6, float-frame branch -- vivit .../dataset.py:244-284: pytorchvideo hands the Dataset float32
+    frames (0..255), ``cv2.resize(frame, (224, 224))`` then runs in FLOAT and ``.astype(np.uint8)``
+    truncates.  Restatement: tap = floor / fraction of ``(d + 0.5) * scale - 0.5`` kept in double until the
+    fraction's final cast to float32; per pass two float32 products and one add; column taps clamp with the
+    fraction reset, row taps clamp without (as in the uint8 path); an exact 2x2 down-scale is INTER_AREA
+    (mean of four).  PINNED LOOSELY: the installed opencv-python (4.13.0, IPP build; reference pins 4.11.0.86)
+    agrees to 1 float32 ulp before truncation, i.e. the uint8 result matches on > 99.5 % of pixels and never
+    differs by more than 1 LSB (tests/test_oracle_golden.py::test_cv2_float_branch)."""
+    img = np.asarray(img)
+    H, W = img.shape[:2]
+    f32 = np.float32
+    src = img.astype(f32)
+    if H == 2 * out_h and W == 2 * out_w:
+        m = (src[0::2, 0::2] + src[0::2, 1::2] + src[1::2, 0::2] + src[1::2, 1::2]) * f32(0.25)
+        return m.astype(np.uint8)
+
+    def taps(dst, n):
+        scale = 1.0 / (np.float64(dst) / np.float64(n))
+        f = (np.arange(dst, dtype=np.float64) + 0.5) * scale - 0.5
+        s = np.floor(f).astype(np.int64)
+        return s, (f - s).astype(f32)
+
+    sy, fy = taps(out_h, H)
+    sx, fx = taps(out_w, W)
+    lo, hi = sx < 0, sx >= W - 1
+    sx = np.where(lo, 0, np.where(hi, W - 1, sx))
+    fx = np.where(lo | hi, f32(0), fx).astype(f32)
+    x1 = np.minimum(sx + 1, W - 1)
+    a0, a1 = (f32(1) - fx).astype(f32), fx
+    y0, y1 = np.clip(sy, 0, H - 1), np.clip(sy + 1, 0, H - 1)
+    b0, b1 = (f32(1) - fy).astype(f32), fy
+    h = (src[:, sx] * a0[None, :, None]).astype(f32) + (src[:, x1] * a1[None, :, None]).astype(f32)
+    out = (h[y0] * b0[:, None, None]).astype(f32) + (h[y1] * b1[:, None, None]).astype(f32)
+    return out.astype(np.uint8)

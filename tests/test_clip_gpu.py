@@ -300,3 +300,33 @@ def test_swin_dataset_train_mode_draws_per_clip():
         want, params = op.ptv_train_chain(host[b][pick], seed=None)
         assert params == ds.last_aug[b]
         assert np.allclose(clips[b, 0].cpu().numpy(), want, atol=1.1e-2, rtol=1e-5)
+
+
+def test_float_frame_branch_of_cv2_resize():
+    """a6, primary Dataset branch (vivit .../dataset.py:244-284): float32 frames -> cv2.resize in float ->
+    truncation.  Kernel vs the oracle restatement: bit-exact; vs the installed cv2: within 1 LSB, > 99.5 % equal."""
+    import cv2
+
+    from lvc_b200 import ClipBuilder
+    from oracle.resize import cv2_resize_linear_f32_trunc
+
+    T = 3
+    host, dev = _videos([(101, 4, 720, 1280, "noise"), (102, 4, 480, 640, "ramp"), (103, 3, 100, 150, "noise"),
+                         (104, 3, 448, 448, "noise"), (105, 3, 224, 224, "noise"), (106, 3, 37, 1000, "noise")])
+    idx = [osm.dataset_indices("uniform", v.shape[0], T) for v in host]
+    out = ClipBuilder("dataset_u8", num_frames=T, float_frames=True)(dev, idx).cpu().numpy()
+    plain = ClipBuilder("dataset_u8", num_frames=T)(dev, idx).cpu().numpy()
+    for b, v in enumerate(host):
+        for t, fi in enumerate(idx[b]):
+            want = cv2_resize_linear_f32_trunc(v[fi])
+            assert np.array_equal(out[b, t], want), (b, t)
+            ref = cv2.resize(v[fi].astype(np.float32), (224, 224)).astype(np.uint8)
+            d = np.abs(ref.astype(np.int16) - out[b, t].astype(np.int16))
+            assert d.max() <= 1 and (d == 0).mean() > 0.995
+            assert np.abs(plain[b, t].astype(np.int16) - out[b, t].astype(np.int16)).max() <= 1
+    # the variant feeds every downstream stage unchanged (LUT normalisation here)
+    f = ClipBuilder("resnet_infer", num_frames=T, float_frames=True)(dev, idx).cpu().numpy()
+    want = op.manual_normalize(np.stack([cv2_resize_linear_f32_trunc(host[0][fi]) for fi in idx[0]]))
+    assert np.array_equal(f[0], want)
+    with pytest.raises(ValueError):
+        ClipBuilder("ptv_eval", num_frames=T, float_frames=True)

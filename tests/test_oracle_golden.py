@@ -114,3 +114,21 @@ def test_patch_embed_restatements(golden):
     assert np.allclose(y.numpy(), g["swin_out"], atol=5e-5)
     y = ope.swin_patch_embed(sd((1, 3, 3, 30, 29), 12), w, b, lw, lb)
     assert np.allclose(y.numpy(), g["swin_out_pad"], atol=5e-5)
+
+
+def test_cv2_float_branch():
+    """a6 float-frame branch (vivit .../dataset.py:244-284): cv2.resize on float32 frames + astype(uint8).
+    The installed OpenCV computes this in an IPP/SIMD path whose last-ulp behaviour is build-specific, so the
+    pin is: never more than 1 LSB apart, > 99.5 % of pixels identical (north_star: resized uint8 within 1 LSB)."""
+    import cv2
+
+    from oracle.resize import cv2_resize_linear_f32_trunc
+
+    rng = np.random.default_rng(0)
+    for (h, w) in [(720, 1280), (480, 640), (100, 150), (300, 200), (224, 224), (448, 448), (37, 1000)]:
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        ref = cv2.resize(img.astype(np.float32), (224, 224)).astype(np.uint8)
+        got = cv2_resize_linear_f32_trunc(img)
+        d = np.abs(ref.astype(np.int16) - got.astype(np.int16))
+        assert d.max() <= 1, (h, w)
+        assert (d == 0).mean() > 0.995, (h, w, float((d == 0).mean()))
