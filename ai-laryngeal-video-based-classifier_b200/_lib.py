@@ -76,6 +76,8 @@ _OPTIONAL_SIGS = {
     "lvc_patch_embed": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_patch_embed_launch_count": (C.c_int, [C.POINTER(EmbedDesc)]),
+    "lvc_embeddings_forward": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

@@ -308,6 +308,11 @@ struct GemmParams {
   const float* ln_b;
   float ln_eps;
   int do_ln, out_f32;
+  // fused embeddings epilogue: emb_mode 1 = VivitEmbeddings, 2 = TimesformerEmbeddings
+  const float* cls;    // [N]
+  const float* pos;    // [(1 + P)][N] position_embeddings
+  const float* temb;   // [T][N] time_embeddings (mode 2, may be NULL = space_only)
+  int emb_mode, emb_P, emb_T;
   const void* diag_a;  // A base pointer for the linear-copy experiment
   int diag;            // LVC_GEMM_DIAG (profiling only): 1 = no output stores, 2 = no MMAs, 4 = no TMA loads
   void* out;
@@ -558,6 +563,7 @@ __device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
 
 constexpr int kGemm2Threads = 320;  // producer warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
 
+template <bool EMB>  // EMB: fused cls / position / time embeddings epilogue (separate instantiation keeps the plain one lean)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemm2Threads, 1)
 lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                        const __grid_constant__ CUtensorMap map_o, const __grid_constant__ GemmParams p) {
@@ -598,6 +604,18 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  if (EMB && warp == 0) {
+    // row 0 of every batch entry: cls_token + position_embeddings[0] (time embeddings do not touch it)
+    const int rows_per_b = 1 + p.emb_P * (p.emb_mode == 2 ? p.emb_T : 1);
+    const int nb = p.M / (p.emb_P * (p.emb_mode == 2 ? p.emb_T : 1));
+    for (int bb = blockIdx.x; bb < nb; bb += gridDim.x)
+      for (int n = lane; n < p.N; n += 32) {
+        const float v = p.cls[n] + p.pos[n];
+        const size_t eo = (size_t)bb * rows_per_b * p.N + n;
+        if (p.out_f32) reinterpret_cast<float*>(p.out)[eo] = v;
+        else reinterpret_cast<__nv_bfloat16*>(p.out)[eo] = __float2bfloat16_rn(v);
+      }
+  }
   if (warp == 0) {
     // ===================== TMA producer (both CTAs; bytes are counted on the LEADER's full barrier) =====
     if (elect_one()) {
@@ -647,7 +665,8 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
     // the warp's swizzled staging tile and handed to the TMA store engine.
     const int q = warp & 3, half = (warp - 2) >> 2;
     const uint32_t leader_tmem_empty0 = mapa(s32(&tmem_empty[0]), 0);
-    const int cpf = p.out_f32 ? 32 : 64;      // columns per fill (128 bytes of output)
+    const bool f32_fill = p.out_f32 || EMB;   // the fused-embeddings epilogue stages fp32
+    const int cpf = f32_fill ? 32 : 64;      // columns per fill (128 bytes of staging)
     const int nfill = half_n / cpf;
     uint32_t local = 0;
     for (int u = pair; u < num_units; u += num_pairs, ++local) {
@@ -666,8 +685,33 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         if (lane == 0) mb_arrive_cluster(leader_tmem_empty0 + acc * 8u);
         continue;
       }
+      // fused embeddings: where this lane's token row goes and which table rows it adds
+      //   ViViT        m = b*P + tok            -> out row b*(1+P) + 1 + tok,        + pos[1 + tok]
+      //   TimeSformer  m = (b*T + t)*P + patch  -> out row b*(1+P*T) + 1 + patch*T + t, + pos[1 + patch] + time[t]
+      int e_out = -1, e_pos = 0, e_t = 0;
+      if (EMB) {
+        const int m = m_warp0 + lane;
+        if (m < p.M) {
+          const int fr = m / p.emb_P, tok = m - fr * p.emb_P;
+          e_pos = 1 + tok;
+          if (p.emb_mode == 1) e_out = fr * (1 + p.emb_P) + 1 + tok;
+          else { const int bb = fr / p.emb_T; e_t = fr - bb * p.emb_T; e_out = bb * (1 + p.emb_P * p.emb_T) + 1 + tok * p.emb_T + e_t; }
+        }
+      }
+      // coalesced pass geometry: 8 lanes cover the 128 bytes of a staged row, 4 rows per step, 8 steps
+      const int c4 = lane & 7;
+      int orow_[8], prow_[8], trow_[8];
+      if (EMB) {
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int r = itr * 4 + (lane >> 3);
+          orow_[itr] = __shfl_sync(0xffffffffu, e_out, r);
+          prow_[itr] = __shfl_sync(0xffffffffu, e_pos, r);
+          trow_[itr] = __shfl_sync(0xffffffffu, e_t, r);
+        }
+      }
       tmem_ld32_async(taddr, va);
-      if (!p.out_f32) tmem_ld32_async(taddr + 32, vb);
+      if (!f32_fill) tmem_ld32_async(taddr + 32, vb);
       for (int f = 0; f < nfill; ++f) {
         const int n0 = n_base + f * cpf;
         tmem_wait_dep(va);
@@ -676,7 +720,7 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
           const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0) + j4);
           va[4 * j4] += b4.x; va[4 * j4 + 1] += b4.y; va[4 * j4 + 2] += b4.z; va[4 * j4 + 3] += b4.w;
         }
-        if (p.out_f32) {
+        if (f32_fill) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) pk[j] = __float_as_uint(va[j]);
         } else {
@@ -691,21 +735,54 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
         }
         if (f + 1 < nfill) {   // next fill's accumulator columns travel while this one is stored
           tmem_ld32_async(taddr + (uint32_t)((f + 1) * cpf), va);
-          if (!p.out_f32) tmem_ld32_async(taddr + (uint32_t)((f + 1) * cpf + 32), vb);
+          if (!f32_fill) tmem_ld32_async(taddr + (uint32_t)((f + 1) * cpf + 32), vb);
         } else {               // accumulator fully read: hand the TMEM buffer back to the MMA issuer
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mb_arrive_cluster(leader_tmem_empty0 + acc * 8u);
         }
-        if (lane == 0) tma_store_wait_read();   // the previous store has finished reading the tile
+        if (!EMB && lane == 0) tma_store_wait_read();   // the previous store has finished reading the tile
         __syncwarp();
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) =
               make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        fence_async_smem();
+        if (!EMB) {
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0 && !(p.diag & 1)) tma_store_2d(&map_o, stg, n0, m_warp0);
+        } else {
+        // fused embeddings: coalesced pass over the staged fp32 tile; position (+ time) rows are added in fp32,
+        // rows scatter to their output slots.  All table loads of the pass are issued before the first use.
+        float4 pe_[8], te_[8];
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          pe_[itr] = make_float4(0.f, 0.f, 0.f, 0.f);
+          te_[itr] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (orow_[itr] >= 0) {
+            pe_[itr] = __ldg(reinterpret_cast<const float4*>(p.pos + (size_t)prow_[itr] * p.N + n0) + c4);
+            if (p.temb) te_[itr] = __ldg(reinterpret_cast<const float4*>(p.temb + (size_t)trow_[itr] * p.N + n0) + c4);
+          }
+        }
         __syncwarp();
-        if (lane == 0 && !(p.diag & 1)) tma_store_2d(&map_o, stg, n0, m_warp0);
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int r = itr * 4 + (lane >> 3);
+          if (orow_[itr] < 0) continue;
+          float4 z = *reinterpret_cast<const float4*>(stg + r * 128 + ((c4 ^ (r & 7)) << 4));
+          z.x += pe_[itr].x + te_[itr].x; z.y += pe_[itr].y + te_[itr].y;
+          z.z += pe_[itr].z + te_[itr].z; z.w += pe_[itr].w + te_[itr].w;
+          const size_t eo = (size_t)orow_[itr] * p.N + n0 + c4 * 4;
+          if (p.out_f32) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + eo) = z;
+          } else {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(z.x, z.y), hi = __floats2bfloat162_rn(z.z, z.w);
+            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + eo) =
+                make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+          }
+        }
+        __syncwarp();   // the tile is rewritten by the next fill
+        }
       }
     }
     if (lane == 0) tma_store_wait_all();
@@ -1020,8 +1097,33 @@ extern "C" int lvc_patch_embed_pack_weights(const lvc_embed_desc* d, const float
   return LVC_OK;
 }
 
+namespace {
+struct EmbTables { const float* cls; const float* pos; const float* temb; int mode; };
+int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packed, const float* bias,
+                     const float* ln_w, const float* ln_b, const EmbTables& et, void* out, void* workspace, void* stream);
+}  // namespace
+
 extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const void* w_packed, const float* bias,
                                const float* ln_w, const float* ln_b, void* out, void* workspace, void* stream) {
+  return patch_embed_impl(d, x, w_packed, bias, ln_w, ln_b, EmbTables{nullptr, nullptr, nullptr, 0}, out, workspace, stream);
+}
+
+extern "C" int lvc_embeddings_forward(const lvc_embed_desc* d, const void* x, const void* w_packed, const float* bias,
+                                      const float* cls_token, const float* position_embeddings,
+                                      const float* time_embeddings, void* out, void* workspace, void* stream) {
+  if (!d) return lvc_fail(LVC_E_INVAL, "embeddings_forward: NULL descriptor");
+  if (d->kind != LVC_EMBED_VIVIT && d->kind != LVC_EMBED_TIMESFORMER)
+    return lvc_fail(LVC_E_NOTSUP, "embeddings_forward: ViViT and TimeSformer only (Video Swin has no cls / position tables)");
+  if (!cls_token || !position_embeddings) return lvc_fail(LVC_E_INVAL, "embeddings_forward: NULL cls_token / position_embeddings");
+  if (d->kind == LVC_EMBED_VIVIT && time_embeddings) return lvc_fail(LVC_E_INVAL, "embeddings_forward: ViViT has no time embeddings");
+  return patch_embed_impl(d, x, w_packed, bias, nullptr, nullptr,
+                          EmbTables{cls_token, position_embeddings, time_embeddings, d->kind == LVC_EMBED_VIVIT ? 1 : 2},
+                          out, workspace, stream);
+}
+
+namespace {
+int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packed, const float* bias,
+                     const float* ln_w, const float* ln_b, const EmbTables& et, void* out, void* workspace, void* stream) {
   EmbedGeom g;
   int rc = make_geom(d, &g);
   if (rc != LVC_OK) return rc;
@@ -1086,6 +1188,11 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   p.out = out;
   p.diag = env_i("LVC_GEMM_DIAG", 0);
   p.diag_a = workspace;
+  p.cls = et.cls; p.pos = et.pos; p.temb = et.temb; p.emb_mode = et.mode;
+  p.emb_P = g.Ho * g.Wo * (et.mode == 1 ? g.To : 1);   // tokens per batch entry (ViViT) / per frame (TimeSformer)
+  p.emb_T = g.To;
+  if (et.mode && ((reinterpret_cast<uintptr_t>(et.pos) & 15) || (et.temb && (reinterpret_cast<uintptr_t>(et.temb) & 15))))
+    return lvc_fail(LVC_E_ALIGN, "embeddings_forward: position / time tables need 16-byte alignment");
   const int stage_bytes = (BM + p.BN) * p.BK * 2;
   const int fixed_bytes = 1024 + 2048 + (g.N + 2 * p.BN) * 4 + 16384;  // alignment, barriers, params, store staging
   // two CTAs per SM when TMEM (2 x <=256 columns) and shared memory allow: doubles the epilogue warps,
@@ -1103,6 +1210,7 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
 
   // tensor-bound shapes (no LayerNorm, 128B-swizzle K blocks, even tile split): CTA-pair kernel
   const bool two_cta = !p.do_ln && p.BK == 64 && p.BN % 128 == 0 && !getenv("LVC_GEMM_1CTA") && sms >= 2;
+  if (et.mode && !two_cta) return lvc_fail(LVC_E_NOTSUP, "embeddings_forward: needs K %% 64 == 0 and embed_dim %% 128 == 0");
   if (two_cta) {
     const int stage2 = (BM + p.BN / 2) * p.BK * 2;
     const int fixed2 = 1024 + 8 * 4096 + 512;  // alignment slack, 8 store tiles, barriers + TMEM slot
@@ -1117,9 +1225,14 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
     if (rc != LVC_OK) return rc;
     rc = make_out_map(&mo, out, (uint64_t)g.M, (uint64_t)g.N, p.out_f32 != 0);
     if (rc != LVC_OK) return rc;
-    LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     const int pairs = std::min(sms / 2, p.m_tiles * p.n_tiles);
-    lvc_embed_gemm2_kernel<<<2 * pairs, kGemm2Threads, smem2, st>>>(ma, mb, mo, p);
+    if (et.mode) {
+      LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      lvc_embed_gemm2_kernel<true><<<2 * pairs, kGemm2Threads, smem2, st>>>(ma, mb, mo, p);
+    } else {
+      LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      lvc_embed_gemm2_kernel<false><<<2 * pairs, kGemm2Threads, smem2, st>>>(ma, mb, mo, p);
+    }
     LVC_CUDA_TRY(cudaGetLastError());
     return LVC_OK;
   }
@@ -1161,3 +1274,4 @@ extern "C" int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const voi
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;
 }
+}  // namespace

@@ -47,7 +47,7 @@ class _EmbedBase(nn.Module):
         return _lib.EmbedDesc(self.kind, _DT[x.dtype], self.x_layout, _DT[self.out_dtype], B, T, H, W,
                               kt, kh, kw, conv.out_channels, float(self._ln()[2]), 0)
 
-    def forward_tokens(self, tokens, batch, frames, height=224, width=224):
+    def forward_tokens(self, tokens, batch, frames, height=224, width=224, emb=None, out_shape=None):
         """Embedding of a clip batch the fused clip kernel already wrote as the bf16 patch matrix
         ``A[M][K]`` (``ClipBuilder(..., layout="TOKENS", patch=(kt,kh,kw))``): no im2col pass, one
         launch.  Returns the flat ``(M, N)`` result; callers reshape to the module's output shape."""
@@ -55,9 +55,10 @@ class _EmbedBase(nn.Module):
         M = tokens.shape[0]
         if tokens.dtype != torch.bfloat16 or tokens.dim() != 2 or not tokens.is_contiguous():
             raise ValueError("tokens must be a contiguous bf16 (M, K) matrix")
-        return self._run(tokens, batch, frames, height, width, (M, conv.out_channels), layout=_lib.LAYOUT_TOKENS)
+        return self._run(tokens, batch, frames, height, width, out_shape or (M, conv.out_channels),
+                         layout=_lib.LAYOUT_TOKENS, emb=emb)
 
-    def _run(self, x, B, T, H, W, out_shape, layout=None):
+    def _run(self, x, B, T, H, W, out_shape, layout=None, emb=None):
         if not x.is_cuda:
             raise RuntimeError(f"{type(self).__name__}: input must be on a CUDA device (no CPU fallback)")
         if x.dtype not in _DT:
@@ -90,6 +91,16 @@ class _EmbedBase(nn.Module):
         if bias is None:
             bias = torch.zeros(conv.out_channels, device=x.device)
         lw, lb, _ = self._ln()
+        if emb is not None:  # fused cls / position / time embeddings
+            cls, pos, temb = (None if t is None else t.detach().float().contiguous().view(-1) for t in emb)
+            self._emb_keep = (cls, pos, temb)
+            st = lib.lvc_embeddings_forward(C.byref(d), x.data_ptr(), self._packed.data_ptr(),
+                                            bias.detach().float().contiguous().data_ptr(), cls.data_ptr(), pos.data_ptr(),
+                                            temb.data_ptr() if temb is not None else None, out.data_ptr(),
+                                            self._ws.data_ptr(), stream)
+            _lib.check(st, type(self).__name__)
+            self.launches += lib.lvc_patch_embed_launch_count(C.byref(d))
+            return out
         st = lib.lvc_patch_embed(C.byref(d), x.data_ptr(), self._packed.data_ptr(),
                                  bias.detach().float().contiguous().data_ptr(),
                                  lw.detach().float().contiguous().data_ptr() if lw is not None else None,
@@ -201,6 +212,65 @@ class PatchEmbed3d(_EmbedBase):
         kt, kh, kw = self.tuple_patch_size
         shape = (B, -(-T // kt), -(-H // kh), -(-W // kw), self.proj.out_channels)
         return self._run(x, B, T, H, W, shape)
+
+
+class VivitEmbeddings(nn.Module):
+    """``transformers`` ``VivitEmbeddings`` (modeling_vivit.py:141-155): tubelet embedding, cls token and position
+    embeddings, produced by ONE GEMM launch whose epilogue adds the tables and writes the (B, 1 + tokens, hidden)
+    layout.  Parameter names match the HF module (``cls_token``, ``position_embeddings``, ``patch_embeddings.*``)."""
+
+    def __init__(self, config=None, out_dtype=torch.bfloat16, **kw):
+        super().__init__()
+        self.patch_embeddings = VivitTubeletEmbeddings(config, out_dtype=out_dtype, **kw)
+        E, P = self.patch_embeddings.embed_dim, self.patch_embeddings.num_patches
+        self.cls_token = nn.Parameter(torch.zeros(1, 1, E))
+        self.position_embeddings = nn.Parameter(torch.zeros(1, P + 1, E))
+
+    @torch.no_grad()
+    def forward(self, pixel_values=None, interpolate_pos_encoding=False, tokens=None, batch=None):
+        pe = self.patch_embeddings
+        if interpolate_pos_encoding:
+            raise NotImplementedError("interpolate_pos_encoding is not fused; sizes must match the config")
+        emb = (self.cls_token, self.position_embeddings, None)
+        if tokens is not None:  # bf16 patch matrix written by the clip kernel (layout="TOKENS")
+            P = pe.num_patches
+            return pe.forward_tokens(tokens, batch, pe.num_frames, emb=emb, out_shape=(batch, 1 + P, pe.embed_dim))
+        B, T, Cc, H, W = pixel_values.shape
+        if H != pe.image_size[0] or W != pe.image_size[1] or T != pe.num_frames:
+            raise ValueError(f"Input ({T}x{H}*{W}) doesn't match model ({pe.num_frames}x{pe.image_size[0]}*{pe.image_size[1]}).")
+        return pe._run(pixel_values, B, T, H, W, (B, 1 + pe.num_patches, pe.embed_dim), emb=emb)
+
+
+class TimesformerEmbeddings(nn.Module):
+    """``transformers`` ``TimesformerEmbeddings`` (modeling_timesformer.py:70-144) for matching sizes: patch
+    embedding, cls token, position embeddings, time embeddings and the (B, patch*T + t) token order, fused into
+    the GEMM epilogue.  ``attention_type='space_only'`` is not supported (its output keeps the (B*T, 197, E) shape)."""
+
+    def __init__(self, config=None, out_dtype=torch.bfloat16, num_frames=8, attention_type="divided_space_time", **kw):
+        super().__init__()
+        self.patch_embeddings = TimesformerPatchEmbeddings(config, out_dtype=out_dtype, **kw)
+        E = self.patch_embeddings.projection.out_channels
+        self.num_patches = self.patch_embeddings.num_patches
+        self.num_frames = getattr(config, "num_frames", num_frames) if config is not None else num_frames
+        self.attention_type = getattr(config, "attention_type", attention_type) if config is not None else attention_type
+        if self.attention_type == "space_only":
+            raise NotImplementedError("space_only attention keeps per-frame cls rows; not fused")
+        self.cls_token = nn.Parameter(torch.zeros(1, 1, E))
+        self.position_embeddings = nn.Parameter(torch.zeros(1, self.num_patches + 1, E))
+        self.time_embeddings = nn.Parameter(torch.zeros(1, self.num_frames, E))
+
+    @torch.no_grad()
+    def forward(self, pixel_values=None, tokens=None, batch=None):
+        pe = self.patch_embeddings
+        E = pe.projection.out_channels
+        emb = (self.cls_token, self.position_embeddings, self.time_embeddings)
+        if tokens is not None:
+            return pe.forward_tokens(tokens, batch, self.num_frames, emb=emb,
+                                     out_shape=(batch, 1 + self.num_patches * self.num_frames, E))
+        B, T, Cc, H, W = pixel_values.shape
+        if (H, W) != tuple(pe.image_size) or T != self.num_frames:
+            raise ValueError("input size does not match the position / time tables (resizing is not fused)")
+        return pe._run(pixel_values, B, T, H, W, (B, 1 + self.num_patches * T, E), emb=emb)
 
 
 def smoke():

@@ -307,6 +307,30 @@ def run_secondary(dev, iters=10):
         else:
             ent["gemm_roofline"] = {"bound": "tensor", "achieved": flops / gemm_ms / 1e9, "peak": tf_peak, "unit": "TFLOP/s",
                                     "frac": flops / gemm_ms / 1e9 / tf_peak}
+        if c["embed"] in ("vivit", "timesformer"):
+            # row f3: cls + position (+ time) embeddings fused into the GEMM epilogue vs the same step done
+            # with torch ops after the plain GEMM (cat / add / permute = extra passes over the 38 MB output)
+            B, T = c["videos"], c["T"]
+            if c["embed"] == "vivit":
+                me = pe.VivitEmbeddings().to(dev)
+                P = me.patch_embeddings.num_patches
+
+                def unfused():
+                    e = m.forward_tokens(tok, B, T).view(B, P, -1)
+                    return torch.cat((me.cls_token.to(e.dtype).expand(B, -1, -1), e), 1) + me.position_embeddings.to(e.dtype)
+            else:
+                me = pe.TimesformerEmbeddings(num_frames=T).to(dev)
+                P = me.num_patches
+
+                def unfused():
+                    e = m.forward_tokens(tok, B, T).view(B * T, P, -1)
+                    e = torch.cat((me.cls_token.to(e.dtype).expand(B * T, -1, -1), e), 1) + me.position_embeddings.to(e.dtype)
+                    cls = e[:B, 0:1]
+                    e = e[:, 1:].reshape(B, T, P, -1).permute(0, 2, 1, 3).reshape(B * P, T, -1) + me.time_embeddings.to(e.dtype)
+                    return torch.cat((cls, e.reshape(B, P * T, -1)), 1)
+            ent["embeddings_fused_ms"] = timed(lambda: me(tokens=tok, batch=B), True)
+            ent["embeddings_unfused_torch_ms"] = timed(unfused, True)
+            del me
         out[name] = ent
         del vids, batch, tok, m
         torch.cuda.empty_cache()

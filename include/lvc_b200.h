@@ -226,6 +226,19 @@ int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const void* w_packed
                     void* workspace, void* stream);
 int lvc_patch_embed_launch_count(const lvc_embed_desc* d);
 
+/* The step after the patch embedding, fused into the GEMM epilogue:
+ *   VIVIT        VivitEmbeddings.forward (transformers modeling_vivit.py:141-155): cat(cls_token, patches) +
+ *                position_embeddings -> out (B, 1 + T/2*14*14, E)
+ *   TIMESFORMER  TimesformerEmbeddings.forward (modeling_timesformer.py:92-144): cat(cls, patches) +
+ *                position_embeddings, then + time_embeddings per frame and the (B, patch*T + t) token order of
+ *                divided space-time attention -> out (B, 1 + 196*T, E); time_embeddings = NULL is "space_only"
+ *                ((B*T, 197, E) is NOT produced: the cls row of each batch entry is written once).
+ * Tables are fp32 device pointers: cls_token [E], position_embeddings [(1 + tokens)][E], time_embeddings [T][E].
+ * Dropout layers are identity (inference / p = 0, the configs' default).  Other arguments as lvc_patch_embed. */
+int lvc_embeddings_forward(const lvc_embed_desc* d, const void* x, const void* w_packed_bf16, const float* bias,
+                           const float* cls_token, const float* position_embeddings,
+                           const float* time_embeddings, void* out, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

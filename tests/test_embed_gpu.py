@@ -159,3 +159,83 @@ def test_fused_token_layout_skips_im2col(preset, kind):
     got = m.forward_tokens(tokens, len(host), T)
     assert m.launches - launches == 1
     assert torch.equal(got.reshape(want.shape), want)
+
+
+# ------------------------------------------------------------------ row f3: fused embeddings epilogue ----
+def _fill(params, seed0, scale=0.02):
+    for k, t in enumerate(params):
+        t.data.copy_(sd(t.shape, seed0 + k, scale))
+
+
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_vivit_embeddings_match_hf_module(out_dtype):
+    """VivitEmbeddings (modeling_vivit.py:141-155): cls token + position embeddings fused into the GEMM epilogue.
+    Oracle = the HF module itself (fp32, CPU) with the same state dict."""
+    from transformers import VivitConfig
+    from transformers.models.vivit.modeling_vivit import VivitEmbeddings as HF
+
+    from lvc_b200.patch_embed import VivitEmbeddings
+
+    cfg = VivitConfig(num_frames=8, hidden_dropout_prob=0.0)
+    ref = HF(cfg).eval()
+    _fill(list(ref.parameters()), 20)
+    mine = VivitEmbeddings(cfg, out_dtype=out_dtype)
+    missing = mine.load_state_dict(ref.state_dict(), strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    mine = mine.cuda()
+    x = sd((3, 8, 3, 224, 224), 5)
+    with torch.no_grad():
+        want = ref(x)
+    y = mine(x.cuda())
+    assert y.dtype == out_dtype and tuple(y.shape) == tuple(want.shape) == (3, 1 + 4 * 196, 768)
+    check(y, want)
+    # the cls row is cls_token + position_embeddings[0], identical for every batch entry
+    c = (ref.cls_token[0, 0] + ref.position_embeddings[0, 0]).detach()
+    assert torch.allclose(y[:, 0].float().cpu(), c.expand(3, -1), atol=2e-2 if out_dtype == torch.bfloat16 else 1e-6)
+
+
+def test_timesformer_embeddings_match_hf_module():
+    """TimesformerEmbeddings (modeling_timesformer.py:92-144), divided space-time: position + time embeddings and the
+    (B, patch*T + t) token order are produced by the GEMM epilogue's scatter."""
+    from transformers import TimesformerConfig
+    from transformers.models.timesformer.modeling_timesformer import TimesformerEmbeddings as HF
+
+    from lvc_b200.patch_embed import TimesformerEmbeddings
+
+    cfg = TimesformerConfig(num_frames=8, hidden_dropout_prob=0.0)
+    ref = HF(cfg).eval()
+    _fill(list(ref.parameters()), 40)
+    mine = TimesformerEmbeddings(cfg, out_dtype=torch.float32)
+    mine.load_state_dict(ref.state_dict(), strict=True)
+    mine = mine.cuda()
+    x = sd((5, 8, 3, 224, 224), 6)   # 5*8*196 = 7840 rows: the last 256-row pair tile is ragged
+    with torch.no_grad():
+        want = ref(x)
+    y = mine(x.cuda())
+    assert tuple(y.shape) == tuple(want.shape) == (5, 1 + 196 * 8, 768)
+    check(y, want)
+    with pytest.raises(ValueError):
+        mine(sd((1, 4, 3, 224, 224), 7).cuda())
+
+
+def test_fused_clip_to_embeddings_pipeline():
+    """clip kernel (token layout) -> one GEMM launch with the embeddings epilogue == module applied to the
+    normalised clip tensor."""
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.patch_embed import VivitEmbeddings
+    from lvc_b200.synth import synth_video
+    from oracle import samplers as osm
+
+    T = 8
+    host = [synth_video(31 + i, 12, 240, 320) for i in range(2)]
+    dev = [torch.from_numpy(v).cuda() for v in host]
+    idx = [osm.dataset_indices("uniform", 12, T) for _ in host]
+    m = VivitEmbeddings(num_frames=T, out_dtype=torch.float32)
+    _fill(list(m.parameters()), 60)
+    m = m.cuda()
+    clip = ClipBuilder("vivit", num_frames=T)(dev, idx)                      # (B,T,3,224,224) fp32
+    tok = ClipBuilder("vivit", num_frames=T, layout="TOKENS", patch=(2, 16, 16))(dev, idx)
+    a = m(clip)
+    b = m(tokens=tok, batch=2)
+    assert tuple(a.shape) == tuple(b.shape) == (2, 1 + 4 * 196, 768)
+    check(b, a.float().cpu())
