@@ -36,6 +36,11 @@ class ClipDesc(C.Structure):
                 ("mean", C.c_float * 3), ("std", C.c_float * 3), ("src_order", C.c_int32), ("src_float", C.c_int32)]
 
 
+class LetterboxGeom(C.Structure):
+    _fields_ = [("src_h", C.c_int32), ("src_w", C.c_int32), ("new_h", C.c_int32), ("new_w", C.c_int32),
+                ("top", C.c_int32), ("left", C.c_int32), ("out_h", C.c_int32), ("out_w", C.c_int32)]
+
+
 class EmbedDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("x_dtype", C.c_int32), ("x_layout", C.c_int32),
                 ("out_dtype", C.c_int32), ("batch", C.c_int32), ("frames", C.c_int32),
@@ -76,6 +81,12 @@ _OPTIONAL_SIGS = {
     "lvc_patch_embed": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_patch_embed_launch_count": (C.c_int, [C.POINTER(EmbedDesc)]),
+    "lvc_letterbox_geometry": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                         C.POINTER(LetterboxGeom)]),
+    "lvc_letterbox_forward": (C.c_int, [C.POINTER(LetterboxGeom), C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "lvc_scale_boxes": (C.c_int, [C.POINTER(LetterboxGeom), C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "lvc_best_boxes": (C.c_int, [C.POINTER(LetterboxGeom), C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float,
+                                 C.c_void_p, C.c_void_p]),
     "lvc_embeddings_forward": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

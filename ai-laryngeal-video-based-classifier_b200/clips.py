@@ -119,6 +119,13 @@ class ClipBuilder:
     def _tables(self, videos, indices, boxes, aug=None):
         B, T = len(videos), self.num_frames
         idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int32).reshape(B, T))
+        # boxes already on the device (yolo.best_boxes): consumed in place, no host round trip
+        dev_boxes = boxes if (torch.is_tensor(boxes) and boxes.is_cuda) else None
+        if dev_boxes is not None:
+            if dev_boxes.dtype != torch.int32 or dev_boxes.numel() != B * T * 4 or not dev_boxes.is_contiguous() \
+                    or dev_boxes.data_ptr() % 16:
+                raise ValueError("device boxes must be a contiguous, 16-byte aligned int32 (B, T, 4) tensor")
+            boxes = None
         nb = 0 if boxes is None else B * T * 16
         vt_bytes = B * C.sizeof(_lib.Video)
         off_idx = (vt_bytes + 15) // 16 * 16
@@ -150,7 +157,9 @@ class ClipBuilder:
         dev = host.to(self.device, non_blocking=True)
         p = dev.data_ptr()
         self._p_aug = p + off_aug if aug is not None else None
-        return dev, host, p, p + off_idx, (p + off_box if boxes is not None else None), max_w
+        self._dev_boxes = dev_boxes
+        p_box = dev_boxes.data_ptr() if dev_boxes is not None else (p + off_box if boxes is not None else None)
+        return dev, host, p, p + off_idx, p_box, max_w
 
     def prepare(self, videos, indices, boxes=None, aug=None):
         """Upload the per-batch tables (video descriptors, indices, boxes, augmentation draws: a few KB,
@@ -166,6 +175,7 @@ class ClipBuilder:
         cb = ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
                        _shape(self.layout, B, T, patch=self.patch))
         cb.p_aug = self._p_aug
+        cb.dev_boxes = self._dev_boxes  # keeps the table alive
         return cb
 
     def run(self, batch, out=None, stats=None):

@@ -1,0 +1,231 @@
+// Detector pre- and post-processing around the (out-of-scope) YOLOv5 network, SURVEY.md 8f.4:
+//   letterbox 640 + BGR->RGB + /255 + CHW      src/yolo_detector.py:52-61
+//   scale_boxes(...).round() + int()           src/yolo_detector.py:76-81
+//   highest-confidence box per frame           src/yolo_detector.py:161 (the reference gates on max confidence)
+// so that ROI boxes are produced and consumed on the device: the int32 rows these kernels write are rows of
+// lvc_clip_forward's `boxes` table.  yolov5's letterbox / scale_boxes are restated from the published
+// ultralytics/yolov5 definitions (utils/augmentations.py, utils/general.py): the reference's yolov5/ submodule
+// is empty and unpinned.  Byte / integer work, HBM-bound: no tensor cores.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+
+#include "lvc_internal.h"
+
+namespace {
+
+constexpr int kLbThreads = 256;
+constexpr int kLbRows = 8;        // output rows per block
+constexpr int kLbMaxW = 4096;     // widest resize target the tap table holds
+
+struct XTap { int off; int a01; };  // byte offset of the left pixel; a0 | a1 << 16; bit 31 of off: right tap clamps
+
+// OpenCV INTER_LINEAR table set-up (cv::resize, 8-bit): fx = (float)((d+0.5)*scale - 0.5) in double without
+// contraction, floor / fraction in float, 11-bit coefficients.
+__device__ __forceinline__ void cv_tap(int d, double scale, int& s, float& fr) {
+  const float f = (float)__dadd_rn(__dmul_rn((double)d + 0.5, scale), -0.5);
+  const float fl = floorf(f);
+  s = (int)fl;
+  fr = __fsub_rn(f, fl);
+}
+__device__ __forceinline__ double cv_scale(int src, int dst) { return __ddiv_rn(1.0, __ddiv_rn((double)dst, (double)src)); }
+__device__ __forceinline__ int coef(float w) { return __float2int_rn(__fmul_rn(w, 2048.0f)); }
+
+struct LbParams {
+  lvc_letterbox_geom g;
+  const uint8_t* frames;
+  void* out;
+  int n, out_bf16;
+};
+
+__global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_constant__ LbParams p) {
+  __shared__ XTap xt[kLbMaxW];
+  const lvc_letterbox_geom& g = p.g;
+  const bool area = g.src_w == 2 * g.new_w && g.src_h == 2 * g.new_h;   // cv::resize switches to INTER_AREA
+  const double sx_scale = cv_scale(g.src_w, g.new_w), sy_scale = cv_scale(g.src_h, g.new_h);
+  for (int x = threadIdx.x; x < g.new_w; x += kLbThreads) {
+    XTap t;
+    if (area) { t.off = 6 * x; t.a01 = 1 | (1 << 16); }
+    else {
+      int sx; float fr;
+      cv_tap(x, sx_scale, sx, fr);
+      if (sx < 0) { sx = 0; fr = 0.f; }
+      if (sx >= g.src_w - 1) { sx = g.src_w - 1; fr = 0.f; }
+      t.off = 3 * sx | ((sx + 1 <= g.src_w - 1) ? 0 : (1 << 31));
+      t.a01 = coef(__fsub_rn(1.0f, fr)) | (coef(fr) << 16);
+    }
+    xt[x] = t;
+  }
+  __syncthreads();
+  const int frame = blockIdx.y;
+  const uint8_t* src = p.frames + (size_t)frame * g.src_h * g.src_w * 3;
+  const size_t plane = (size_t)g.out_h * g.out_w;
+  const float pad = __fdiv_rn(114.0f, 255.0f);
+  for (int r = 0; r < kLbRows; ++r) {
+    const int oy = blockIdx.x * kLbRows + r;
+    if (oy >= g.out_h) break;
+    const int iy = oy - g.top;
+    const bool row_in = iy >= 0 && iy < g.new_h;
+    int y0 = 0, y1 = 0, b0 = 0, b1 = 0;
+    if (row_in) {
+      if (area) { y0 = 2 * iy; y1 = 2 * iy + 1; }
+      else {
+        int sy; float fr;
+        cv_tap(iy, sy_scale, sy, fr);
+        y0 = min(max(sy, 0), g.src_h - 1);
+        y1 = min(max(sy + 1, 0), g.src_h - 1);
+        b0 = coef(__fsub_rn(1.0f, fr));   // cv::resize does not reset the fraction of clamped ROWS
+        b1 = coef(fr);
+      }
+    }
+    const uint8_t* r0 = src + (size_t)y0 * g.src_w * 3;
+    const uint8_t* r1 = src + (size_t)y1 * g.src_w * 3;
+    for (int ox = threadIdx.x; ox < g.out_w; ox += kLbThreads) {
+      const int ix = ox - g.left;
+      float v[3] = {pad, pad, pad};
+      if (row_in && ix >= 0 && ix < g.new_w) {
+        const XTap t = xt[ix];
+        const int off = t.off & 0x7fffffff, d1 = (t.off < 0) ? 0 : 3;
+        const int a0 = t.a01 & 0xffff, a1 = t.a01 >> 16;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const int s0 = a0 * __ldg(r0 + off + c) + a1 * __ldg(r0 + off + d1 + c);
+          const int s1 = a0 * __ldg(r1 + off + c) + a1 * __ldg(r1 + off + d1 + c);
+          const int u = area ? ((s0 + s1 + 2) >> 2) : ((((b0 * (s0 >> 4)) >> 16) + ((b1 * (s1 >> 4)) >> 16) + 2) >> 2);
+          v[c] = __fdiv_rn((float)u, 255.0f);
+        }
+      }
+      // transpose(2,0,1)[::-1]: output channel k is input channel 2 - k
+      const size_t e = (size_t)frame * 3 * plane + (size_t)oy * g.out_w + ox;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (p.out_bf16) reinterpret_cast<__nv_bfloat16*>(p.out)[e + k * plane] = __float2bfloat16_rn(v[2 - k]);
+        else __stcs(reinterpret_cast<float*>(p.out) + e + k * plane, v[2 - k]);
+      }
+    }
+  }
+}
+
+// yolov5 scale_boxes: gain and pad in double (python floats), applied to float32 box coordinates; clip; round
+// half to even; int().
+struct BoxScale { float gain, pad_x, pad_y; int w, h; };
+BoxScale box_scale(const lvc_letterbox_geom& g) {
+  const double gain = std::fmin((double)g.out_h / (double)g.src_h, (double)g.out_w / (double)g.src_w);
+  BoxScale b;
+  b.gain = (float)gain;
+  b.pad_x = (float)(((double)g.out_w - (double)g.src_w * gain) / 2.0);
+  b.pad_y = (float)(((double)g.out_h - (double)g.src_h * gain) / 2.0);
+  b.w = g.src_w; b.h = g.src_h;
+  return b;
+}
+__device__ __forceinline__ int4 scale_one(const float* d, const BoxScale& s) {
+  const float x1 = __fdiv_rn(__fsub_rn(d[0], s.pad_x), s.gain), y1 = __fdiv_rn(__fsub_rn(d[1], s.pad_y), s.gain);
+  const float x2 = __fdiv_rn(__fsub_rn(d[2], s.pad_x), s.gain), y2 = __fdiv_rn(__fsub_rn(d[3], s.pad_y), s.gain);
+  return make_int4((int)rintf(fminf(fmaxf(x1, 0.f), (float)s.w)), (int)rintf(fminf(fmaxf(y1, 0.f), (float)s.h)),
+                   (int)rintf(fminf(fmaxf(x2, 0.f), (float)s.w)), (int)rintf(fminf(fmaxf(y2, 0.f), (float)s.h)));
+}
+
+__global__ void lvc_scale_boxes_kernel(const float* __restrict__ det, int n, int row_stride, BoxScale s, int4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = scale_one(det + (size_t)i * row_stride, s);
+}
+
+// One block per frame: arg-max of the confidence over the frame's detections (ties: lowest row index).
+__global__ void __launch_bounds__(128) lvc_best_boxes_kernel(const float* __restrict__ det, const int32_t* __restrict__ frame_of,
+                                                            int n_det, float conf_thres, BoxScale s, int4* __restrict__ out) {
+  __shared__ float s_conf[128];
+  __shared__ int s_idx[128];
+  const int frame = blockIdx.x;
+  float best = -1.f;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < n_det; i += blockDim.x) {
+    if (frame_of[i] != frame) continue;
+    const float c = det[(size_t)i * 6 + 4];
+    if (c >= conf_thres && (c > best || (c == best && i < bi))) { best = c; bi = i; }
+  }
+  s_conf[threadIdx.x] = best; s_idx[threadIdx.x] = bi;
+  __syncthreads();
+  for (int o = 64; o; o >>= 1) {
+    if (threadIdx.x < o) {
+      const float c = s_conf[threadIdx.x + o];
+      const int j = s_idx[threadIdx.x + o];
+      if (c > s_conf[threadIdx.x] || (c == s_conf[threadIdx.x] && j < s_idx[threadIdx.x])) { s_conf[threadIdx.x] = c; s_idx[threadIdx.x] = j; }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0)
+    out[frame] = s_conf[0] >= 0.f ? scale_one(det + (size_t)s_idx[0] * 6, s) : make_int4(-1, -1, -1, -1);
+}
+
+int check_geom(const lvc_letterbox_geom* g, const char* who) {
+  if (!g) return lvc_fail(LVC_E_INVAL, "%s: NULL geometry", who);
+  if (g->src_h <= 0 || g->src_w <= 0 || g->new_h <= 0 || g->new_w <= 0 || g->top < 0 || g->left < 0 ||
+      g->out_h < g->top + g->new_h || g->out_w < g->left + g->new_w)
+    return lvc_fail(LVC_E_INVAL, "%s: inconsistent letterbox geometry (use lvc_letterbox_geometry)", who);
+  return LVC_OK;
+}
+
+}  // namespace
+
+extern "C" int lvc_letterbox_geometry(int32_t src_h, int32_t src_w, int32_t shape_h, int32_t shape_w, int32_t stride,
+                                      int32_t auto_pad, int32_t scaleup, lvc_letterbox_geom* out) {
+  if (!out) return lvc_fail(LVC_E_INVAL, "letterbox_geometry: NULL output");
+  if (src_h <= 0 || src_w <= 0 || shape_h <= 0 || shape_w <= 0 || stride <= 0)
+    return lvc_fail(LVC_E_INVAL, "letterbox_geometry: extents and stride must be positive");
+  // python: r = min(new_shape[0] / shape[0], new_shape[1] / shape[1]); new_unpad = int(round(shape[1] * r)), ...
+  double r = std::fmin((double)shape_h / (double)src_h, (double)shape_w / (double)src_w);
+  if (!scaleup) r = std::fmin(r, 1.0);
+  const int new_w = (int)std::nearbyint((double)src_w * r), new_h = (int)std::nearbyint((double)src_h * r);
+  if (new_w <= 0 || new_h <= 0) return lvc_fail(LVC_E_SHAPE, "letterbox_geometry: frame collapses to zero size");
+  int dw = shape_w - new_w, dh = shape_h - new_h;
+  if (auto_pad) { dw %= stride; dh %= stride; }   // np.mod: minimum rectangle
+  const double hw = dw / 2.0, hh = dh / 2.0;
+  const int top = (int)std::nearbyint(hh - 0.1), bottom = (int)std::nearbyint(hh + 0.1);
+  const int left = (int)std::nearbyint(hw - 0.1), right = (int)std::nearbyint(hw + 0.1);
+  out->src_h = src_h; out->src_w = src_w; out->new_h = new_h; out->new_w = new_w;
+  out->top = top; out->left = left; out->out_h = new_h + top + bottom; out->out_w = new_w + left + right;
+  return LVC_OK;
+}
+
+extern "C" int lvc_letterbox_forward(const lvc_letterbox_geom* g, const uint8_t* frames, int32_t n, int32_t out_dtype,
+                                     void* out, void* stream) {
+  int rc = check_geom(g, "letterbox_forward");
+  if (rc != LVC_OK) return rc;
+  if (!frames || !out) return lvc_fail(LVC_E_INVAL, "letterbox_forward: NULL pointer");
+  if (n <= 0 || n > 65535) return lvc_fail(LVC_E_INVAL, "letterbox_forward: 1..65535 frames per call");
+  if (out_dtype != LVC_DT_F32 && out_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "letterbox_forward: out_dtype must be f32 or bf16");
+  if (g->new_w > kLbMaxW) return lvc_fail(LVC_E_SHAPE, "letterbox_forward: resize target wider than %d", kLbMaxW);
+  LbParams p;
+  p.g = *g; p.frames = frames; p.out = out; p.n = n; p.out_bf16 = out_dtype == LVC_DT_BF16;
+  dim3 grid((g->out_h + kLbRows - 1) / kLbRows, n);
+  lvc_letterbox_kernel<<<grid, kLbThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}
+
+extern "C" int lvc_scale_boxes(const lvc_letterbox_geom* g, const float* det, int32_t n, int32_t row_stride,
+                               int32_t* boxes_out, void* stream) {
+  int rc = check_geom(g, "scale_boxes");
+  if (rc != LVC_OK) return rc;
+  if (n == 0) return LVC_OK;
+  if (!det || !boxes_out || n < 0 || row_stride < 4) return lvc_fail(LVC_E_INVAL, "scale_boxes: bad argument");
+  if (reinterpret_cast<uintptr_t>(boxes_out) & 15) return lvc_fail(LVC_E_ALIGN, "scale_boxes: boxes_out must be 16-byte aligned");
+  lvc_scale_boxes_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(det, n, row_stride, box_scale(*g),
+                                                                                      reinterpret_cast<int4*>(boxes_out));
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}
+
+extern "C" int lvc_best_boxes(const lvc_letterbox_geom* g, const float* det, const int32_t* frame_of, int32_t n_det,
+                              int32_t n_frames, float conf_thres, int32_t* boxes_out, void* stream) {
+  int rc = check_geom(g, "best_boxes");
+  if (rc != LVC_OK) return rc;
+  if (n_frames <= 0 || n_det < 0 || !boxes_out || (n_det > 0 && (!det || !frame_of))) return lvc_fail(LVC_E_INVAL, "best_boxes: bad argument");
+  if (reinterpret_cast<uintptr_t>(boxes_out) & 15) return lvc_fail(LVC_E_ALIGN, "best_boxes: boxes_out must be 16-byte aligned");
+  lvc_best_boxes_kernel<<<n_frames, 128, 0, static_cast<cudaStream_t>(stream)>>>(det, frame_of, n_det, conf_thres, box_scale(*g),
+                                                                                reinterpret_cast<int4*>(boxes_out));
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
+}

@@ -239,6 +239,38 @@ int lvc_embeddings_forward(const lvc_embed_desc* d, const void* x, const void* w
                            const float* cls_token, const float* position_embeddings,
                            const float* time_embeddings, void* out, void* workspace, void* stream);
 
+/* --------------------------------------------- detector pre / post-processing ---- */
+
+/* Geometry of yolov5 `letterbox(im, new_shape, stride=stride)` with its defaults auto=True, scaleFill=False,
+ * scaleup=True (src/yolo_detector.py:52; ultralytics/yolov5 utils/augmentations.py -- an un-vendored, unpinned
+ * submodule of the reference: restated from its published definition). */
+typedef struct {
+  int32_t src_h, src_w;   /* decoded frame */
+  int32_t new_h, new_w;   /* cv2.resize target: round(src * r), r = min(shape_h / src_h, shape_w / src_w) */
+  int32_t top, left;      /* border before the image: round(d/2 - 0.1) */
+  int32_t out_h, out_w;   /* network input: new + top + bottom, new + left + right (multiples of stride when auto) */
+} lvc_letterbox_geom;
+int lvc_letterbox_geometry(int32_t src_h, int32_t src_w, int32_t shape_h, int32_t shape_w, int32_t stride,
+                           int32_t auto_pad, int32_t scaleup, lvc_letterbox_geom* out);
+/* src/yolo_detector.py:52-61 for n frames in one launch: cv2.resize(INTER_LINEAR, bit-exact uint8) to
+ * (new_w, new_h), constant border 114, HWC->CHW with the channel order REVERSED (`transpose(2,0,1)[::-1]`: the
+ * reference feeds BGR frames, the network sees RGB), float(x) / 255.
+ *   frames  device  uint8 (n, src_h, src_w, 3);  out  device  (n, 3, out_h, out_w) of out_dtype (F32 or BF16) */
+int lvc_letterbox_forward(const lvc_letterbox_geom* g, const uint8_t* frames, int32_t n, int32_t out_dtype,
+                          void* out, void* stream);
+/* src/yolo_detector.py:76: `scale_boxes(im.shape[2:], det[:, :4], im0.shape).round()` (yolov5 utils/general.py:
+ * subtract the letterbox pad, divide by the gain, clip to the frame) followed by the int() of :81.
+ *   det  device  float rows of `row_stride` floats starting with xyxy (yolov5 NMS output rows are xyxy,conf,cls);
+ *   boxes_out  device  int32 [n][4] -- directly usable as rows of lvc_clip_forward's `boxes` table. */
+int lvc_scale_boxes(const lvc_letterbox_geom* g, const float* det, int32_t n, int32_t row_stride,
+                    int32_t* boxes_out, void* stream);
+/* Per frame, the highest-confidence detection becomes the frame's ROI (the reference gates on max confidence,
+ * src/yolo_detector.py:161); frames without a detection >= conf_thres get x1 = -1 (= full frame).
+ *   det  device  float [n_det][6] xyxy,conf,cls in letterboxed coordinates; frame_of  device int32 [n_det];
+ *   boxes_out  device int32 [n_frames][4], written completely. */
+int lvc_best_boxes(const lvc_letterbox_geom* g, const float* det, const int32_t* frame_of, int32_t n_det,
+                   int32_t n_frames, float conf_thres, int32_t* boxes_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
