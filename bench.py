@@ -409,8 +409,14 @@ def main():
         cores = cbm.host_cores()
         per = max(1, int(round(160 / cores)))  # ~10-20 s of CPU work in total
         v = cbm.run(wl["h"], wl["w"], wl["frames"], wl["T"], cores, per, repeats=3)
+        # the same recipe three ways -- one process, the reference's DataLoader-style 4 workers
+        # (vivit_transformer/main.py:49), all host cores (the headline `value`)
+        v1 = cbm.run(wl["h"], wl["w"], wl["frames"], wl["T"], 1, 6, repeats=3)
+        v4 = cbm.run(wl["h"], wl["w"], wl["frames"], wl["T"], min(4, cores), 6, repeats=3)
         line["cpu_baseline"] = {"value": v, "unit": "clips/s", "cores": cores, "kind": "port",
-                                "sample": f"{cores} single-thread workers x {per} clip(s), median of 3 (cv2.resize + /255 + mean/std + permute)"}
+                                "sample": f"{cores} single-thread workers x {per} clip(s), median of 3 (cv2.resize + /255 + mean/std + permute)",
+                                "ways": {"1_process_1_thread": v1, "4_workers": v4, "all_cores": v,
+                                         "os_cpu_count": os.cpu_count()}}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
