@@ -398,7 +398,7 @@ def main():
                     "steps": r["e2e_steps"], "path": "pinned host frames read by the fused kernel over PCIe (zero-copy, tapped rows only) -> clips in HBM -> D2H checksums"},
             "gpu_launches": r["launches"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                         "traffic": traffic, "peak_source": src, "kernel": "lvc_clip_cv2_kernel",
+                         "traffic": traffic, "peak_source": src, "kernel": "lvc_clip_kernel<MODE_CV2>",
                          "algorithmic_bytes_per_launch": frames * bpf, "kernel_ms": launch_s * 1e3},
             "per_rank": [[float(v) for v in g.tolist()] for g in gathered]}
     if world == 1 and not args.no_secondary:
