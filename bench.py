@@ -154,6 +154,8 @@ def run_b200(args, wl):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL's own banner / debug lines go to stderr: stdout carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     B, N, H, W, T = wl["videos"], wl["frames"], wl["h"], wl["w"], wl["T"]
 
