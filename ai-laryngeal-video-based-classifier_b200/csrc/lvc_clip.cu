@@ -41,7 +41,7 @@ struct StageHdr {
   int ox;         // PTV: first source column held in the row slots
   int nw;         // PTV: width of the short-side-scaled image
   int left;       // PTV: centre-crop offset in the scaled image
-  int pad;
+  int rlo;        // VIVIT bands: first resized row held in the intermediate buffer (nw = first row the NEXT band owns)
   RowDesc rows[kMaxRPS];
 };
 enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
@@ -57,6 +57,8 @@ struct ClipParams {
   int T;
   int layout, out_dtype;
   int bands, rows_per_band;  // bands per frame, output rows per band
+  int v_stages;              // VIVIT: stages per band (resized rows incl. the Pillow halo, rounded up to rps)
+  int ring_off;              // byte offset of the source-row ring in shared memory
   int total_items;           // B*T*bands
   int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
   float mean[3], std[3];     // PTV normalisation
@@ -134,7 +136,7 @@ __device__ __forceinline__ int coef(float w) { return __float2int_rn(__fmul_rn(w
 namespace {
 
 // Shared memory map: [0,256) full/empty mbarriers | StageHdr[kMaxStages] | LUT 3x256 f32 |
-// (MODE_VIVIT: Pillow tap table, 2x2 row buffers, 224x672 intermediate frame) | ring.
+// (MODE_VIVIT: Pillow tap table, 2x2 row buffers, intermediate rows of one band x 672 B) | ring.
 constexpr int kHdrOff = 256;
 constexpr int kLutOff = kHdrOff + kMaxStages * (int)sizeof(StageHdr);
 constexpr int kAuxOff = (kLutOff + 3 * 256 * 4 + 127) / 128 * 128;
@@ -142,8 +144,6 @@ constexpr int kRowBytes = S * 3;                    // one resized RGB row
 constexpr int kVivitTapOff = kAuxOff;               // int4[224]: ymin, k0, k1, k2
 constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][672]
 constexpr int kVivitInterOff = kVivitRowBufOff + kGroups * 2 * kRowBytes;
-constexpr int kVivitEnd = (kVivitInterOff + S * kRowBytes + 127) / 128 * 128;
-__host__ __device__ constexpr int ring_off(int mode) { return mode == MODE_VIVIT ? kVivitEnd : kAuxOff; }
 
 // Pillow BILINEAR 224 -> 256 taps for cropped output coordinate d (source coordinate d + 16 of the
 // 256-wide image): precompute_coeffs + normalize_coeffs_8bpc in double, support 1 (up-scale).
@@ -245,11 +245,11 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   uint64_t* empty = full + kMaxStages;
   StageHdr* hdrs = reinterpret_cast<StageHdr*>(smem + kHdrOff);
   float* lut = reinterpret_cast<float*>(smem + kLutOff);
-  uint8_t* ring = smem + ring_off(MODE);
+  uint8_t* ring = smem + p.ring_off;
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const int stages_per_item = p.rows_per_band / p.rps;
+  const int stages_per_item = MODE == MODE_VIVIT ? p.v_stages : p.rows_per_band / p.rps;
 
   if (tid == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -307,6 +307,15 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           sh = min(max(bx.w, oy + 1), v.height) - oy;
         }
       }
+      // VIVIT bands: output rows [band*R, band*R+R) of the cropped Pillow image need the resized rows
+      // [rlo, rhi] (Pillow's vertical window, 2-3 taps); the band OWNS (checksums) rows [rlo, next band's rlo)
+      int rlo = 0, own_hi = S;
+      if (MODE == MODE_VIVIT) {
+        const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
+        rlo = vt[band * p.rows_per_band].x;
+        if (band + 1 < p.bands) own_hi = vt[(band + 1) * p.rows_per_band].x;
+        else own_hi = vt[S - 1].x + (vt[S - 1].w ? 3 : 2);   // one past the last resized row the crop reads
+      }
       const bool area = MODE != MODE_PTV && (sw == 2 * S) && (sh == 2 * S);
       const double scale_y = cv_scale(sh);
       const uint64_t row_bytes = (uint64_t)v.width * 3u;
@@ -315,7 +324,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       for (int st = 0; st < stages_per_item; ++st, ++it) {
         const int slot = it % p.stages;
         const uint32_t phase = (it / p.stages) & 1u;
-        const int oy_first = band * p.rows_per_band + st * p.rps;
+        const int oy_first = MODE == MODE_VIVIT ? rlo + st * p.rps : band * p.rows_per_band + st * p.rps;
         if (lane == 0) mbar_wait(&empty[slot], phase ^ 1u);
         __syncwarp();
         uint32_t my_bytes = 0, bulk_bytes = 0;
@@ -324,7 +333,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         bool leader = false;
         uint8_t* stage_base = ring + (size_t)slot * nrows * p.pitch;
         if (lane < nrows) {
-          const int r = lane >> 1, oyr = oy_first + r;
+          const int r = lane >> 1, oyr = min(oy_first + r, S - 1);   // VIVIT halo stages may run past the last row
           int ysrc;
           if (MODE == MODE_PTV) {
             int y0, y1; float l0, l1;
@@ -366,7 +375,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
         if (lane == 0) {
           h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first; h->flags = (area ? 1 : 0) | (flip << 1);
-          h->ox = ox; h->nw = nw; h->left = left;
+          h->ox = ox; h->nw = (MODE == MODE_VIVIT) ? own_hi : nw; h->left = left; h->rlo = rlo;
         }
         if (leader && bulk_bytes < my_bytes) {
           // last bytes of the buffer: not a whole 16-byte granule, copy them by hand
@@ -517,7 +526,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             }
           }
         }
-        acc += (unsigned)(v[0] + v[1] + v[2]);
+        if (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw)) acc += (unsigned)(v[0] + v[1] + v[2]);  // bands: owned rows only
         if (MODE == MODE_VIVIT) {
           // Pillow horizontal pass of this row (224 -> cropped 224 of 256), rounded to uint8
           uint8_t* rb = smem + kVivitRowBufOff + (g * 2 + parity) * kRowBytes;
@@ -530,7 +539,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           for (int c = 0; c < 3; ++c) {
             int ss = (1 << 21) + tp[c] * hx.y + tp[3 + c] * hx.z;
             if (hx.w) ss += tp[6 + c] * hx.w;
-            inter[oyr * kRowBytes + x * 3 + c] = (uint8_t)clip8(ss >> 22);
+            inter[(oyr - h->rlo) * kRowBytes + x * 3 + c] = (uint8_t)clip8(ss >> 22);
           }
           continue;
         }
@@ -555,11 +564,12 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       // the whole frame went through the horizontal pass: Pillow vertical pass + LUT + store
       consumers_bar();
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
-      for (int y = g; y < S; y += kGroups) {
+      const int band = item % p.bands, ylo = band * p.rows_per_band, rlo = vt[ylo].x;
+      for (int y = ylo + g; y < ylo + p.rows_per_band; y += kGroups) {
         const size_t cstride = fo.cstride;
         const size_t eoff = row_offset(p, fo, y) + xoff;
         const int4 ty = vt[y];
-        const uint8_t* tp = inter + ty.x * kRowBytes + x * 3;
+        const uint8_t* tp = inter + (ty.x - rlo) * kRowBytes + x * 3;
         int v[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
@@ -687,13 +697,33 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
   // 8 output rows per stage amortise the per-stage bookkeeping when the row slots are small enough
   // to keep >= 3 stages in flight; wide sources (1080p) use 4 rows per stage and a deeper ring
+  // MODE_VIVIT: the Pillow stage needs its vertical window on chip.  A band of R output rows spans at most
+  // floor((R-1)*7/8) + 4 resized rows (halo included); pick the band count that minimises rounds x rows per
+  // item (whole frames when the batch is large enough that quantisation does not matter).  Fewer rows in
+  // the intermediate buffer also leave more shared memory for the source-row ring.
+  int v_nb = 1, v_res = S;
+  if (mode == MODE_VIVIT) {
+    static const int kVB[] = {1, 2, 4, 7, 8, 14};
+    const long long nframes = (long long)d->batch * d->num_frames;
+    const int forced_nb = env_int("LVC_CLIP_VBANDS", 0);
+    long long best_cost = -1;
+    for (int nb : kVB) {
+      const int R = S / nb;
+      const int res = ((R - 1) * 7) / 8 + 4;   // nb == 1: rows 13..210, the crop never reads the rest
+      const long long rounds = (nframes * nb + di.sms - 1) / di.sms;
+      const long long cost = rounds * ((res + 7) / 8 * 8 + R / 2 + 6);   // resize rows + Pillow vertical rows + per-item fixed
+      if (forced_nb ? nb == forced_nb : (best_cost < 0 || cost < best_cost)) { best_cost = cost; v_nb = nb; v_res = res; }
+    }
+  }
+  const int ring_base = mode == MODE_VIVIT ? (kVivitInterOff + (v_res + 7) / 8 * 8 * kRowBytes + 127) / 128 * 128 : kAuxOff;
+  p.ring_off = ring_base;
   p.rps = env_int("LVC_CLIP_RPS", 0);
   if (p.rps == 0) {
-    const int budget0 = std::min(di.max_smem, 200 * 1024) - ring_off(mode);
+    const int budget0 = std::min(di.max_smem, 200 * 1024) - ring_base;
     p.rps = (budget0 / (16 * p.pitch) >= 3) ? 8 : 4;
   }
   if (p.rps < kGroups || p.rps > kMaxRPS || (p.rps % kGroups) || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
-  const int fixed = ring_off(mode);
+  const int fixed = ring_base;
   const int smem_budget = std::min(di.max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, fixed + 64 * 1024));
   int stage_bytes = 2 * p.rps * p.pitch;
   while ((smem_budget - fixed) / stage_bytes < 2 && p.rps > kGroups) {
@@ -716,8 +746,8 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
     if (rb % p.rps) continue;
     if (forced ? rb == forced : (int64_t)frames * (S / rb) >= 8LL * grid_max) { p.rows_per_band = rb; break; }
   }
-  if (mode == MODE_VIVIT) p.rows_per_band = S;  // the Pillow stage needs the whole frame on chip
   p.bands = S / p.rows_per_band;
+  if (mode == MODE_VIVIT) { p.bands = v_nb; p.rows_per_band = S / v_nb; p.v_stages = (v_res + p.rps - 1) / p.rps; }
   p.total_items = frames * p.bands;
   const int grid = std::min(p.total_items, grid_max);
   cudaStream_t st = static_cast<cudaStream_t>(stream);

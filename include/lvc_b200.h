@@ -171,7 +171,8 @@ typedef struct {
  *                    no detection = full frame; NULL = no ROI
  *   lut      device  float[3*256] from lvc_build_lut (ignored for PTV_EVAL / U8 output)
  *   out      device  B*T*3*224*224 elements of out_dtype in `layout`
- *   stats    device  uint64[B] or NULL: += sum of the clip's resized uint8 samples (checksum)
+ *   stats    device  uint64[B] or NULL: += sum of the clip's resized uint8 samples (checksum); for
+ *                    LVC_RESAMPLE_CV2_PIL256 the samples of the resized rows the 224-crop reads (13..210)
  */
 int lvc_clip_forward(const lvc_clip_desc* desc, const lvc_video* videos, const int32_t* indices,
                      const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
