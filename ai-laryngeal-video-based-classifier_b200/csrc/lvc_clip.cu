@@ -140,9 +140,9 @@ namespace {
 constexpr int kHdrOff = 256;
 constexpr int kLutOff = kHdrOff + kMaxStages * (int)sizeof(StageHdr);
 constexpr int kAuxOff = (kLutOff + 3 * 256 * 4 + 127) / 128 * 128;
-constexpr int kRowBytes = S * 3;                    // one resized RGB row
+constexpr int kRowBytes = S * 4;                    // one resized row, a 32-bit word (R | G<<8 | B<<16) per pixel
 constexpr int kVivitTapOff = kAuxOff;               // int4[224]: ymin, k0, k1, k2
-constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][672]
+constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][224 words]
 constexpr int kVivitInterOff = kVivitRowBufOff + kGroups * 2 * kRowBytes;
 
 // Pillow BILINEAR 224 -> 256 taps for cropped output coordinate d (source coordinate d + 16 of the
@@ -529,18 +529,20 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         if (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw)) acc += (unsigned)(v[0] + v[1] + v[2]);  // bands: owned rows only
         if (MODE == MODE_VIVIT) {
           // Pillow horizontal pass of this row (224 -> cropped 224 of 256), rounded to uint8
-          uint8_t* rb = smem + kVivitRowBufOff + (g * 2 + parity) * kRowBytes;
+          // (one word per pixel: a store and up to three loads per thread instead of 3 + 9 byte accesses)
+          uint32_t* rb = reinterpret_cast<uint32_t*>(smem + kVivitRowBufOff + (g * 2 + parity) * kRowBytes);
           parity ^= 1;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) rb[x * 3 + c] = (uint8_t)v[c];
+          rb[x] = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16);
           group_bar(g);
-          const uint8_t* tp = rb + hx.x * 3;
+          const uint32_t w0 = rb[hx.x], w1 = rb[hx.x + 1], w2 = hx.w ? rb[hx.x + 2] : 0u;
+          uint32_t packed = 0;
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
-            int ss = (1 << 21) + tp[c] * hx.y + tp[3 + c] * hx.z;
-            if (hx.w) ss += tp[6 + c] * hx.w;
-            inter[(oyr - h->rlo) * kRowBytes + x * 3 + c] = (uint8_t)clip8(ss >> 22);
+            const int ss = (1 << 21) + (int)((w0 >> (8 * c)) & 0xffu) * hx.y + (int)((w1 >> (8 * c)) & 0xffu) * hx.z +
+                           (int)((w2 >> (8 * c)) & 0xffu) * hx.w;
+            packed |= (uint32_t)clip8(ss >> 22) << (8 * c);
           }
+          reinterpret_cast<uint32_t*>(inter)[(oyr - h->rlo) * S + x] = packed;
           continue;
         }
         if (p.out_dtype == LVC_DT_F32) {
@@ -569,12 +571,13 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         const size_t cstride = fo.cstride;
         const size_t eoff = row_offset(p, fo, y) + xoff;
         const int4 ty = vt[y];
-        const uint8_t* tp = inter + (ty.x - rlo) * kRowBytes + x * 3;
+        const uint32_t* tp = reinterpret_cast<const uint32_t*>(inter) + (ty.x - rlo) * S + x;
+        const uint32_t w0 = tp[0], w1 = tp[S], w2 = ty.w ? tp[2 * S] : 0u;
         int v[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          int ss = (1 << 21) + tp[c] * ty.y + tp[kRowBytes + c] * ty.z;
-          if (ty.w) ss += tp[2 * kRowBytes + c] * ty.w;
+          const int ss = (1 << 21) + (int)((w0 >> (8 * c)) & 0xffu) * ty.y + (int)((w1 >> (8 * c)) & 0xffu) * ty.z +
+                         (int)((w2 >> (8 * c)) & 0xffu) * ty.w;
           v[c] = clip8(ss >> 22);
         }
         if (p.out_dtype == LVC_DT_F32) {

@@ -1,0 +1,18 @@
+"""Bounded randomised parity sweep (scripts/fuzz_parity.py): random frame sizes, out-of-range indices, ROI boxes that
+stick out of the frame, all presets, RGB / BGR sources -- every case bit-exact against the oracle (float chain within
+the tolerance of tests/test_clip_gpu.py)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_randomised_parity_sweep():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_parity.py"), "40", "7"], capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "40/40 cases match" in r.stdout
