@@ -16,3 +16,12 @@ def test_randomised_parity_sweep():
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "40/40 cases match" in r.stdout
+
+
+def test_randomised_embed_sweep():
+    """Ragged token counts (partial 128/256-row tiles), both dtypes, plain and fused-embeddings epilogues."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_embed.py"), "24", "11"], capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "24/24 cases match" in r.stdout
