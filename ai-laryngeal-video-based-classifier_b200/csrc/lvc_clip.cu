@@ -189,6 +189,9 @@ __device__ __forceinline__ void ptv_geom(int H, int W, int size, int& nh, int& n
   else { nh = size; nw = (int)floor(__dmul_rn(__ddiv_rn((double)W, (double)H), (double)size)); }
 }
 __device__ __forceinline__ int center_crop_origin(int n) { return (int)rint((double)(n - S) / 2.0); }
+__device__ __forceinline__ void ring_next(int& slot, uint32_t& phase, int stages) {
+  if (++slot == stages) { slot = 0; phase ^= 1u; }
+}
 __device__ __forceinline__ void group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(2 + g), "r"(S) : "memory");
 }
@@ -227,10 +230,10 @@ __device__ __forceinline__ FrameOut frame_out(const ClipParams& p, int f, int b,
   return o;
 }
 __device__ __forceinline__ size_t row_offset(const ClipParams& p, const FrameOut& o, int y) {
-  if (p.layout != LVC_LAYOUT_TOKENS) return o.base + (size_t)y * o.rowmul;
+  if (p.layout != LVC_LAYOUT_TOKENS) return o.base + (size_t)((unsigned)y * o.rowmul);   // < 2^32: one IMAD.WIDE
   const unsigned ho = p.kh_shift >= 0 ? ((unsigned)y >> p.kh_shift) : ((unsigned)y / (unsigned)p.kh);
   const unsigned dy = (unsigned)y - ho * p.kh;
-  return o.base + (size_t)ho * o.rowmul + dy * p.kw;
+  return o.base + (size_t)(ho * o.rowmul + dy * (unsigned)p.kw);
 }
 __device__ __forceinline__ size_t col_offset(const ClipParams& p, int x) {
   if (p.layout == LVC_LAYOUT_BTHWC) return (size_t)x * 3;
@@ -269,7 +272,8 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
     const uint64_t policy = policy_evict_first();
     const int nrows = 2 * p.rps;
     const unsigned lanes = nrows >= 32 ? 0xffffffffu : ((1u << nrows) - 1u);
-    uint32_t it = 0;
+    int slot = 0;          // ring position and phase advance incrementally (no per-stage div / mod)
+    uint32_t phase = 0;
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       const int f = item / p.bands, band = item - f * p.bands;
       const int b = f / p.T;
@@ -321,9 +325,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       const uint64_t row_bytes = (uint64_t)v.width * 3u;
       const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
       const uint64_t buf_end = v.base + (uint64_t)v.nbytes;
-      for (int st = 0; st < stages_per_item; ++st, ++it) {
-        const int slot = it % p.stages;
-        const uint32_t phase = (it / p.stages) & 1u;
+      for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
         const int oy_first = MODE == MODE_VIVIT ? rlo + st * p.rps : band * p.rows_per_band + st * p.rps;
         if (lane == 0) mbar_wait(&empty[slot], phase ^ 1u);
         __syncwarp();
@@ -404,7 +406,8 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   float lx0 = 0.f, lx1 = 0.f;
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
   int acc_b = -1;
-  uint32_t it = 0;
+  int slot = 0;
+  uint32_t phase = 0;
   const size_t xoff = col_offset(p, x);
   // MODE_VIVIT state: Pillow horizontal taps of this thread's column, row-buffer parity
   int4 hx = make_int4(0, 0, 0, 0);
@@ -414,9 +417,8 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     int f = 0;
-    for (int st = 0; st < stages_per_item; ++st, ++it) {
-      const int slot = it % p.stages;
-      mbar_wait(&full[slot], (it / p.stages) & 1u);
+    for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
+      mbar_wait(&full[slot], phase);
       const StageHdr* h = &hdrs[slot];
       const int sw = h->sw, flags = h->flags, oy0 = h->oy0;
       f = h->frame;
