@@ -239,3 +239,26 @@ def test_fused_clip_to_embeddings_pipeline():
     b = m(tokens=tok, batch=2)
     assert tuple(a.shape) == tuple(b.shape) == (2, 1 + 4 * 196, 768)
     check(b, a.float().cpu())
+
+
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_vivit_embeddings_16_frames_ragged_last_tile(out_dtype):
+    """num_frames = 16, B = 3: 4704 token rows leave a ragged last 256-row pair tile; rows of one warp stay inside
+    one batch entry (1568 tokens per clip is a multiple of 32) while 128-row CTA tiles straddle entries."""
+    from transformers import VivitConfig
+    from transformers.models.vivit.modeling_vivit import VivitEmbeddings as HF
+
+    from lvc_b200.patch_embed import VivitEmbeddings
+
+    cfg = VivitConfig(num_frames=16, hidden_dropout_prob=0.0)
+    ref = HF(cfg).eval()
+    _fill(list(ref.parameters()), 80)
+    mine = VivitEmbeddings(cfg, out_dtype=out_dtype)
+    mine.load_state_dict(ref.state_dict(), strict=True)
+    mine = mine.cuda()
+    x = sd((3, 16, 3, 224, 224), 9)
+    with torch.no_grad():
+        want = ref(x)
+    y = mine(x.cuda())
+    assert tuple(y.shape) == tuple(want.shape) == (3, 1 + 8 * 196, 768)
+    check(y, want)
