@@ -17,8 +17,9 @@
 namespace {
 
 constexpr int kLbThreads = 256;
-constexpr int kLbRows = 8;        // output rows per block
+constexpr int kLbRows = 16;       // output rows per block
 constexpr int kLbMaxW = 4096;     // widest resize target the tap table holds
+constexpr int kLbUnroll = 3;      // pixels per thread and pass (768 columns per pass)
 
 struct XTap { int off; int a01; };  // byte offset of the left pixel; a0 | a1 << 16; bit 31 of off: right tap clamps
 
@@ -58,51 +59,91 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
     }
     xt[x] = t;
   }
-  __syncthreads();
-  const int frame = blockIdx.y;
-  const uint8_t* src = p.frames + (size_t)frame * g.src_h * g.src_w * 3;
-  const size_t plane = (size_t)g.out_h * g.out_w;
-  const float pad = __fdiv_rn(114.0f, 255.0f);
-  for (int r = 0; r < kLbRows; ++r) {
-    const int oy = blockIdx.x * kLbRows + r;
-    if (oy >= g.out_h) break;
-    const int iy = oy - g.top;
-    const bool row_in = iy >= 0 && iy < g.new_h;
-    int y0 = 0, y1 = 0, b0 = 0, b1 = 0;
-    if (row_in) {
-      if (area) { y0 = 2 * iy; y1 = 2 * iy + 1; }
+  // x / 255 for every uint8 value (IEEE division = what torch's CPU `im /= 255` computes), once per block
+  __shared__ float s_div[256];
+  __shared__ int4 s_row[kLbRows];   // y0, y1, b0, b1 of the block's rows (y0 < 0: border row)
+  for (int i = threadIdx.x; i < 256; i += kLbThreads) s_div[i] = __fdiv_rn((float)i, 255.0f);
+  if (threadIdx.x < kLbRows) {
+    const int iy = blockIdx.x * kLbRows + threadIdx.x - g.top;
+    int4 rt = make_int4(-1, 0, 0, 0);
+    if (iy >= 0 && iy < g.new_h) {
+      if (area) rt = make_int4(2 * iy, 2 * iy + 1, 0, 0);
       else {
         int sy; float fr;
         cv_tap(iy, sy_scale, sy, fr);
-        y0 = min(max(sy, 0), g.src_h - 1);
-        y1 = min(max(sy + 1, 0), g.src_h - 1);
-        b0 = coef(__fsub_rn(1.0f, fr));   // cv::resize does not reset the fraction of clamped ROWS
-        b1 = coef(fr);
+        // cv::resize does not reset the fraction of clamped ROWS
+        rt = make_int4(min(max(sy, 0), g.src_h - 1), min(max(sy + 1, 0), g.src_h - 1), coef(__fsub_rn(1.0f, fr)), coef(fr));
       }
     }
+    s_row[threadIdx.x] = rt;
+  }
+  __syncthreads();
+  const int frame = blockIdx.y;
+  const uint8_t* src = p.frames + (size_t)frame * g.src_h * g.src_w * 3;
+  const uint8_t* frames_end = p.frames + (size_t)p.n * g.src_h * g.src_w * 3;
+  const size_t plane = (size_t)g.out_h * g.out_w;
+  const float pad = s_div[114];
+  for (int r = 0; r < kLbRows; ++r) {
+    const int oy = blockIdx.x * kLbRows + r;
+    if (oy >= g.out_h) break;
+    const int4 rt = s_row[r];
+    const bool row_in = rt.x >= 0;
+    const int y0 = max(rt.x, 0), y1 = rt.y, b0 = rt.z, b1 = rt.w;
     const uint8_t* r0 = src + (size_t)y0 * g.src_w * 3;
     const uint8_t* r1 = src + (size_t)y1 * g.src_w * 3;
-    for (int ox = threadIdx.x; ox < g.out_w; ox += kLbThreads) {
-      const int ix = ox - g.left;
-      float v[3] = {pad, pad, pad};
-      if (row_in && ix >= 0 && ix < g.new_w) {
+    // kLbUnroll pixels per thread and pass: all source words are requested before the first one is used, so
+    // a thread keeps up to 18 loads in flight (the kernel is latency-bound otherwise)
+    for (int ox0 = threadIdx.x; ox0 < g.out_w; ox0 += kLbThreads * kLbUnroll) {
+      uint32_t lo0[kLbUnroll], hi0[kLbUnroll], lo1[kLbUnroll], hi1[kLbUnroll], a01[kLbUnroll];
+      bool in[kLbUnroll];
+#pragma unroll
+      for (int u = 0; u < kLbUnroll; ++u) {
+        const int ox = ox0 + u * kLbThreads, ix = ox - g.left;
+        in[u] = row_in && ox < g.out_w && ix >= 0 && ix < g.new_w;
+        lo0[u] = hi0[u] = lo1[u] = hi1[u] = a01[u] = 0u;
+        if (!in[u]) continue;
         const XTap t = xt[ix];
         const int off = t.off & 0x7fffffff, d1 = (t.off < 0) ? 0 : 3;
-        const int a0 = t.a01 & 0xffff, a1 = t.a01 >> 16;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const int s0 = a0 * __ldg(r0 + off + c) + a1 * __ldg(r0 + off + d1 + c);
-          const int s1 = a0 * __ldg(r1 + off + c) + a1 * __ldg(r1 + off + d1 + c);
-          const int u = area ? ((s0 + s1 + 2) >> 2) : ((((b0 * (s0 >> 4)) >> 16) + ((b1 * (s1 >> 4)) >> 16) + 2) >> 2);
-          v[c] = __fdiv_rn((float)u, 255.0f);
+        a01[u] = (uint32_t)t.a01;
+        const uint8_t* q0 = r0 + off;
+        const uint8_t* q1 = r1 + off;
+        if (d1 == 3 && q0 + 12 <= frames_end && q1 + 12 <= frames_end) {
+          // 6 bytes (2 pixels x 3 channels) per row from three aligned 32-bit loads and a funnel shift
+          const uint32_t sh0 = ((uint32_t)(uintptr_t)q0 & 3u) * 8u, sh1 = ((uint32_t)(uintptr_t)q1 & 3u) * 8u;
+          const uint32_t* w0 = reinterpret_cast<const uint32_t*>((uintptr_t)q0 & ~(uintptr_t)3);
+          const uint32_t* w1 = reinterpret_cast<const uint32_t*>((uintptr_t)q1 & ~(uintptr_t)3);
+          const uint32_t a = __ldg(w0), bq = __ldg(w0 + 1), cq = __ldg(w0 + 2), d = __ldg(w1), e = __ldg(w1 + 1), fq = __ldg(w1 + 2);
+          lo0[u] = __funnelshift_r(a, bq, sh0); hi0[u] = __funnelshift_r(bq, cq, sh0);
+          lo1[u] = __funnelshift_r(d, e, sh1); hi1[u] = __funnelshift_r(e, fq, sh1);
+        } else {   // clamped right edge or the last bytes of the buffer: byte loads into the same layout
+          lo0[u] = __ldg(q0) | (__ldg(q0 + 1) << 8) | (__ldg(q0 + 2) << 16) | (__ldg(q0 + d1) << 24);
+          hi0[u] = __ldg(q0 + d1 + 1) | (__ldg(q0 + d1 + 2) << 8);
+          lo1[u] = __ldg(q1) | (__ldg(q1 + 1) << 8) | (__ldg(q1 + 2) << 16) | (__ldg(q1 + d1) << 24);
+          hi1[u] = __ldg(q1 + d1 + 1) | (__ldg(q1 + d1 + 2) << 8);
         }
       }
-      // transpose(2,0,1)[::-1]: output channel k is input channel 2 - k
-      const size_t e = (size_t)frame * 3 * plane + (size_t)oy * g.out_w + ox;
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        if (p.out_bf16) reinterpret_cast<__nv_bfloat16*>(p.out)[e + k * plane] = __float2bfloat16_rn(v[2 - k]);
-        else __stcs(reinterpret_cast<float*>(p.out) + e + k * plane, v[2 - k]);
+      for (int u = 0; u < kLbUnroll; ++u) {
+        const int ox = ox0 + u * kLbThreads;
+        if (ox >= g.out_w) continue;
+        float v[3] = {pad, pad, pad};
+        if (in[u]) {
+          const uint32_t sel[3] = {0x4430u, 0x4441u, 0x4452u};   // (c of pixel 0, c of pixel 1) of the 8 bytes
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const int s0 = (int)__dp2a_lo(a01[u], __byte_perm(lo0[u], hi0[u], sel[c]), 0u);
+            const int s1 = (int)__dp2a_lo(a01[u], __byte_perm(lo1[u], hi1[u], sel[c]), 0u);
+            const int uu = area ? ((s0 + s1 + 2) >> 2) : ((((b0 * (s0 >> 4)) >> 16) + ((b1 * (s1 >> 4)) >> 16) + 2) >> 2);
+            v[c] = s_div[uu];
+          }
+        }
+        // transpose(2,0,1)[::-1]: output channel k is input channel 2 - k
+        const size_t e = (size_t)frame * 3 * plane + (size_t)oy * g.out_w + ox;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          if (p.out_bf16) reinterpret_cast<__nv_bfloat16*>(p.out)[e + k * plane] = __float2bfloat16_rn(v[2 - k]);
+          else __stcs(reinterpret_cast<float*>(p.out) + e + k * plane, v[2 - k]);
+        }
       }
     }
   }

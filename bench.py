@@ -154,9 +154,19 @@ def run_b200(args, wl):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # NCCL's own banner / debug lines go to stderr: stdout carries exactly one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout at communicator creation: point fd 1 at stderr while the
+        # communicator comes up, so stdout carries exactly one JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     B, N, H, W, T = wl["videos"], wl["frames"], wl["h"], wl["w"], wl["T"]
 
     # ---- synthetic decoded frames: video v of the job = seed 1000+v, sharded v -> rank (v mod world)
