@@ -415,6 +415,21 @@ def main():
             "per_rank": [[float(v) for v in g.tolist()] for g in gathered]}
     if world == 1 and not args.no_secondary:
         line["secondary"] = run_secondary(torch.device("cuda", local))
+        if not args.no_cpu_baseline:
+            # the reference's CPU recipe of each secondary config on the host cores, same run:
+            # clip construction on a pool of single-thread workers, fp32 patch embedding on all threads
+            from oracle import cpu_baseline as cbm
+
+            cores = cbm.host_cores()
+            for name, rec, kind in (("vivit_cfg2", "vivit", "vivit"), ("timesformer_cfg3", "timesformer", "timesformer"),
+                                    ("swin_cfg4", "swin_roi", "swin")):
+                c = SECONDARY[name]
+                clip_rate = cbm.run(c["h"], c["w"], 48, c["T"], cores, 1, repeats=2, recipe=rec)
+                emb_ms = cbm.embed_cpu_ms(kind, c["videos"], c["T"], cores)
+                both = 1.0 / (1.0 / clip_rate + emb_ms * 1e-3 / c["videos"])
+                line["secondary"][name]["cpu_reference"] = {
+                    "clips_per_s": both, "clip_recipe_clips_per_s": clip_rate, "embed_ms_per_batch": emb_ms, "cores": cores,
+                    "sample": f"{cores} single-thread workers x 1 clip, median of 2; fp32 torch embed on {cores} threads, median of 2"}
     if not args.no_cpu_baseline:
         from oracle import cpu_baseline as cbm
 
