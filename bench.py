@@ -319,6 +319,26 @@ def run_secondary(dev, iters=10):
         else:
             ent["gemm_roofline"] = {"bound": "tensor", "achieved": flops / gemm_ms / 1e9, "peak": tf_peak, "unit": "TFLOP/s",
                                     "frac": flops / gemm_ms / 1e9 / tf_peak}
+        # host-inclusive throughput (wall clock, Python call path included): two eager launches per batch vs the
+        # captured CUDA graph of [table upload -> clip kernel -> GEMM] (pipeline.ClipEmbedPipeline)
+        from lvc_b200.pipeline import ClipEmbedPipeline
+
+        def wall(fn, n=100):
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(n):
+                fn()
+            torch.cuda.synchronize()
+            return (time.perf_counter() - t0) / n
+
+        eager_s = wall(lambda: m.forward_tokens(cb(vids, idx, boxes=boxes), c["videos"], c["T"]))
+        pipe = ClipEmbedPipeline(cb, m, vids, c["T"], boxes=boxes is not None)
+        graph_s = wall(lambda: pipe(idx, boxes))
+        ent["host_inclusive"] = {"eager_clips_per_s": c["videos"] / eager_s, "graph_clips_per_s": c["videos"] / graph_s,
+                                 "eager_ms_per_batch": eager_s * 1e3, "graph_ms_per_batch": graph_s * 1e3}
+        del pipe
         if c["embed"] in ("vivit", "timesformer"):
             # row f3: cls + position (+ time) embeddings fused into the GEMM epilogue vs the same step done
             # with torch ops after the plain GEMM (cat / add / permute = extra passes over the 38 MB output)

@@ -117,3 +117,38 @@ def test_ptv_transform_and_sharded_loader():
     tr, va, te = create_dataloaders(args, {"train": "random", "val": "uniform", "test": "uniform"}, None,
                                     frame_sources={"train": src, "val": src, "test": src})
     assert len(va) == 3 and sum(len(b["pixel_values"]) for b in va) == 5
+
+
+def test_clip_embed_pipeline_graph_replay_matches_eager():
+    """CUDA-graph pipeline (table upload -> clip kernel -> GEMM) == the two eager calls, across changing index tables,
+    ROI boxes and swapped videos."""
+    import numpy as np
+    import torch
+
+    from lvc_b200 import ClipBuilder, sampling
+    from lvc_b200.patch_embed import TimesformerPatchEmbeddings
+    from lvc_b200.pipeline import ClipEmbedPipeline
+    from lvc_b200.synth import synth_video
+
+    T = 4
+    vids = [torch.from_numpy(synth_video(40 + i, 12, 240, 320)).cuda() for i in range(3)]
+    cb = ClipBuilder("timesformer", num_frames=T, layout="TOKENS", patch=(1, 16, 16))
+    m = TimesformerPatchEmbeddings(out_dtype=torch.float32).cuda()
+    pipe = ClipEmbedPipeline(cb, m, vids, T, boxes=True)
+    rng = sampling.SamplerRng(3)
+    g = np.random.default_rng(0)
+    for it in range(4):
+        idx = np.array([sampling.get_sampling_indices("random", 12, T, rng) for _ in vids], np.int32)
+        boxes = np.full((3, T, 4), -1, np.int32)
+        if it % 2:
+            x1, y1 = g.integers(0, 100, (3, T)), g.integers(0, 80, (3, T))
+            boxes = np.stack([x1, y1, x1 + 150, y1 + 120], -1).astype(np.int32)
+        if it == 2:
+            vids = [torch.from_numpy(synth_video(50 + i, 12, 240, 320)).cuda() for i in range(3)]
+            pipe.set_videos(vids)
+        got = pipe(idx, boxes).clone()
+        want = m.forward_tokens(cb(vids, idx, boxes=boxes), 3, T)
+        assert torch.equal(got, want)
+    assert pipe.replays == 4
+    with pytest.raises(ValueError):
+        pipe.set_videos([torch.zeros(2, 100, 100, 3, dtype=torch.uint8, device="cuda")] * 3)
