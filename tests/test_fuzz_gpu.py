@@ -25,3 +25,11 @@ def test_randomised_embed_sweep():
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "24/24 cases match" in r.stdout
+
+
+def test_randomised_detector_pre_post_sweep():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_yolo.py"), "40", "13"], capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "40/40 cases match" in r.stdout
