@@ -170,7 +170,9 @@ __device__ __forceinline__ int4 pil_tap(int d) {
   }
   return make_int4(xmin, k[0], k[1], k[2]);
 }
-__device__ __forceinline__ int clip8(int v) { return min(max(v, 0), 255); }
+// Pillow's clip8 is the identity here: bilinear weights are non-negative and their integer sum is within
+// 2^22 +- 2 (<= 3 taps, each rounded to nearest), so 2^21 + sum(p*k) >> 22 stays in [0, 255] for p in [0, 255].
+__device__ __forceinline__ int clip8(int v) { return v; }
 
 // torch bilinear (align_corners=False) source coordinate, exactly as ATen's CPU kernel evaluates it:
 // src = max(fma(scale, dst + 0.5, -0.5), 0); i0 = min(floor(src), in-1); lambda = clamp(src - i0, 0, 1).
