@@ -271,28 +271,3 @@ class TimesformerEmbeddings(nn.Module):
         if (H, W) != tuple(pe.image_size) or T != self.num_frames:
             raise ValueError("input size does not match the position / time tables (resizing is not fused)")
         return pe._run(pixel_values, B, T, H, W, (B, 1 + self.num_patches * T, E), emb=emb)
-
-
-def smoke():
-    """Tiny ViViT tubelet embedding on cuda:0 against the fp32 oracle (called by __graft_entry__.smoke)."""
-    from oracle import patch_embed as ope
-
-    torch.manual_seed(0)
-    m = VivitTubeletEmbeddings(num_frames=4, image_size=64).cuda()
-    x = torch.randn(2, 4, 3, 64, 64, device="cuda")
-    y = m(x).float().cpu()
-    ref = ope.vivit_tubelet_embed(x.cpu(), m.projection.weight.detach().cpu(), m.projection.bias.detach().cpu())
-    e_max, e_l2 = ope.rel_err(y, ref)
-    assert e_max <= 1e-2 and e_l2 <= 1e-2, (e_max, e_l2)
-    print(f"smoke ok: tcgen05 tubelet embedding {tuple(y.shape)} rel err max {e_max:.2e} l2 {e_l2:.2e}")
-    # Video Swin: short-K GEMM + LayerNorm kernel
-    from functools import partial
-
-    sw = PatchEmbed3d([2, 4, 4], 3, 128, partial(nn.LayerNorm, eps=1e-5)).cuda()
-    xs = torch.randn(1, 3, 4, 64, 64, device="cuda")
-    ys = sw(xs).float().cpu()
-    rs = ope.swin_patch_embed(xs.cpu(), sw.proj.weight.detach().cpu(), sw.proj.bias.detach().cpu(),
-                              sw.norm.weight.detach().cpu(), sw.norm.bias.detach().cpu())
-    e_max, e_l2 = ope.rel_err(ys, rs)
-    assert e_max <= 1e-2 and e_l2 <= 1e-2, (e_max, e_l2)
-    print(f"smoke ok: Swin patch embedding + LayerNorm {tuple(ys.shape)} rel err max {e_max:.2e} l2 {e_l2:.2e}")

@@ -1,5 +1,5 @@
 """Randomised parity sweep of the patch-embedding kernels (ragged token counts, both output dtypes, both input
-layouts) against fp32 torch on the CPU.  python scripts/fuzz_embed.py [cases] [seed]"""
+layouts) against fp32 torch on the CPU.  python tests/fuzz_embed.py [cases] [seed]"""
 import os
 import sys
 from functools import partial

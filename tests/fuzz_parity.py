@@ -1,5 +1,5 @@
 """Randomised parity sweep of the fused clip kernel against the oracle (GPU box): random frame sizes, ROI boxes,
-index tables, presets, layouts and source orders.  python scripts/fuzz_parity.py [cases] [seed]"""
+index tables, presets, layouts and source orders.  python tests/fuzz_parity.py [cases] [seed]"""
 import os
 import sys
 

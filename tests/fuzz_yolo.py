@@ -1,4 +1,4 @@
-"""Randomised parity sweep of the detector pre / post-processing kernels: python scripts/fuzz_yolo.py [cases] [seed]"""
+"""Randomised parity sweep of the detector pre / post-processing kernels: python tests/fuzz_yolo.py [cases] [seed]"""
 import os
 import sys
 

@@ -1,4 +1,4 @@
-"""Bounded randomised parity sweep (scripts/fuzz_parity.py): random frame sizes, out-of-range indices, ROI boxes that
+"""Bounded randomised parity sweep (tests/fuzz_parity.py): random frame sizes, out-of-range indices, ROI boxes that
 stick out of the frame, all presets, RGB / BGR sources -- every case bit-exact against the oracle (float chain within
 the tolerance of tests/test_clip_gpu.py)."""
 import os
@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 
 def test_randomised_parity_sweep():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_parity.py"), "40", "7"], capture_output=True,
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "fuzz_parity.py"), "40", "7"], capture_output=True,
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "40/40 cases match" in r.stdout
@@ -21,7 +21,7 @@ def test_randomised_parity_sweep():
 def test_randomised_embed_sweep():
     """Ragged token counts (partial 128/256-row tiles), both dtypes, plain and fused-embeddings epilogues."""
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_embed.py"), "24", "11"], capture_output=True,
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "fuzz_embed.py"), "24", "11"], capture_output=True,
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "24/24 cases match" in r.stdout
@@ -29,7 +29,7 @@ def test_randomised_embed_sweep():
 
 def test_randomised_detector_pre_post_sweep():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_yolo.py"), "40", "13"], capture_output=True,
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "fuzz_yolo.py"), "40", "13"], capture_output=True,
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "40/40 cases match" in r.stdout
