@@ -15,6 +15,10 @@ def __getattr__(name):  # torch-dependent parts load lazily
         from . import clips
 
         return getattr(clips, name)
+    if name in ("VivitImageProcessor", "TimesformerImageProcessor", "PtvEvalTransform", "PtvTrainTransform"):
+        from . import processors
+
+        return getattr(processors, name)
     if name in ("clips", "datasets", "dataloader", "processors", "patch_embed", "decode", "sharding"):
         import importlib
 

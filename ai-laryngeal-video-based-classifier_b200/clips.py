@@ -9,6 +9,8 @@ normalisation of a reference recipe, in a single fused kernel launch.  Presets:
   vivit         cv2.resize 224 -> VivitImageProcessor -> (B,T,C,H,W)      vivit .../trainers/trainer.py:62-95
   dataset_u8    cv2.resize 224 -> uint8 (B,T,H,W,3)                       vivit .../dataset.py:271-292
   ptv_eval      ShortSideScale(256)+CenterCrop(224)+Normalize (float)     videoswintransformer/.../dataset.py:164-172
+  vivit_raw     RAW frames -> VivitImageProcessor (Pillow shortest edge 256, crop 224)   vivit_transformer/data_preprocessing.py:16
+  timesformer_raw  RAW frames -> VideoMAE-class processor (shortest edge 224, crop 224)  timesformer_transformer/data_preprocessing_timesformer.py:16
 """
 import ctypes as C
 
@@ -31,7 +33,11 @@ PRESETS = {
     "vivit": (_lib.RESAMPLE_CV2_PIL256, _lib.LUT_MUL64, 1 / 127.5, True, IMAGENET_STANDARD, "BTCHW", torch.float32),
     "dataset_u8": (_lib.RESAMPLE_CV2, None, 0.0, False, KINETICS, "BTHWC", torch.uint8),
     "ptv_eval": (_lib.RESAMPLE_PTV_EVAL, None, 0.0, False, KINETICS, "BCTHW", torch.float32),
+    "vivit_raw": (_lib.RESAMPLE_PIL_SHORT, _lib.LUT_MUL64, 1 / 127.5, True, IMAGENET_STANDARD, "BTCHW", torch.float32),
+    "timesformer_raw": (_lib.RESAMPLE_PIL_SHORT, _lib.LUT_MUL64, 1 / 255, False, KINETICS, "BTCHW", torch.float32),
 }
+# shortest_edge of the HF processors' resize step (VivitImageProcessor / VideoMAEImageProcessor defaults)
+HF_SHORTEST_EDGE = {"vivit_raw": 256, "timesformer_raw": 224}
 
 
 def build_lut(kind, scale, offset, mean, std):
@@ -77,7 +83,7 @@ class ClipBuilder:
     """
 
     def __init__(self, preset="resnet_infer", num_frames=32, mean=None, std=None, layout=None, dtype=None,
-                 device=None, patch=None, src_order="RGB", float_frames=False):
+                 device=None, patch=None, src_order="RGB", float_frames=False, shortest_edge=None):
         if preset not in PRESETS:
             raise ValueError(f"unknown preset {preset!r}; choose from {sorted(PRESETS)}")
         if not torch.cuda.is_available():
@@ -96,8 +102,12 @@ class ClipBuilder:
         # float_frames: resize as the reference's primary Dataset branch does (pytorchvideo decode gives float32
         # frames, vivit .../dataset.py:244-284): cv2.resize in float, then truncation to uint8
         self.float_frames = bool(float_frames)
-        if self.float_frames and rs == _lib.RESAMPLE_PTV_EVAL:
+        if self.float_frames and rs in (_lib.RESAMPLE_PTV_EVAL, _lib.RESAMPLE_PIL_SHORT):
             raise ValueError("float_frames applies to the cv2.resize presets only")
+        # *_raw presets: the HF processor's own resize (size={"shortest_edge": E}) on frames of any size
+        self.shortest_edge = int(shortest_edge if shortest_edge is not None else HF_SHORTEST_EDGE.get(preset, 0))
+        if rs == _lib.RESAMPLE_PIL_SHORT and self.shortest_edge < 224:
+            raise ValueError("shortest_edge must be >= 224 (a smaller resize would make the centre crop pad)")
         # layout="TOKENS": write the bf16 patch matrix A[M][K] of a (kt,kh,kw) patch embedding directly
         self.patch = tuple(int(v) for v in patch) if patch is not None else (0, 0, 0)
         if self.layout == "TOKENS":
@@ -135,7 +145,7 @@ class ClipBuilder:
         host = torch.empty(off_aug + na, dtype=torch.uint8).pin_memory()
         hv = host.numpy()
         vt = (_lib.Video * B).from_buffer(hv)  # writes straight into the pinned buffer
-        max_w = 0
+        max_w = self._max_h = 0
         for i, v in enumerate(videos):
             resident = v.is_cuda or (self.allow_pinned_host and v.is_pinned())
             if v.dtype != torch.uint8 or v.dim() != 4 or v.shape[-1] != 3 or not resident or not v.is_contiguous():
@@ -145,6 +155,7 @@ class ClipBuilder:
             vt[i].base, vt[i].nbytes = v.data_ptr(), v.numel()
             vt[i].n_frames, vt[i].height, vt[i].width = v.shape[0], v.shape[1], v.shape[2]
             max_w = max(max_w, v.shape[2])
+            self._max_h = max(self._max_h, v.shape[1])
         hv[off_idx:off_idx + idx.nbytes] = idx.view(np.uint8).reshape(-1)
         if boxes is not None:
             bx = np.ascontiguousarray(np.asarray(boxes, dtype=np.int32).reshape(B, T, 4))
@@ -169,12 +180,15 @@ class ClipBuilder:
         B, T = len(videos), self.num_frames
         if aug is not None and self.resample != _lib.RESAMPLE_PTV_EVAL:
             raise ValueError("aug belongs to the pytorchvideo chain (preset 'ptv_eval')")
+        if boxes is not None and self.resample == _lib.RESAMPLE_PIL_SHORT:
+            raise ValueError("the *_raw presets take whole frames (no ROI boxes)")
         tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes, aug)
         d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, *self.patch,
                           (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std), self.src_order, int(self.float_frames))
         cb = ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
                        _shape(self.layout, B, T, patch=self.patch))
         cb.p_aug = self._p_aug
+        cb.max_h = self._max_h
         cb.dev_boxes = self._dev_boxes  # keeps the table alive
         return cb
 
@@ -185,6 +199,15 @@ class ClipBuilder:
         elif tuple(out.shape) != batch.shape or out.dtype != self.dtype or not out.is_contiguous():
             raise ValueError("out has the wrong shape, dtype or strides")
         stream = torch.cuda.current_stream(self.device).cuda_stream
+        if self.resample == _lib.RESAMPLE_PIL_SHORT:
+            if stats is not None:
+                raise ValueError("the *_raw presets have no checksum output")
+            st = _lib.lib().lvc_hf_clip_forward(C.byref(batch.desc), self.shortest_edge, batch.max_h, batch.p_vid,
+                                                batch.p_idx, self.lut.data_ptr() if self.lut is not None else None,
+                                                out.data_ptr(), stream)
+            _lib.check(st, "lvc_hf_clip_forward")
+            self.launches += 1
+            return out
         st = _lib.lib().lvc_clip_forward_aug(C.byref(batch.desc), batch.p_vid, batch.p_idx, batch.p_box,
                                              getattr(batch, "p_aug", None),
                                              self.lut.data_ptr() if self.lut is not None else None,
@@ -219,7 +242,7 @@ class ClipBuilder:
         (each distinct frame once), then run the kernel on the staged frames."""
         T = self.num_frames
         if zero_copy is None:
-            zero_copy = all((not v.is_cuda) and v.is_pinned() for v in host_videos) and self.resample != _lib.RESAMPLE_PTV_EVAL
+            zero_copy = all((not v.is_cuda) and v.is_pinned() for v in host_videos) and self.resample not in (_lib.RESAMPLE_PTV_EVAL, _lib.RESAMPLE_PIL_SHORT)
         if zero_copy:
             self.allow_pinned_host = True
             try:

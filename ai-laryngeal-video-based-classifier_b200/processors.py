@@ -11,8 +11,11 @@
 Call signature and result follow the HF processors: ``proc(images, return_tensors="pt", **kw)`` returns
 a mapping with ``"pixel_values"``: float32 ``(B, T, 3, 224, 224)`` (B = 1 for one video), supporting
 ``.keys()``, ``[k]``, ``.items()`` -- but the tensor is already on the GPU, so the caller's ``.to(device)``
-is a no-op.  Frames must be uint8 RGB; any source size is resized with cv2-exact bilinear first (the
-reference always hands over 224x224 frames, where that stage is the identity).
+is a no-op.  Frames must be uint8 RGB.  224x224 frames (what the reference's Datasets hand over) take the
+fused clip kernel's presets; frames of any other size -- the stand-alone scripts data_preprocessing.py:16,
+data_preprocessing_timesformer.py:16 pass decoded frames as they are -- take the processor's own geometry:
+Pillow BILINEAR resize of the shortest edge (256 ViViT / 224 VideoMAE-class), centre crop 224
+(``lvc_hf_clip_forward``), bit-exact against transformers.
 """
 import numpy as np
 import torch
@@ -55,6 +58,8 @@ def _as_videos(images, device):
 
 class _ClipProcessor:
     preset = None
+    raw_preset = None   # used when the frames are not already 224x224
+    shortest_edge = None
 
     def __init__(self, image_mean=None, image_std=None, device=None, **ignored):
         # the reference passes extra kwargs (num_frames, image_size, patch_size) the HF class ignores
@@ -64,17 +69,21 @@ class _ClipProcessor:
         self.device = device
         self._builders = {}
 
-    def _builder(self, T):
-        if T not in self._builders:
-            self._builders[T] = ClipBuilder(self.preset, num_frames=T, mean=self.image_mean, std=self.image_std,
-                                            device=self.device)
-        return self._builders[T]
+    def _builder(self, T, raw=False):
+        if (T, raw) not in self._builders:
+            self._builders[T, raw] = ClipBuilder(self.raw_preset if raw else self.preset, num_frames=T,
+                                                 mean=self.image_mean, std=self.image_std, device=self.device,
+                                                 shortest_edge=self.shortest_edge if raw else None)
+        return self._builders[T, raw]
 
     def _check(self, kw):
         for key in ("size", "crop_size"):
             v = kw.get(key)
             if v is not None and (v.get("height", 224) != 224 or v.get("width", 224) != 224):
                 raise NotImplementedError(f"{key}={v}: only 224x224 is supported")
+        for key in ("do_resize", "do_center_crop", "do_rescale", "do_normalize"):
+            if kw.get(key) is False:
+                raise NotImplementedError(f"{key}=False: the fused kernel always runs the whole chain")
 
     def __call__(self, images=None, return_tensors="pt", videos=None, **kw):
         if images is None:
@@ -88,7 +97,12 @@ class _ClipProcessor:
         if any(v.shape[0] != T for v in vids):
             raise ValueError("all videos of a batch must have the same number of frames")
         idx = np.tile(np.arange(T, dtype=np.int32), (len(vids), 1))
-        return BatchFeature(pixel_values=self._builder(T)(vids, idx))
+        raw = any(tuple(v.shape[1:3]) != (224, 224) for v in vids)
+        if raw and "height" in (kw.get("size") or {}):
+            # size={"height", "width"} on other sizes is an aspect-changing Pillow resize: not fused
+            raise NotImplementedError("size={'height': 224, 'width': 224} is fused for 224x224 frames only; "
+                                      "omit `size` for the processor's shortest-edge geometry")
+        return BatchFeature(pixel_values=self._builder(T, raw)(vids, idx))
 
     preprocess = __call__
 
@@ -98,6 +112,8 @@ class VivitImageProcessor(_ClipProcessor):
     ``x/127.5 - 1``, mean/std 0.5 -> values in [-3, 1]."""
 
     preset = "vivit"
+    raw_preset = "vivit_raw"
+    shortest_edge = 256
 
     def _check(self, kw):
         super()._check(kw)
@@ -110,6 +126,8 @@ class TimesformerImageProcessor(_ClipProcessor):
     checkpoint's mean/std are not available offline: pass them, default 0.45/0.225."""
 
     preset = "timesformer"
+    raw_preset = "timesformer_raw"   # the checkpoint's preprocessor_config: shortest_edge 224, crop 224
+    shortest_edge = 224
 
     def __init__(self, image_mean=None, image_std=None, **kw):
         super().__init__(image_mean if image_mean is not None else KINETICS[0],

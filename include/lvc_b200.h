@@ -125,7 +125,10 @@ enum {
   /* pytorchvideo eval chain on float frames: ShortSideScale(256) via torch bilinear
    * (align_corners=False), CenterCrop(224), (x-mean)/std without /255
    * (videoswintransformer/.../dataset.py:164-172).  Uses mean/std, not the LUT. */
-  LVC_RESAMPLE_PTV_EVAL = 2
+  LVC_RESAMPLE_PTV_EVAL = 2,
+  /* HF image processor on RAW frames of any size: Pillow BILINEAR (antialiased) resize of the shortest edge,
+   * centre crop 224, LUT.  Only through lvc_hf_clip_forward (lvc_clip_forward rejects it). */
+  LVC_RESAMPLE_PIL_SHORT = 3
 };
 enum {
   LVC_LAYOUT_BTCHW = 0,
@@ -188,6 +191,21 @@ int lvc_clip_forward(const lvc_clip_desc* desc, const lvc_video* videos, const i
 int lvc_clip_forward_aug(const lvc_clip_desc* desc, const lvc_video* videos, const int32_t* indices,
                          const int32_t* boxes, const int32_t* aug, const float* lut, void* out,
                          uint64_t* stats, void* stream);
+
+/* The HF image processors applied to RAW decoded frames, as the reference's stand-alone preprocessing scripts
+ * call them (vivit_transformer/data_preprocessing.py:16 `image_processor(list(video), return_tensors="pt")`,
+ * timesformer_transformer/data_preprocessing_timesformer.py:16, vivit_transformer/inference.py:187):
+ * resize(shortest_edge) with PIL BILINEAR -- Pillow widens the triangle filter with the down-scale and rounds to
+ * uint8 after each of its two passes -- centre crop 224, rescale + normalise (the LUT), layout.
+ *   shortest_edge  256 for VivitImageProcessor, 224 for the VideoMAE-class processor; >= 224
+ *   max_height     largest frame height among the B videos (with desc->max_width it sizes the shared-memory
+ *                  buffers; a larger video is a contract violation and traps).  Down-scales up to 11.5x.
+ * desc->resample is ignored (LVC_RESAMPLE_PIL_SHORT implied), desc->src_float must be 0; no ROI boxes, no stats.
+ * Output size is (int(E*W/H)|E) x (E|int(E*H/W)) as get_resize_output_image_size computes it, cropped at
+ * ((nh-224)//2, (nw-224)//2).  Bit-exact against the processor (tests/test_hfraw_gpu.py). */
+int lvc_hf_clip_forward(const lvc_clip_desc* desc, int32_t shortest_edge, int32_t max_height,
+                        const lvc_video* videos, const int32_t* indices, const float* lut, void* out,
+                        void* stream);
 
 /* Number of kernel launches lvc_clip_forward enqueues for this descriptor (for accounting). */
 int lvc_clip_launch_count(const lvc_clip_desc* desc);

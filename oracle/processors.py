@@ -75,6 +75,26 @@ def vivit_processor(frames224):
     return out
 
 
+def hf_shortest_edge_crop_u8(frames, edge, crop=224):
+    """Geometry the HF video processors apply to RAW frames (data_preprocessing.py:16,
+    data_preprocessing_timesformer.py:16): ``resize(size={"shortest_edge": edge}, resample=BILINEAR)`` through
+    Pillow, then ``center_crop(crop)``; uint8 (T, crop, crop, 3).  transformers image_transforms.py
+    get_resize_output_image_size / resize / center_crop."""
+    T, H, W, _ = frames.shape
+    if H <= W:
+        nh, nw = edge, int(edge * W / H)
+    else:
+        nh, nw = int(edge * H / W), edge
+    top, left = (nh - crop) // 2, (nw - crop) // 2
+    return np.stack([pil_resize_bilinear_u8(frames[t], nh, nw)[top : top + crop, left : left + crop] for t in range(T)])
+
+
+def videomae_processor_raw(frames, mean=(0.45, 0.45, 0.45), std=(0.225, 0.225, 0.225), edge=224):
+    """VideoMAEImageProcessor defaults of the TimeSformer checkpoint on raw frames: shortest edge 224
+    (Pillow BILINEAR), centre crop 224, then ``videomae_processor``'s rescale + normalise."""
+    return videomae_processor(hf_shortest_edge_crop_u8(np.asarray(frames), edge), mean, std)
+
+
 def videomae_processor(frames224, mean=(0.45, 0.45, 0.45), std=(0.225, 0.225, 0.225)):
     """a8 -- VideoMAE-class processor as forced to size=crop=224 at
     timesformer .../trainers/trainer.py:91-98 (resize and crop are identities on 224x224

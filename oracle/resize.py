@@ -120,7 +120,9 @@ def pil_bilinear_coeffs(in_size, out_size):
             t = (x + xmin - center + 0.5) * ss
             t = -t if t < 0 else t
             w[x] = 1.0 - t if t < 1.0 else 0.0
-        ww = w.sum()
+        ww = 0.0
+        for x in range(n):  # Pillow accumulates in tap order (numpy's sum is pairwise from 8 terms up)
+            ww += float(w[x])
         if ww != 0.0:
             w = w / ww
         for x in range(n):

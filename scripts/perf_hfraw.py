@@ -1,0 +1,30 @@
+"""Timing of the raw-frame HF processor kernel (lvc_hf_clip_forward) on the device."""
+import sys
+import torch
+sys.path.insert(0, ".")
+from lvc_b200 import ClipBuilder
+
+def run(preset, shape, B=8, T=32, n=40, iters=20):
+    vids = [torch.randint(0, 256, (n,) + shape + (3,), dtype=torch.uint8, device="cuda") for _ in range(B)]
+    idx = torch.randint(0, n, (B, T)).numpy()
+    cb = ClipBuilder(preset, num_frames=T)
+    batch = cb.prepare(vids, idx)
+    out = cb.run(batch)
+    for _ in range(3):
+        cb.run(batch, out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        cb.run(batch, out)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    E = cb.shortest_edge
+    h, w = shape
+    side = 224 / E * min(h, w)
+    alg = B * T * (side * side * 3 + 224 * 224 * 3 * 4)
+    print(f"{preset:16s} {h}x{w} B={B} T={T}: {ms:.3f} ms  {B / ms * 1e3:.0f} clips/s  {alg / ms / 1e6:.0f} GB/s algorithmic")
+
+for preset in ("vivit_raw", "timesformer_raw"):
+    for shape in ((1080, 1920), (720, 1280), (480, 640), (256, 340)):
+        run(preset, shape)

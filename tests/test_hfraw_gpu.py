@@ -1,0 +1,114 @@
+"""GPU parity: lvc_hf_clip_forward (HF processors on RAW frames, presets vivit_raw / timesformer_raw) against
+the oracle and against transformers itself.  Bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(720, 1280), (480, 640), (300, 200), (256, 256), (231, 517), (1080, 1920), (224, 224), (1100, 240),
+          (225, 225), (2160, 3840)]
+
+
+def _frames(shape, n=3, seed=0):
+    rng = np.random.default_rng(seed)
+    return rng.integers(0, 256, (n,) + shape + (3,), dtype=np.uint8)
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_vivit_raw_vs_oracle(shape):
+    from lvc_b200 import ClipBuilder
+    from oracle import processors as op
+
+    fr = _frames(shape, 3, seed=shape[0])
+    idx = [[2, 0, 1, 1]]
+    out = ClipBuilder("vivit_raw", num_frames=4)([torch.from_numpy(fr).cuda()], idx)
+    ref = op.vivit_processor(fr[[2, 0, 1, 1]])
+    assert torch.equal(out[0].cpu(), torch.from_numpy(ref))
+
+
+@pytest.mark.parametrize("shape", SHAPES[:8])
+def test_timesformer_raw_vs_oracle(shape):
+    from lvc_b200 import ClipBuilder
+    from oracle import processors as op
+
+    fr = _frames(shape, 2, seed=shape[1])
+    out = ClipBuilder("timesformer_raw", num_frames=2)([torch.from_numpy(fr).cuda()], [[0, 1]])
+    ref = op.videomae_processor_raw(fr)
+    assert torch.equal(out[0].cpu(), torch.from_numpy(ref))
+
+
+def test_ragged_batch_layouts_bgr():
+    """Videos of different sizes in one launch; every layout; BGR sources."""
+    from lvc_b200 import ClipBuilder
+    from oracle import processors as op
+
+    shapes = [(480, 640), (720, 1280), (300, 200), (1080, 1920), (224, 224)]
+    vids = [_frames(s, 5, seed=i) for i, s in enumerate(shapes)]
+    rng = np.random.default_rng(9)
+    idx = rng.integers(0, 5, (len(vids), 4))
+    dv = [torch.from_numpy(v).cuda() for v in vids]
+    u8 = np.stack([op.hf_shortest_edge_crop_u8(v[idx[b]], 256) for b, v in enumerate(vids)])   # (B,T,224,224,3)
+    out = ClipBuilder("vivit_raw", num_frames=4, layout="BTHWC", dtype=torch.uint8)(dv, idx)
+    assert np.array_equal(out.cpu().numpy(), u8)
+    ref = np.stack([op.vivit_processor(v[idx[b]]) for b, v in enumerate(vids)])               # (B,T,3,224,224)
+    out = ClipBuilder("vivit_raw", num_frames=4)(dv, idx)
+    assert np.array_equal(out.cpu().numpy(), ref)
+    out = ClipBuilder("vivit_raw", num_frames=4, layout="BCTHW", dtype=torch.bfloat16)(dv, idx)
+    want = torch.from_numpy(ref).permute(0, 2, 1, 3, 4).to(torch.bfloat16)
+    assert torch.equal(out.cpu(), want)
+    # tokens = the ViViT tubelet GEMM operand: (B*T/2*14*14, 3*2*16*16), K ordered (c, kt, kh, kw)
+    out = ClipBuilder("vivit_raw", num_frames=4, layout="TOKENS", patch=(2, 16, 16))(dv, idx)
+    x = torch.from_numpy(ref).to(torch.bfloat16)                                               # B,T,C,H,W
+    B = len(vids)
+    tok = x.view(B, 2, 2, 3, 14, 16, 14, 16).permute(0, 1, 4, 6, 3, 2, 5, 7).reshape(B * 2 * 196, 1536)
+    assert torch.equal(out.cpu(), tok)
+    # BGR sources: the gather swaps channels
+    dvb = [v.flip(-1).contiguous() for v in dv]
+    out = ClipBuilder("vivit_raw", num_frames=4, src_order="BGR")(dvb, idx)
+    assert np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_raw_equals_224_preset_on_224_frames():
+    from lvc_b200 import ClipBuilder
+
+    fr = torch.from_numpy(_frames((224, 224), 4, seed=3)).cuda()
+    idx = [[0, 1, 2, 3]]
+    assert torch.equal(ClipBuilder("vivit_raw", num_frames=4)([fr], idx), ClipBuilder("vivit", num_frames=4)([fr], idx))
+    assert torch.equal(ClipBuilder("timesformer_raw", num_frames=4)([fr], idx),
+                       ClipBuilder("timesformer", num_frames=4)([fr], idx))
+
+
+@pytest.mark.parametrize("shape", [(360, 640), (720, 1280), (512, 384)])
+def test_processor_dropin_vs_transformers(shape):
+    """data_preprocessing.py:16 / data_preprocessing_timesformer.py:16: `image_processor(list(frames),
+    return_tensors='pt')` on decoded frames of the video's own size."""
+    tr = pytest.importorskip("transformers")
+    import lvc_b200
+
+    fr = _frames(shape, 4, seed=11)
+    ref = tr.VivitImageProcessor()(list(fr), return_tensors="pt")["pixel_values"]
+    got = lvc_b200.VivitImageProcessor()(list(fr), return_tensors="pt")["pixel_values"]
+    assert got.shape == ref.shape and torch.equal(got.cpu(), ref)
+    mean, std = [0.45] * 3, [0.225] * 3
+    # legacy (transformers 4.48.2) VideoMAE chain, see tests/test_hfraw_cpu.py
+    legacy = tr.VivitImageProcessor(size={"shortest_edge": 224}, crop_size={"height": 224, "width": 224}, offset=False,
+                                    rescale_factor=1 / 255, image_mean=mean, image_std=std)
+    ref = legacy(list(fr), return_tensors="pt")["pixel_values"]
+    got = lvc_b200.TimesformerImageProcessor(image_mean=mean, image_std=std)(list(fr), return_tensors="pt")["pixel_values"]
+    assert torch.equal(got.cpu(), ref)
+    with pytest.raises(NotImplementedError):
+        lvc_b200.TimesformerImageProcessor()(list(fr), size={"height": 224, "width": 224})
+
+
+def test_errors():
+    from lvc_b200 import ClipBuilder
+
+    fr = torch.from_numpy(_frames((300, 300), 2)).cuda()
+    with pytest.raises(ValueError):
+        ClipBuilder("vivit_raw", num_frames=2, shortest_edge=200)
+    with pytest.raises(ValueError):
+        ClipBuilder("vivit_raw", num_frames=2)([fr], [[0, 1]], boxes=np.zeros((1, 2, 4), np.int32))
+    big = torch.zeros((1, 224 * 13, 224 * 13, 3), dtype=torch.uint8, device="cuda")   # 13x down-scale: > 24 taps
+    with pytest.raises(ValueError):
+        ClipBuilder("timesformer_raw", num_frames=1)([big], [[0]])
