@@ -15,6 +15,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 
 #include "lvc_internal.h"
 
@@ -22,8 +23,7 @@ namespace {
 
 constexpr int S = 224;        // crop / output size
 constexpr int KT = 24;        // most taps per output sample: ceil(scale)*2+1 <= 24, scale <= 11.5
-constexpr int kThreads = 256;
-constexpr int kWarps = kThreads / 32;
+constexpr int kMaxThreads = 512;
 constexpr int kCH = 32;       // source rows per staged block: one row per lane in the horizontal pass
 constexpr int IP = S + 1;     // words per row of the intermediate ring (odd: lane = row writes hit 32 banks)
 
@@ -82,11 +82,14 @@ __device__ __forceinline__ void hf_geom(int H, int W, int E, int& nh, int& nw) {
 __device__ __forceinline__ void cp_async4(void* dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
 }
+__device__ __forceinline__ void cp_async4s(uint32_t dst_shared, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_shared), "l"(src) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-__global__ void __launch_bounds__(kThreads) lvc_pil_kernel(const __grid_constant__ PilParams p) {
+__global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_constant__ PilParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int kt = p.kt;
   int* hk = reinterpret_cast<int*>(smem);                 // [kt][S]  horizontal weights, tap-major
@@ -100,6 +103,7 @@ __global__ void __launch_bounds__(kThreads) lvc_pil_kernel(const __grid_constant
   uint32_t* inter = reinterpret_cast<uint32_t*>(lut + 768);            // [ir][IP] ring of horizontally resized rows
   uint32_t* rows = inter + (size_t)p.ir * IP;                          // [2][kCH][pitch_words]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kThreads = blockDim.x, kWarps = kThreads >> 5;
   if (p.lut)
     for (int i = tid; i < 768; i += kThreads) lut[i] = p.lut[i];
   int cw = -1, ch_ = -1;   // frame size the tables were built for
@@ -150,14 +154,24 @@ __global__ void __launch_bounds__(kThreads) lvc_pil_kernel(const __grid_constant
         if (nwords > p.pitch_words) __trap();   // frame larger than the descriptor says
         if (lane == 0) rsh[(q & 1) * kCH + j] = sh;
         uint32_t* dst = slot + (size_t)j * p.pitch_words;
-        for (int i = lane; i < nwords; i += 32) {
-          const uint64_t wa = a4 + 4u * (uint64_t)i;
-          if (wa + 4 <= buf_end) cp_async4(dst + i, reinterpret_cast<const void*>(wa));
-          else {   // last bytes of the buffer
-            uint32_t w = 0;
-            for (int qq = 0; qq < 4; ++qq)
-              if (wa + qq < buf_end) w |= (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(wa + qq)) << (8 * qq);
-            dst[i] = w;
+        if (a4 + 4u * (uint64_t)nwords <= buf_end) {   // every row but the buffer's last: no per-word bound check
+          const uint8_t* g = reinterpret_cast<const uint8_t*>(a4) + 4 * lane;
+          uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst) + 4u * lane;
+          int left = nwords - lane;
+          for (; left > 96; left -= 128, g += 512, sa += 512) {
+            cp_async4s(sa, g); cp_async4s(sa + 128, g + 128); cp_async4s(sa + 256, g + 256); cp_async4s(sa + 384, g + 384);
+          }
+          for (; left > 0; left -= 32, g += 128, sa += 128) cp_async4s(sa, g);
+        } else {
+          for (int i = lane; i < nwords; i += 32) {
+            const uint64_t wa = a4 + 4u * (uint64_t)i;
+            if (wa + 4 <= buf_end) cp_async4(dst + i, reinterpret_cast<const void*>(wa));
+            else {   // last bytes of the buffer
+              uint32_t w = 0;
+              for (int qq = 0; qq < 4; ++qq)
+                if (wa + qq < buf_end) w |= (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(wa + qq)) << (8 * qq);
+              dst[i] = w;
+            }
           }
         }
       }
@@ -288,25 +302,31 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
   p.edge = shortest_edge; p.kt_tok = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
   p.kt = 2 * cs + 1;
   p.ir = kCH + p.kt + 1;
-  // Column segments: as few as keep two CTAs resident per SM (their barriers and copy waits then overlap).
+  // Column segments: the fewest that keep a CTA's footprint under 128 KB (measured best on B200: larger stages
+  // gain nothing, smaller ones pay more barriers and overlap columns).
   const size_t fixed = (size_t)(2 * p.kt * S + 4 * S + 2 * kCH + 768) * 4 + (size_t)p.ir * IP * 4;
   static const int kSegs[] = {1, 2, 4, 7, 14, 28};
   size_t smem = 0;
   int pick = -1;
+  const char* env_seg = std::getenv("LVC_PIL_NSEG");   // tuning override
+  const int force_seg = env_seg ? std::atoi(env_seg) : 0;
   for (int pass = 0; pass < 2 && pick < 0; ++pass)
     for (int i = 0; i < 6; ++i) {
+      if (force_seg > 0 && (kSegs[i] != force_seg || pass == 0)) continue;
       const int xs = S / kSegs[i];
       const int span_px = std::min((int)(xs * scale) + 2 * cs + 3, d->max_width);
       int pw = (span_px * 3 + 6) / 4 + 1;
       pw |= 1;
       const size_t need = fixed + (size_t)2 * kCH * pw * 4;
-      if (need <= (pass == 0 ? (size_t)(max_smem / 2 - 2048) : (size_t)max_smem)) {
+      if (need <= (pass == 0 ? (size_t)128 * 1024 : (size_t)max_smem)) {
         pick = i; p.nseg = kSegs[i]; p.pitch_words = pw; smem = need;
         break;
       }
     }
   if (pick < 0) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: frames too large for shared memory");
-  const int per_sm = std::max(1, std::min(2, (int)((size_t)max_smem / (smem + 1024))));
+  int threads = 512;
+  if (const char* env_t = std::getenv("LVC_PIL_THREADS")) threads = std::max(256, std::min(kMaxThreads, std::atoi(env_t) / 32 * 32));
+  const int per_sm = std::max(1, std::min(std::min(2, 2048 / threads), (int)((size_t)max_smem / (smem + 1024))));
   const int slots = sms * per_sm;
   // Bands per frame: minimise rounds x source rows per item (each band re-reads a halo of ~kt rows)
   const int frames = d->batch * d->num_frames;
@@ -317,10 +337,14 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
     const double cost = std::ceil((double)frames * nb / slots) * (R * scale + p.kt + 16);
     if (cost < best * 0.97) { best = cost; p.bands = nb; p.R = R; }
   }
+  if (const char* env_b = std::getenv("LVC_PIL_BANDS")) {   // tuning override
+    const int nb = std::atoi(env_b);
+    if (nb > 0 && S % nb == 0) { p.bands = nb; p.R = S / nb; }
+  }
   p.total_items = frames * p.bands;
   LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_pil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = std::min(p.total_items, slots);
-  lvc_pil_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  lvc_pil_kernel<<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;
 }

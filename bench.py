@@ -255,6 +255,29 @@ SECONDARY = {
 }
 
 
+def _hf_raw_cpu(frames=8):
+    """The reference's own call for this path -- transformers' VivitImageProcessor (numpy + Pillow) on raw
+    1080p frames -- timed in one process on a bounded sample; else the oracle's restatement."""
+    import numpy as np
+
+    fr = np.random.default_rng(0).integers(0, 256, (frames, 1080, 1920, 3), dtype=np.uint8)
+    try:
+        from transformers import VivitImageProcessor
+
+        proc, kind = VivitImageProcessor(), "reference (transformers + Pillow)"
+        fn = lambda: proc(list(fr), return_tensors="pt")  # noqa: E731
+    except Exception:  # transformers / Pillow missing on the box
+        from oracle import processors as op
+
+        kind, fn = "port (oracle.processors.vivit_processor)", (lambda: op.vivit_processor(fr))
+    fn()
+    t0 = time.perf_counter()
+    fn()
+    dt = time.perf_counter() - t0
+    return {"clips_per_s": frames / dt / 32.0, "frames_per_s": frames / dt, "cores": 1, "kind": kind,
+            "sample": f"{frames} raw 1080p frames, one process, second of two calls"}
+
+
 def run_secondary(dev, iters=10):
     """Parity-case configs timed as fused pipelines: clip kernel (token layout, bf16) -> tcgen05 GEMM.
     Reported beside the headline line; the GEMM alone is timed with an L2 flush between iterations."""
@@ -366,6 +389,33 @@ def run_secondary(dev, iters=10):
         out[name] = ent
         del vids, batch, tok, m
         torch.cuda.empty_cache()
+    # HF image processor applied to RAW 1080p frames (data_preprocessing.py:16 -- Pillow antialiased shortest-edge
+    # resize 256 + centre crop 224 + rescale/normalise): lvc_hf_clip_forward, timed alone with an L2 flush
+    B, T, n, h, w = 8, 32, 40, 1080, 1920
+    g = torch.Generator(device=dev).manual_seed(11)
+    vids = [torch.randint(0, 256, (n, h, w, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(B)]
+    idx = np.stack([np.sort(np.random.default_rng(b).integers(0, n, T)) for b in range(B)]).astype(np.int32)
+    cb = ClipBuilder("vivit_raw", num_frames=T)
+    batch = cb.prepare(vids, idx)
+    clip = torch.empty(batch.shape, dtype=torch.float32, device=dev)
+    ts = []
+    for _ in range(3 + iters):
+        flush.zero_()
+        torch.cuda._sleep(400000)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        cb.run(batch, clip)
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ms = statistics.median(ts[3:])
+    side = 224.0 / 256.0 * h   # the crop's footprint in the source
+    alg = B * T * (side * side * 3 + 224 * 224 * 3 * 4)
+    out["hf_raw_1080p"] = {"source": "VivitImageProcessor on raw 1080p frames, 8 clips x 32 frames (data_preprocessing.py:16)",
+                           "kernel": "lvc_pil_kernel", "kernel_ms": ms, "clips_per_s": B / (ms * 1e-3),
+                           "algorithmic_gb_per_s": alg / ms / 1e6, "bound": "issue (integer MAC + LDS.U8), see DESIGN.md 4.7"}
+    del vids, batch, clip
+    torch.cuda.empty_cache()
     return out
 
 
@@ -450,6 +500,8 @@ def main():
                 line["secondary"][name]["cpu_reference"] = {
                     "clips_per_s": both, "clip_recipe_clips_per_s": clip_rate, "embed_ms_per_batch": emb_ms, "cores": cores,
                     "sample": f"{cores} single-thread workers x 1 clip, median of 2; fp32 torch embed on {cores} threads, median of 2"}
+        if not args.no_cpu_baseline and "hf_raw_1080p" in line["secondary"]:
+            line["secondary"]["hf_raw_1080p"]["cpu_reference"] = _hf_raw_cpu()
     if not args.no_cpu_baseline:
         from oracle import cpu_baseline as cbm
 

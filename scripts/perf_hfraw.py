@@ -25,6 +25,9 @@ def run(preset, shape, B=8, T=32, n=40, iters=20):
     alg = B * T * (side * side * 3 + 224 * 224 * 3 * 4)
     print(f"{preset:16s} {h}x{w} B={B} T={T}: {ms:.3f} ms  {B / ms * 1e3:.0f} clips/s  {alg / ms / 1e6:.0f} GB/s algorithmic")
 
-for preset in ("vivit_raw", "timesformer_raw"):
-    for shape in ((1080, 1920), (720, 1280), (480, 640), (256, 340)):
-        run(preset, shape)
+if len(sys.argv) > 1:   # one configuration (for ncu): preset H W
+    run(sys.argv[1], (int(sys.argv[2]), int(sys.argv[3])), iters=2)
+else:
+    for preset in ("vivit_raw", "timesformer_raw"):
+        for shape in ((1080, 1920), (720, 1280), (480, 640), (256, 340)):
+            run(preset, shape)
