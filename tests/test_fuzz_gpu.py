@@ -33,3 +33,12 @@ def test_randomised_detector_pre_post_sweep():
                        text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "40/40 cases match" in r.stdout
+
+
+def test_randomised_raw_processor_sweep():
+    """Random frame sizes (1 px to 4K, portrait, odd), mixed per batch, both HF presets, edges 224/256/300."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "fuzz_hfraw.py"), "30", "17"], capture_output=True,
+                       text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "30/30 cases match" in r.stdout
