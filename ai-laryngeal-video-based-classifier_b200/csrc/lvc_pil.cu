@@ -69,6 +69,7 @@ __device__ Taps pil_taps(int xx, int in_size, int out_size, int* kk, int stride,
     const double k = ww != 0.0 ? __ddiv_rn(w[x], ww) : w[x];
     kk[x * stride] = (int)(k < 0.0 ? __dadd_rn(-0.5, __dmul_rn(k, 4194304.0)) : __dadd_rn(0.5, __dmul_rn(k, 4194304.0)));
   }
+  for (int x = n; x < kt; ++x) kk[x * stride] = 0;   // the passes run a fixed tap count: padding taps weigh nothing
   Taps t; t.xmin = xmin; t.n = n;
   return t;
 }
@@ -89,9 +90,10 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
+template <int NT>   // taps per sample held in the tables (>= 2*ceil(scale) + 1), fully unrolled in both passes
 __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_constant__ PilParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
-  const int kt = p.kt;
+  constexpr int kt = NT;
   int* hk = reinterpret_cast<int*>(smem);                 // [kt][S]  horizontal weights, tap-major
   int* vk = hk + kt * S;                                  // [kt][S]  vertical weights of the 224 cropped rows
   int* hmin = vk + kt * S;                                // [S] first source column / tap count per output column
@@ -195,12 +197,11 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
                               rsh[(q & 1) * kCH + lane];
         uint32_t* irow = inter + (size_t)(r % p.ir) * IP;
         for (int x = xa + warp; x < xa + xseg; x += kWarps) {
-          const int n = hn[x];
           const uint8_t* src = rowp + (hmin[x] - c0) * 3;
           const int* k = hk + x;
           int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-#pragma unroll 4
-          for (int i = 0; i < n; ++i) {
+#pragma unroll
+          for (int i = 0; i < NT; ++i) {
             const int kv = k[i * S];
             a0 += src[3 * i] * kv; a1 += src[3 * i + 1] * kv; a2 += src[3 * i + 2] * kv;
           }
@@ -215,14 +216,13 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
         int ne = next_emit;
         while (ne < oy1 && vmin[ne] + vn[ne] <= done) ++ne;
         for (int oy = next_emit + warp; oy < ne; oy += kWarps) {
-          const int n = vn[oy];
           const int* k = vk + oy;
           const int s0 = vmin[oy] % p.ir;
           for (int x = lane; x < S; x += 32) {
             int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
             int sl = s0;
-#pragma unroll 4
-            for (int i = 0; i < n; ++i) {
+#pragma unroll
+            for (int i = 0; i < NT; ++i) {
               const uint32_t w = inter[(size_t)sl * IP + x];
               const int kv = k[i * S];
               a0 += (int)(w & 0xffu) * kv; a1 += (int)((w >> 8) & 0xffu) * kv; a2 += (int)((w >> 16) & 0xffu) * kv;
@@ -255,6 +255,14 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
     }
     cp_async_wait0();
   }
+}
+
+template <int NT>
+int pil_launch(const PilParams& p, int grid, int threads, size_t smem, void* stream) {
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_pil_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lvc_pil_kernel<NT><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
 }
 
 int pil_device(int* sms, int* max_smem) {
@@ -295,12 +303,16 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
   // most a factor (1 + 1/E).  The tap tables hold 2*ceil(scale) + 1 <= KT entries per sample.
   const double scale = std::max(1.0, (double)std::min(d->max_width, max_height) / (double)shortest_edge * (1.0 + 1.0 / shortest_edge));
   const int cs = (int)std::ceil(scale);
-  if (2 * cs + 1 > KT) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: down-scale %.2f needs more than %d taps", scale, KT);
+  if (std::ceil(2.0 * scale) > KT - 1) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: down-scale %.2f needs more than %d taps", scale, KT);
   PilParams p{};
   p.videos = videos; p.indices = indices; p.lut = lut; p.out = out;
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype; p.bgr = d->src_order == LVC_SRC_BGR;
   p.edge = shortest_edge; p.kt_tok = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
-  p.kt = 2 * cs + 1;
+  // a sample's window [int(c - s + .5), int(c + s + .5)) holds fewer than 2s + 1, i.e. at most ceil(2s), samples
+  static const int kTapSteps[] = {2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 15, 17, 19, 21, 23};
+  const int need_taps = (int)std::ceil(2.0 * scale);
+  p.kt = 23;
+  for (int i = 16; i >= 0; --i) if (kTapSteps[i] >= need_taps) p.kt = kTapSteps[i];
   p.ir = kCH + p.kt + 1;
   // Column segments: the fewest that keep a CTA's footprint under 128 KB (measured best on B200: larger stages
   // gain nothing, smaller ones pay more barriers and overlap columns).
@@ -317,7 +329,7 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
       const int span_px = std::min((int)(xs * scale) + 2 * cs + 3, d->max_width);
       int pw = (span_px * 3 + 6) / 4 + 1;
       pw |= 1;
-      const size_t need = fixed + (size_t)2 * kCH * pw * 4;
+      const size_t need = fixed + (size_t)2 * kCH * pw * 4 + 128;   // slack: padding taps read past the last staged row
       if (need <= (pass == 0 ? (size_t)128 * 1024 : (size_t)max_smem)) {
         pick = i; p.nseg = kSegs[i]; p.pitch_words = pw; smem = need;
         break;
@@ -342,9 +354,13 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
     if (nb > 0 && S % nb == 0) { p.bands = nb; p.R = S / nb; }
   }
   p.total_items = frames * p.bands;
-  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_pil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = std::min(p.total_items, slots);
-  lvc_pil_kernel<<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(p);
-  LVC_CUDA_TRY(cudaGetLastError());
-  return LVC_OK;
+  switch (p.kt) {
+#define LVC_PIL_CASE(N) case N: return pil_launch<N>(p, grid, threads, smem, stream);
+    LVC_PIL_CASE(2) LVC_PIL_CASE(3) LVC_PIL_CASE(4) LVC_PIL_CASE(5) LVC_PIL_CASE(6) LVC_PIL_CASE(7) LVC_PIL_CASE(8) LVC_PIL_CASE(9)
+    LVC_PIL_CASE(10) LVC_PIL_CASE(11) LVC_PIL_CASE(12) LVC_PIL_CASE(13) LVC_PIL_CASE(15) LVC_PIL_CASE(17)
+    LVC_PIL_CASE(19) LVC_PIL_CASE(21)
+#undef LVC_PIL_CASE
+    default: return pil_launch<23>(p, grid, threads, smem, stream);
+  }
 }
