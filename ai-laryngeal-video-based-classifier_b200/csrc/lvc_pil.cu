@@ -87,7 +87,6 @@ __device__ __forceinline__ void cp_async4s(uint32_t dst_shared, const void* src)
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_shared), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 template <int NT>   // taps per sample held in the tables (>= 2*ceil(scale) + 1), fully unrolled in both passes
@@ -183,10 +182,11 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
     cp_async_commit();
     int next_emit = oy0;
     for (int q = 0; q < nchunk; ++q) {
-      if (q + 1 < nchunk) issue(q + 1);
+      cp_async_wait0();
+      __syncthreads();   // chunk q landed (every thread's copies), rsh[] is visible; everyone is past chunk q-1:
+                         // its slot may be refilled and the ring rows its vertical pass read may be overwritten
+      if (q + 1 < nchunk) issue(q + 1);   // overlaps the passes below
       cp_async_commit();
-      cp_async_wait1();
-      __syncthreads();   // chunk q landed (every thread's copies) and rsh[] is visible
       const int rb = q / p.nseg, seg = q - rb * p.nseg;
       const int xa = seg * xseg;
       const int c0 = hmin[xa];
@@ -251,7 +251,6 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
         }
         next_emit = ne;
       }
-      __syncthreads();   // slot q & 1 and the ring rows just read are free again
     }
     cp_async_wait0();
   }
@@ -314,8 +313,8 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
   p.kt = 23;
   for (int i = 16; i >= 0; --i) if (kTapSteps[i] >= need_taps) p.kt = kTapSteps[i];
   p.ir = kCH + p.kt + 1;
-  // Column segments: the fewest that keep a CTA's footprint under 128 KB (measured best on B200: larger stages
-  // gain nothing, smaller ones pay more barriers and overlap columns).
+  // Column segments: the fewest that keep a CTA under 128 KB -- tuned on B200 over 480p / 720p / 1080p at both
+  // edges: bigger stages gain nothing, smaller ones add barriers and column overlap (LVC_PIL_NSEG overrides).
   const size_t fixed = (size_t)(2 * p.kt * S + 4 * S + 2 * kCH + 768) * 4 + (size_t)p.ir * IP * 4;
   static const int kSegs[] = {1, 2, 4, 7, 14, 28};
   size_t smem = 0;

@@ -413,7 +413,7 @@ def run_secondary(dev, iters=10):
     alg = B * T * (side * side * 3 + 224 * 224 * 3 * 4)
     out["hf_raw_1080p"] = {"source": "VivitImageProcessor on raw 1080p frames, 8 clips x 32 frames (data_preprocessing.py:16)",
                            "kernel": "lvc_pil_kernel", "kernel_ms": ms, "clips_per_s": B / (ms * 1e-3),
-                           "algorithmic_gb_per_s": alg / ms / 1e6, "bound": "issue (integer MAC + LDS.U8), see DESIGN.md 4.7"}
+                           "algorithmic_gb_per_s": alg / ms / 1e6, "bound": "issue (integer MAC + LDS.U8), see DESIGN.md 4.6"}
     del vids, batch, clip
     torch.cuda.empty_cache()
     return out
