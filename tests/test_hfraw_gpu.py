@@ -112,3 +112,40 @@ def test_errors():
     big = torch.zeros((1, 224 * 13, 224 * 13, 3), dtype=torch.uint8, device="cuda")   # 13x down-scale: > 24 taps
     with pytest.raises(ValueError):
         ClipBuilder("timesformer_raw", num_frames=1)([big], [[0]])
+
+
+def test_raw_frames_to_vivit_embeddings_graph_pipeline():
+    """data_preprocessing.py:16 followed by the model's first layer: raw 360p frames -> VivitImageProcessor geometry
+    (token layout) -> tubelet GEMM + cls / position embeddings, replayed as one CUDA graph; against transformers'
+    processor + VivitEmbeddings on the CPU (fp32)."""
+    tr = pytest.importorskip("transformers")
+    from transformers.models.vivit.modeling_vivit import VivitEmbeddings as HF
+
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.patch_embed import VivitEmbeddings
+    from lvc_b200.pipeline import ClipEmbedPipeline
+
+    T, B = 8, 2
+    cfg = tr.VivitConfig(num_frames=T, hidden_dropout_prob=0.0)
+    ref = HF(cfg).eval()
+    g = torch.Generator().manual_seed(5)
+    for p in ref.parameters():
+        p.data = torch.randn(p.shape, generator=g) * 0.05
+    mine = VivitEmbeddings(cfg, out_dtype=torch.float32)
+    mine.load_state_dict(ref.state_dict(), strict=True)
+    mine = mine.cuda()
+    vids = [_frames((360, 640), 12, seed=40 + b) for b in range(B)]
+    dv = [torch.from_numpy(v).cuda() for v in vids]
+    cb = ClipBuilder("vivit_raw", num_frames=T, layout="TOKENS", patch=(2, 16, 16))
+    pipe = ClipEmbedPipeline(cb, mine.patch_embeddings, dv, T, embeddings=mine)
+    proc = tr.VivitImageProcessor()
+    for trial in range(2):
+        idx = np.random.default_rng(trial).integers(0, 12, (B, T))
+        got = pipe(idx).float().cpu()
+        px = torch.cat([proc(list(v[idx[b]]), return_tensors="pt")["pixel_values"] for b, v in enumerate(vids)])
+        with torch.no_grad():
+            want = ref(px)
+        assert got.shape == want.shape
+        err = (got - want).abs().max() / want.abs().max()
+        l2 = (got - want).norm() / want.norm()
+        assert err <= 1e-2 and l2 <= 1e-2, (float(err), float(l2))   # north_star: 1e-2 relative for the embeds (bf16 operands)
