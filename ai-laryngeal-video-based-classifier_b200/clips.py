@@ -106,8 +106,9 @@ class ClipBuilder:
             raise ValueError("float_frames applies to the cv2.resize presets only")
         # *_raw presets: the HF processor's own resize (size={"shortest_edge": E}) on frames of any size
         self.shortest_edge = int(shortest_edge if shortest_edge is not None else HF_SHORTEST_EDGE.get(preset, 0))
-        if rs == _lib.RESAMPLE_PIL_SHORT and self.shortest_edge < 224:
-            raise ValueError("shortest_edge must be >= 224 (a smaller resize would make the centre crop pad)")
+        # shortest_edge=0: size={"height": 224, "width": 224} -- both axes to 224, aspect not kept
+        if rs == _lib.RESAMPLE_PIL_SHORT and self.shortest_edge != 0 and self.shortest_edge < 224:
+            raise ValueError("shortest_edge must be 0 (exact 224x224) or >= 224 (a smaller resize would make the centre crop pad)")
         # layout="TOKENS": write the bf16 patch matrix A[M][K] of a (kt,kh,kw) patch embedding directly
         self.patch = tuple(int(v) for v in patch) if patch is not None else (0, 0, 0)
         if self.layout == "TOKENS":

@@ -76,7 +76,8 @@ __device__ Taps pil_taps(int xx, int in_size, int out_size, int* kk, int stride,
 
 // HF get_resize_output_image_size(shortest_edge = E, default_to_square = False): python int(E * long / short)
 __device__ __forceinline__ void hf_geom(int H, int W, int E, int& nh, int& nw) {
-  if (H <= W) { nh = E; nw = (int)__ddiv_rn((double)(E * (long long)W), (double)H); }
+  if (E == 0) { nh = S; nw = S; }   // size = {"height": 224, "width": 224}: both axes to 224, aspect not kept
+  else if (H <= W) { nh = E; nw = (int)__ddiv_rn((double)(E * (long long)W), (double)H); }
   else { nw = E; nh = (int)__ddiv_rn((double)(E * (long long)H), (double)W); }
 }
 
@@ -279,7 +280,7 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
                                    void* stream) {
   if (!d || !videos || !indices || !out) return lvc_fail(LVC_E_INVAL, "lvc_hf_clip_forward: NULL argument");
   if (d->out_size != S) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: out_size %d unsupported (224 only)", d->out_size);
-  if (shortest_edge < S) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: shortest_edge %d < crop %d (the processor would pad)", shortest_edge, S);
+  if (shortest_edge != 0 && shortest_edge < S) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: shortest_edge %d < crop %d (the processor would pad)", shortest_edge, S);
   if (d->batch <= 0 || d->num_frames <= 0 || d->max_width <= 0 || max_height <= 0)
     return lvc_fail(LVC_E_INVAL, "lvc_hf_clip_forward: batch, num_frames, max_width and max_height must be positive");
   if (d->layout < LVC_LAYOUT_BTCHW || d->layout > LVC_LAYOUT_TOKENS || d->out_dtype < LVC_DT_F32 || d->out_dtype > LVC_DT_U8)
@@ -300,7 +301,9 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
 
   // Down-scale bound: short side <= min(max_w, max_h); the long side's scale W / int(E*W/H) exceeds short/E by at
   // most a factor (1 + 1/E).  The tap tables hold 2*ceil(scale) + 1 <= KT entries per sample.
-  const double scale = std::max(1.0, (double)std::min(d->max_width, max_height) / (double)shortest_edge * (1.0 + 1.0 / shortest_edge));
+  const double scale = shortest_edge == 0
+      ? std::max(1.0, (double)std::max(d->max_width, max_height) / S)   // exact 224 x 224: each axis has its own scale
+      : std::max(1.0, (double)std::min(d->max_width, max_height) / (double)shortest_edge * (1.0 + 1.0 / shortest_edge));
   const int cs = (int)std::ceil(scale);
   if (std::ceil(2.0 * scale) > KT - 1) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: down-scale %.2f needs more than %d taps", scale, KT);
   PilParams p{};

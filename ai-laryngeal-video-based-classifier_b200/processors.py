@@ -64,23 +64,26 @@ class _ClipProcessor:
     def __init__(self, image_mean=None, image_std=None, device=None, **ignored):
         # the reference passes extra kwargs (num_frames, image_size, patch_size) the HF class ignores
         self.image_mean, self.image_std = image_mean, image_std
-        self.size = {"height": 224, "width": 224}
+        # settable like the HF attributes (timesformer .../trainers/trainer.py:23-24 assigns height/width = 224)
+        self.size = {"shortest_edge": self.shortest_edge}
         self.crop_size = {"height": 224, "width": 224}
         self.device = device
         self._builders = {}
 
-    def _builder(self, T, raw=False):
-        if (T, raw) not in self._builders:
-            self._builders[T, raw] = ClipBuilder(self.raw_preset if raw else self.preset, num_frames=T,
-                                                 mean=self.image_mean, std=self.image_std, device=self.device,
-                                                 shortest_edge=self.shortest_edge if raw else None)
-        return self._builders[T, raw]
+    def _builder(self, T, raw=False, exact=False):
+        key = (T, raw, exact)
+        if key not in self._builders:
+            self._builders[key] = ClipBuilder(self.raw_preset if raw else self.preset, num_frames=T,
+                                              mean=self.image_mean, std=self.image_std, device=self.device,
+                                              shortest_edge=(0 if exact else self.shortest_edge) if raw else None)
+        return self._builders[key]
 
     def _check(self, kw):
         for key in ("size", "crop_size"):
-            v = kw.get(key)
-            if v is not None and (v.get("height", 224) != 224 or v.get("width", 224) != 224):
-                raise NotImplementedError(f"{key}={v}: only 224x224 is supported")
+            v = kw.get(key) or getattr(self, key)
+            if v.get("height", 224) != 224 or v.get("width", 224) != 224 or \
+                    v.get("shortest_edge", self.shortest_edge) != self.shortest_edge:
+                raise NotImplementedError(f"{key}={v}: only 224x224 or shortest_edge={self.shortest_edge} is supported")
         for key in ("do_resize", "do_center_crop", "do_rescale", "do_normalize"):
             if kw.get(key) is False:
                 raise NotImplementedError(f"{key}=False: the fused kernel always runs the whole chain")
@@ -98,11 +101,10 @@ class _ClipProcessor:
             raise ValueError("all videos of a batch must have the same number of frames")
         idx = np.tile(np.arange(T, dtype=np.int32), (len(vids), 1))
         raw = any(tuple(v.shape[1:3]) != (224, 224) for v in vids)
-        if raw and "height" in (kw.get("size") or {}):
-            # size={"height", "width"} on other sizes is an aspect-changing Pillow resize: not fused
-            raise NotImplementedError("size={'height': 224, 'width': 224} is fused for 224x224 frames only; "
-                                      "omit `size` for the processor's shortest-edge geometry")
-        return BatchFeature(pixel_values=self._builder(T, raw)(vids, idx))
+        # size={"height": 224, "width": 224} (given per call, or set on the instance as timesformer
+        # .../trainers/trainer.py:23-24 does) on other sizes: Pillow resizes both axes to 224, aspect not kept
+        exact = raw and "height" in (kw.get("size") or self.size)
+        return BatchFeature(pixel_values=self._builder(T, raw, exact)(vids, idx))
 
     preprocess = __call__
 
@@ -115,10 +117,6 @@ class VivitImageProcessor(_ClipProcessor):
     raw_preset = "vivit_raw"
     shortest_edge = 256
 
-    def _check(self, kw):
-        super()._check(kw)
-        if kw.get("size") not in (None, {"shortest_edge": 256}) and "height" not in (kw.get("size") or {}):
-            raise NotImplementedError("only the default shortest_edge=256 geometry is fused")
 
 
 class TimesformerImageProcessor(_ClipProcessor):

@@ -197,7 +197,9 @@ int lvc_clip_forward_aug(const lvc_clip_desc* desc, const lvc_video* videos, con
  * timesformer_transformer/data_preprocessing_timesformer.py:16, vivit_transformer/inference.py:187):
  * resize(shortest_edge) with PIL BILINEAR -- Pillow widens the triangle filter with the down-scale and rounds to
  * uint8 after each of its two passes -- centre crop 224, rescale + normalise (the LUT), layout.
- *   shortest_edge  256 for VivitImageProcessor, 224 for the VideoMAE-class processor; >= 224
+ *   shortest_edge  256 for VivitImageProcessor, 224 for the VideoMAE-class processor; >= 224.  0 = the call form
+ *                  `size={"height": 224, "width": 224}` (timesformer .../trainers/trainer.py:91-98): both axes are
+ *                  resized to 224 independently (aspect not kept), the crop is the identity
  *   max_height     largest frame height among the B videos (with desc->max_width it sizes the shared-memory
  *                  buffers; a larger video is a contract violation and traps).  Down-scales up to 11.5x.
  * desc->resample is ignored (LVC_RESAMPLE_PIL_SHORT implied), desc->src_float must be 0; no ROI boxes, no stats.

@@ -89,6 +89,14 @@ def hf_shortest_edge_crop_u8(frames, edge, crop=224):
     return np.stack([pil_resize_bilinear_u8(frames[t], nh, nw)[top : top + crop, left : left + crop] for t in range(T)])
 
 
+def videomae_processor_exact(frames, mean=(0.45, 0.45, 0.45), std=(0.225, 0.225, 0.225)):
+    """The call form of timesformer .../trainers/trainer.py:91-98 on frames that are NOT 224x224:
+    ``size={"height": 224, "width": 224}`` resizes both axes to 224 with Pillow BILINEAR (aspect not kept), the
+    224 crop is the identity; then ``videomae_processor``'s rescale + normalise."""
+    frames = np.asarray(frames)
+    return videomae_processor(np.stack([pil_resize_bilinear_u8(f, 224, 224) for f in frames]), mean, std)
+
+
 def videomae_processor_raw(frames, mean=(0.45, 0.45, 0.45), std=(0.225, 0.225, 0.225), edge=224):
     """VideoMAEImageProcessor defaults of the TimeSformer checkpoint on raw frames: shortest edge 224
     (Pillow BILINEAR), centre crop 224, then ``videomae_processor``'s rescale + normalise."""

@@ -43,3 +43,15 @@ def test_pil_many_taps_vs_pillow():
         img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
         ref = np.asarray(Image.fromarray(img).resize((ow, oh), Image.BILINEAR))
         assert np.array_equal(pil_resize_bilinear_u8(img, oh, ow), ref)
+
+
+@pytest.mark.parametrize("shape", [(720, 1280), (300, 200), (231, 517)])
+def test_oracle_vs_hf_exact_224(shape):
+    """size={"height": 224, "width": 224} on frames of another size (aspect-changing Pillow resize)."""
+    tr = pytest.importorskip("transformers")
+    frames = np.random.default_rng(shape[0]).integers(0, 256, (2,) + shape + (3,), dtype=np.uint8)
+    mean, std = (0.45, 0.45, 0.45), (0.225, 0.225, 0.225)
+    proc = tr.VivitImageProcessor(size={"height": 224, "width": 224}, crop_size={"height": 224, "width": 224},
+                                  offset=False, rescale_factor=1 / 255, image_mean=list(mean), image_std=list(std))
+    ref = proc(list(frames), return_tensors="np")["pixel_values"][0]
+    assert np.array_equal(op.videomae_processor_exact(frames, mean, std), ref)

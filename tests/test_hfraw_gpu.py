@@ -97,8 +97,19 @@ def test_processor_dropin_vs_transformers(shape):
     ref = legacy(list(fr), return_tensors="pt")["pixel_values"]
     got = lvc_b200.TimesformerImageProcessor(image_mean=mean, image_std=std)(list(fr), return_tensors="pt")["pixel_values"]
     assert torch.equal(got.cpu(), ref)
+    # the trainer's call form (size / crop_size = 224 x 224, trainer.py:91-98) on frames of another size:
+    # Pillow resizes both axes to 224, aspect not kept
+    exact = tr.VivitImageProcessor(size={"height": 224, "width": 224}, crop_size={"height": 224, "width": 224},
+                                   offset=False, rescale_factor=1 / 255, image_mean=mean, image_std=std)
+    ref = exact(list(fr), return_tensors="pt")["pixel_values"]
+    mine = lvc_b200.TimesformerImageProcessor(image_mean=mean, image_std=std)
+    got = mine(images=list(fr), return_tensors="pt", do_resize=True, size={"height": 224, "width": 224},
+               do_center_crop=True, crop_size={"height": 224, "width": 224})["pixel_values"]
+    assert torch.equal(got.cpu(), ref)
+    mine.size = {"height": 224, "width": 224}   # trainer.py:23
+    assert torch.equal(mine(list(fr), return_tensors="pt")["pixel_values"].cpu(), ref)
     with pytest.raises(NotImplementedError):
-        lvc_b200.TimesformerImageProcessor()(list(fr), size={"height": 224, "width": 224})
+        mine(list(fr), size={"height": 256, "width": 256})
 
 
 def test_errors():
