@@ -252,6 +252,9 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   float* lut = reinterpret_cast<float*>(smem + kLutOff);
   uint8_t* ring = smem + p.ring_off;
 
+  // a kernel launched behind this one with programmatic stream serialization (the patch-embedding GEMM) may be
+  // scheduled as SMs free up; it waits for this grid to complete before it touches global data
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const int stages_per_item = MODE == MODE_VIVIT ? p.v_stages : p.rows_per_band / p.rps;

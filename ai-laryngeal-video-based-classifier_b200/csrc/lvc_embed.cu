@@ -14,6 +14,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
+#include <utility>
 
 #include <algorithm>
 #include <cstdint>
@@ -522,6 +523,11 @@ lvc_embed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
 // (MMA issuer stalls on the `full` barriers), this cuts the feed by a third and deepens the ring.
 namespace {
 
+// Programmatic dependent launch: the kernel may start while its predecessor in the stream is still running (its
+// prologue overlaps the predecessor's tail); nothing the predecessor wrote may be read, and nothing it may still read
+// may be overwritten, before this returns.  A no-op when the launch carries no programmatic-serialization attribute.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t cluster_rank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -603,6 +609,7 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
   cluster_sync_all();   // peer barriers are initialised before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();       // everything above touched no global data
 
   if (EMB && warp == 0) {
     // row 0 of every batch entry: cls_token + position_embeddings[0] (time embeddings do not touch it)
@@ -839,6 +846,17 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   float* s_bias = reinterpret_cast<float*>(smem_a + (size_t)p.stages * a_bytes + 512);
   float* s_lnw = s_bias + N;
   float* s_lnb = s_lnw + N;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_o);
+    for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
+    for (int a = 0; a < NG; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
+    mb_init(b_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  griddep_wait();   // barrier set-up and the TMEM allocation overlap the previous kernel's tail; parameters do not
   for (int i = threadIdx.x; i < N; i += kSwinThreads) {
     s_lnw[i] = p.do_ln ? p.ln_w[i] : 1.f;
     s_lnb[i] = p.do_ln ? p.ln_b[i] : 0.f;
@@ -857,16 +875,6 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   for (int i = threadIdx.x; i < BM * 64 / 16; i += kSwinThreads)
     reinterpret_cast<uint4*>(smem_ones)[i] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
   fence_async_smem();   // generic-proxy writes above are read by the tensor core (async proxy)
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&map_a);
-    tma_prefetch_desc(&map_b);
-    tma_prefetch_desc(&map_o);
-    for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
-    for (int a = 0; a < NG; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
-    mb_init(b_full, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -1075,6 +1083,20 @@ int env_i(const char* name, int dflt) {
   return (v && *v) ? atoi(v) : dflt;
 }
 
+// Launch with programmatic stream serialization: the grid may be scheduled while the previous kernel in the stream
+// (the clip kernel of a pipeline, the im2col pass) drains; the kernels call griddep_wait() before touching global data.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = env_i("LVC_NO_PDL", 0) ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 }  // namespace
 
 extern "C" int64_t lvc_patch_embed_workspace(const lvc_embed_desc* d) {
@@ -1228,10 +1250,10 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
     const int pairs = std::min(sms / 2, p.m_tiles * p.n_tiles);
     if (et.mode) {
       LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-      lvc_embed_gemm2_kernel<true><<<2 * pairs, kGemm2Threads, smem2, st>>>(ma, mb, mo, p);
+      LVC_CUDA_TRY(launch_pdl(lvc_embed_gemm2_kernel<true>, 2 * pairs, kGemm2Threads, smem2, st, ma, mb, mo, p));
     } else {
       LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_gemm2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-      lvc_embed_gemm2_kernel<false><<<2 * pairs, kGemm2Threads, smem2, st>>>(ma, mb, mo, p);
+      LVC_CUDA_TRY(launch_pdl(lvc_embed_gemm2_kernel<false>, 2 * pairs, kGemm2Threads, smem2, st, ma, mb, mo, p));
     }
     LVC_CUDA_TRY(cudaGetLastError());
     return LVC_OK;
@@ -1254,10 +1276,10 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
       p.tmem_cols = 512;  // kSwinGroups accumulators of N columns
       if (p.out_f32) {
         LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-        lvc_embed_swin_kernel<4, true><<<grid3, kSwinThreads, smem3, st>>>(ma, mb, mo, p);
+        LVC_CUDA_TRY(launch_pdl(lvc_embed_swin_kernel<4, true>, grid3, kSwinThreads, smem3, st, ma, mb, mo, p));
       } else {
         LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-        lvc_embed_swin_kernel<4, false><<<grid3, kSwinThreads, smem3, st>>>(ma, mb, mo, p);
+        LVC_CUDA_TRY(launch_pdl(lvc_embed_swin_kernel<4, false>, grid3, kSwinThreads, smem3, st, ma, mb, mo, p));
       }
       LVC_CUDA_TRY(cudaGetLastError());
       return LVC_OK;

@@ -104,6 +104,9 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
   float* lut = reinterpret_cast<float*>(rsh + 2 * kCH);   // [3*256]
   uint32_t* inter = reinterpret_cast<uint32_t*>(lut + 768);            // [ir][IP] ring of horizontally resized rows
   uint32_t* rows = inter + (size_t)p.ir * IP;                          // [2][kCH][pitch_words]
+  // a kernel launched behind this one with programmatic stream serialization (the patch-embedding GEMM) may be
+  // scheduled as SMs free up; it waits for this grid to complete before it touches global data
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kThreads = blockDim.x, kWarps = kThreads >> 5;
   if (p.lut)
