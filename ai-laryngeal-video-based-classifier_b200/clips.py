@@ -151,6 +151,8 @@ class ClipBuilder:
             resident = v.is_cuda or (self.allow_pinned_host and v.is_pinned())
             if v.dtype != torch.uint8 or v.dim() != 4 or v.shape[-1] != 3 or not resident or not v.is_contiguous():
                 raise ValueError("each video must be a contiguous CUDA uint8 tensor of shape (N, H, W, 3)")
+            if min(v.shape[:3]) < 1:   # the reference raises on a video without frames (vivit .../dataset.py:217)
+                raise ValueError(f"video {i} has no frames or an empty frame: shape {tuple(v.shape)}")
             if v.data_ptr() % 16:
                 raise ValueError("video storage must be 16-byte aligned")
             vt[i].base, vt[i].nbytes = v.data_ptr(), v.numel()

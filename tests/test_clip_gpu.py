@@ -153,6 +153,8 @@ def test_edge_cases_empty_ragged_short_and_out_of_range():
         cb([dev[0].float()], [idx[0]])
     with pytest.raises(ValueError):
         ClipBuilder("nope")
+    with pytest.raises(ValueError):   # a video without frames (the reference raises too, vivit .../dataset.py:217)
+        cb([torch.empty((0, 120, 160, 3), dtype=torch.uint8, device="cuda")], [list(range(16))])
 
 
 def test_full_size_properties_1080p():
