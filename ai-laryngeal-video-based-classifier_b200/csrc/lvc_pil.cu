@@ -143,8 +143,7 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
     const int nchunk = nblk * p.nseg;
 
     // stage chunk q = (row block, column segment) into slot q & 1 with 4-byte async copies
-    auto issue = [&](int q) {
-      const int rb = q / p.nseg, seg = q - rb * p.nseg;
+    auto issue = [&](int q, int rb, int seg) {
       const int xa = seg * xseg, xb = xa + xseg;
       const int c0 = hmin[xa], c1 = hmin[xb - 1] + hn[xb - 1];
       const int span = (c1 - c0) * 3;
@@ -182,16 +181,20 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
       }
     };
 
-    issue(0);
+    issue(0, 0, 0);
     cp_async_commit();
     int next_emit = oy0;
+    int rb = 0, seg = 0;               // chunk q = (row block rb, column segment seg), tracked without divisions
+    int ring0 = r0 % p.ir;             // ring slot of the row block's first row
     for (int q = 0; q < nchunk; ++q) {
       cp_async_wait0();
       __syncthreads();   // chunk q landed (every thread's copies), rsh[] is visible; everyone is past chunk q-1:
                          // its slot may be refilled and the ring rows its vertical pass read may be overwritten
-      if (q + 1 < nchunk) issue(q + 1);   // overlaps the passes below
+      if (q + 1 < nchunk) {               // overlaps the passes below
+        const bool wrap = seg + 1 == p.nseg;
+        issue(q + 1, wrap ? rb + 1 : rb, wrap ? 0 : seg + 1);
+      }
       cp_async_commit();
-      const int rb = q / p.nseg, seg = q - rb * p.nseg;
       const int xa = seg * xseg;
       const int c0 = hmin[xa];
       const int r = r0 + rb * kCH + lane;   // this lane's source row
@@ -199,7 +202,9 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
       if (r < r1) {
         const uint8_t* rowp = reinterpret_cast<const uint8_t*>(rows + ((size_t)(q & 1) * kCH + lane) * p.pitch_words) +
                               rsh[(q & 1) * kCH + lane];
-        uint32_t* irow = inter + (size_t)(r % p.ir) * IP;
+        int rslot = ring0 + lane;
+        if (rslot >= p.ir) rslot -= p.ir;   // kCH <= ir: one wrap at most
+        uint32_t* irow = inter + (size_t)rslot * IP;
         for (int x = xa + warp; x < xa + xseg; x += kWarps) {
           const uint8_t* src = rowp + (hmin[x] - c0) * 3;
           const int* k = hk + x;
@@ -254,6 +259,12 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
           }
         }
         next_emit = ne;
+        ring0 += kCH;
+        if (ring0 >= p.ir) ring0 -= p.ir;
+        ++rb;
+        seg = 0;
+      } else {
+        ++seg;
       }
     }
     cp_async_wait0();
