@@ -1208,7 +1208,9 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
   p.do_ln = d->kind == LVC_EMBED_SWIN;
   p.out_f32 = d->out_dtype == LVC_DT_F32;
   p.out = out;
-  p.diag = env_i("LVC_GEMM_DIAG", 0);
+  // Directed-experiment knobs (scripts/gemm_probe.py): results are WRONG with any bit set and some combinations
+  // (2 | 4 with the embeddings epilogue) never terminate, so they need a second, explicit opt-in.
+  p.diag = env_i("LVC_PROFILING_KNOBS", 0) ? env_i("LVC_GEMM_DIAG", 0) : 0;
   p.diag_a = workspace;
   p.cls = et.cls; p.pos = et.pos; p.temb = et.temb; p.emb_mode = et.mode;
   p.emb_P = g.Ho * g.Wo * (et.mode == 1 ? g.To : 1);   // tokens per batch entry (ViViT) / per frame (TimeSformer)

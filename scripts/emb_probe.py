@@ -1,6 +1,8 @@
 """Times the fused-embeddings GEMM variants (profiling aid): python scripts/emb_probe.py"""
 import json
 import os
+
+os.environ["LVC_PROFILING_KNOBS"] = "1"  # opt in to the LVC_GEMM_DIAG experiment knobs
 import sys
 
 import torch

@@ -2,6 +2,8 @@
 python scripts/gemm_probe.py  -> one JSON line per (shape, knob) with CUDA-event medians."""
 import json
 import os
+
+os.environ["LVC_PROFILING_KNOBS"] = "1"  # opt in to the LVC_GEMM_DIAG experiment knobs
 import sys
 
 import torch

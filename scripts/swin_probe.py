@@ -1,6 +1,8 @@
 """Directed timing experiments on the short-K GEMM + LayerNorm kernel (profiling aid, GPU box only)."""
 import json
 import os
+
+os.environ["LVC_PROFILING_KNOBS"] = "1"  # opt in to the LVC_GEMM_DIAG experiment knobs
 import sys
 from functools import partial
 
