@@ -410,6 +410,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   int xo = 0, d1 = 0, a0 = 0, a1 = 0;
   float lx0 = 0.f, lx1 = 0.f;
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
+  const bool want_stats = p.stats != nullptr;
   int acc_b = -1;
   int slot = 0;
   uint32_t phase = 0;
@@ -533,7 +534,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             }
           }
         }
-        if (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw)) acc += (unsigned)(v[0] + v[1] + v[2]);  // bands: owned rows only
+        if (want_stats && (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw))) acc += (unsigned)(v[0] + v[1] + v[2]);  // bands: owned rows only
         if (MODE == MODE_VIVIT) {
           // Pillow horizontal pass of this row (224 -> cropped 224 of 256), rounded to uint8
           // (one word per pixel: a store and up to three loads per thread instead of 3 + 9 byte accesses)
