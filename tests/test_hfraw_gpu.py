@@ -63,6 +63,14 @@ def test_ragged_batch_layouts_bgr():
     B = len(vids)
     tok = x.view(B, 2, 2, 3, 14, 16, 14, 16).permute(0, 1, 4, 6, 3, 2, 5, 7).reshape(B * 2 * 196, 1536)
     assert torch.equal(out.cpu(), tok)
+    # TimeSformer operand: (B*T*14*14, 3*16*16), one frame per token group
+    out = ClipBuilder("vivit_raw", num_frames=4, layout="TOKENS", patch=(1, 16, 16))(dv, idx)
+    tok = x.view(B, 4, 3, 14, 16, 14, 16).permute(0, 1, 3, 5, 2, 4, 6).reshape(B * 4 * 196, 768)
+    assert torch.equal(out.cpu(), tok)
+    # Swin operand: (B*T/2*56*56, 3*2*4*4)
+    out = ClipBuilder("vivit_raw", num_frames=4, layout="TOKENS", patch=(2, 4, 4))(dv, idx)
+    tok = x.view(B, 2, 2, 3, 56, 4, 56, 4).permute(0, 1, 4, 6, 3, 2, 5, 7).reshape(B * 2 * 56 * 56, 96)
+    assert torch.equal(out.cpu(), tok)
     # BGR sources: the gather swaps channels
     dvb = [v.flip(-1).contiguous() for v in dv]
     out = ClipBuilder("vivit_raw", num_frames=4, src_order="BGR")(dvb, idx)
