@@ -13,6 +13,7 @@ OK, E_INVAL, E_SHAPE, E_CUDA, E_ALIGN, E_NOTSUP = 0, -1, -2, -3, -4, -5
 SAMPLE = {"uniform": 0, "random_window": 1, "random": 2}
 VARIANT_DATASET, VARIANT_CLAMPED, VARIANT_NUMPY_INFER = 0, 1, 2
 LUT_DIV, LUT_MUL64 = 0, 1
+HF_SRC_HOST = 1
 RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL, RESAMPLE_PIL_SHORT = 0, 1, 2, 3
 LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC, LAYOUT_TOKENS = 0, 1, 2, 3
 DT_F32, DT_BF16, DT_U8 = 0, 1, 2
@@ -71,6 +72,8 @@ _SIGS = {
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_hf_clip_forward": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p]),
+    "lvc_hf_clip_forward_ex": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_torch_randint": (C.c_int, [C.POINTER(Rng), C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "lvc_torch_rand": (C.c_float, [C.POINTER(Rng)]),
     "lvc_train_aug_draw": (C.c_int, [C.POINTER(Rng), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double,

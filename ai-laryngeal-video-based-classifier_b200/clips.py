@@ -67,6 +67,25 @@ def tapped_row_bytes(videos, indices, boxes, T, S=224):
     return int(total)
 
 
+def raw_crop_bytes(videos, T, edge, S=224):
+    """Bytes the raw-frame kernel fetches per batch: the source rows x columns the centre crop's filter windows
+    cover, per output frame (row segments are fetched 16-byte granular; this is the pixel count x 3)."""
+    total = 0
+    for v in videos:
+        h, w = int(v.shape[1]), int(v.shape[2])
+        if edge == 0:
+            nh = nw = S
+        elif h <= w:
+            nh, nw = edge, int(edge * w / h)
+        else:
+            nh, nw = int(edge * h / w), edge
+        sy, sx = max(h / nh, 1.0), max(w / nw, 1.0)
+        rows = min(h, int(S * h / nh + 2 * sy + 2))
+        cols = min(w, int(S * w / nw + 2 * sx + 2))
+        total += T * rows * cols * 3
+    return int(total)
+
+
 def _shape(layout, B, T, S=224, patch=None):
     if layout == "TOKENS":
         kt, kh, kw = patch
@@ -147,6 +166,7 @@ class ClipBuilder:
         hv = host.numpy()
         vt = (_lib.Video * B).from_buffer(hv)  # writes straight into the pinned buffer
         max_w = self._max_h = 0
+        self._host_src = False
         for i, v in enumerate(videos):
             resident = v.is_cuda or (self.allow_pinned_host and v.is_pinned())
             if v.dtype != torch.uint8 or v.dim() != 4 or v.shape[-1] != 3 or not resident or not v.is_contiguous():
@@ -157,6 +177,7 @@ class ClipBuilder:
                 raise ValueError("video storage must be 16-byte aligned")
             vt[i].base, vt[i].nbytes = v.data_ptr(), v.numel()
             vt[i].n_frames, vt[i].height, vt[i].width = v.shape[0], v.shape[1], v.shape[2]
+            self._host_src = self._host_src or not v.is_cuda
             max_w = max(max_w, v.shape[2])
             self._max_h = max(self._max_h, v.shape[1])
         hv[off_idx:off_idx + idx.nbytes] = idx.view(np.uint8).reshape(-1)
@@ -192,6 +213,7 @@ class ClipBuilder:
                        _shape(self.layout, B, T, patch=self.patch))
         cb.p_aug = self._p_aug
         cb.max_h = self._max_h
+        cb.host_src = self._host_src
         cb.dev_boxes = self._dev_boxes  # keeps the table alive
         return cb
 
@@ -205,9 +227,11 @@ class ClipBuilder:
         if self.resample == _lib.RESAMPLE_PIL_SHORT:
             if stats is not None:
                 raise ValueError("the *_raw presets have no checksum output")
-            st = _lib.lib().lvc_hf_clip_forward(C.byref(batch.desc), self.shortest_edge, batch.max_h, batch.p_vid,
-                                                batch.p_idx, self.lut.data_ptr() if self.lut is not None else None,
-                                                out.data_ptr(), stream)
+            # frames in pinned host memory: the kernel reads them over PCIe with row-granular bulk copies
+            flags = _lib.HF_SRC_HOST if getattr(batch, "host_src", False) else 0
+            st = _lib.lib().lvc_hf_clip_forward_ex(C.byref(batch.desc), self.shortest_edge, batch.max_h, flags, batch.p_vid,
+                                                   batch.p_idx, self.lut.data_ptr() if self.lut is not None else None,
+                                                   out.data_ptr(), stream)
             _lib.check(st, "lvc_hf_clip_forward")
             self.launches += 1
             return out
@@ -245,14 +269,17 @@ class ClipBuilder:
         (each distinct frame once), then run the kernel on the staged frames."""
         T = self.num_frames
         if zero_copy is None:
-            zero_copy = all((not v.is_cuda) and v.is_pinned() for v in host_videos) and self.resample not in (_lib.RESAMPLE_PTV_EVAL, _lib.RESAMPLE_PIL_SHORT)
+            zero_copy = all((not v.is_cuda) and v.is_pinned() for v in host_videos) and self.resample != _lib.RESAMPLE_PTV_EVAL
         if zero_copy:
             self.allow_pinned_host = True
             try:
                 res = self(host_videos, indices, boxes=boxes, out=out, stats=stats)
             finally:
                 self.allow_pinned_host = False
-            self.last_h2d_bytes = tapped_row_bytes(host_videos, indices, boxes, T)
+            if self.resample == _lib.RESAMPLE_PIL_SHORT:
+                self.last_h2d_bytes = raw_crop_bytes(host_videos, T, self.shortest_edge)
+            else:
+                self.last_h2d_bytes = tapped_row_bytes(host_videos, indices, boxes, T)
             return res
         idx = np.asarray(indices, dtype=np.int64).reshape(len(host_videos), T)
         staged, remap, h2d = [], [], 0

@@ -39,6 +39,7 @@ struct PilParams {
   int pitch_words;              // words per staged source-row segment (odd)
   int ir;                       // rows in the intermediate ring: kCH + kt + 1
   int kt_tok, kh, kw;           // LVC_LAYOUT_TOKENS: patch size (output = GEMM operand A[M][K], bf16)
+  int bulk;                     // rows staged with 16-byte-granular bulk copies (frames in pinned HOST memory, read over PCIe)
 };
 
 struct Taps { int xmin, n; };
@@ -87,6 +88,25 @@ __device__ __forceinline__ void cp_async4(void* dst, const void* src) {
 __device__ __forceinline__ void cp_async4s(uint32_t dst_shared, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst_shared), "l"(src) : "memory");
 }
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(s32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
+// 1-D bulk async copy global (or pinned host) -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(s32(dst)), "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -101,9 +121,12 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
   int* vmin = hn + S;                                     // [S] first source row / tap count per output row
   int* vn = vmin + S;
   int* rsh = vn + S;                                      // [2][kCH] byte shift of each staged row
-  float* lut = reinterpret_cast<float*>(rsh + 2 * kCH);   // [3*256]
+  uint64_t* full = reinterpret_cast<uint64_t*>(rsh + 2 * kCH);   // [2] bulk mode: bytes of a slot have landed
+  float* lut = reinterpret_cast<float*>(full + 2);          // [3*256]
   uint32_t* inter = reinterpret_cast<uint32_t*>(lut + 768);            // [ir][IP] ring of horizontally resized rows
-  uint32_t* rows = inter + (size_t)p.ir * IP;                          // [2][kCH][pitch_words]
+  // [2][kCH][pitch_words], 16-byte aligned (bulk copies land here)
+  const size_t rows_off = ((size_t)(reinterpret_cast<uint8_t*>(inter + (size_t)p.ir * IP) - smem) + 15) & ~(size_t)15;
+  uint32_t* rows = reinterpret_cast<uint32_t*>(smem + rows_off);   // offset arithmetic keeps the shared address space
   // a kernel launched behind this one with programmatic stream serialization (the patch-embedding GEMM) may be
   // scheduled as SMs free up; it waits for this grid to complete before it touches global data
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -111,6 +134,12 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
   const int kThreads = blockDim.x, kWarps = kThreads >> 5;
   if (p.lut)
     for (int i = tid; i < 768; i += kThreads) lut[i] = p.lut[i];
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  uint32_t gq = 0;         // chunks staged so far by this CTA: slot = gq & 1, barrier phase = (gq >> 1) & 1
   int cw = -1, ch_ = -1;   // frame size the tables were built for
   const size_t plane = (size_t)S * S;
   const int xseg = S / p.nseg;
@@ -142,12 +171,42 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
     const int nblk = (r1 - r0 + kCH - 1) / kCH;
     const int nchunk = nblk * p.nseg;
 
-    // stage chunk q = (row block, column segment) into slot q & 1 with 4-byte async copies
-    auto issue = [&](int q, int rb, int seg) {
+    // stage chunk (row block, column segment) into slot `sl`: 4-byte async copies from HBM (any alignment, odd word
+    // pitch), or -- frames in pinned host memory -- one 16-byte-granular bulk copy per row (PCIe wants large requests;
+    // the 4-way bank conflicts of the 16-byte pitch hide behind the bus)
+    auto issue = [&](int sl, int rb, int seg) {
       const int xa = seg * xseg, xb = xa + xseg;
       const int c0 = hmin[xa], c1 = hmin[xb - 1] + hn[xb - 1];
       const int span = (c1 - c0) * 3;
-      uint32_t* slot = rows + (size_t)(q & 1) * kCH * p.pitch_words;
+      uint32_t* slot = rows + (size_t)sl * kCH * p.pitch_words;
+      if (p.bulk) {
+        if (warp == 0) {
+          const int r = r0 + rb * kCH + lane;
+          uint32_t bulk_bytes = 0;
+          uint64_t a16 = 0;
+          uint8_t* dst = reinterpret_cast<uint8_t*>(slot + (size_t)lane * p.pitch_words);
+          if (r < r1) {
+            const uint64_t a = frame_base + ((uint64_t)r * (uint64_t)W + (uint64_t)c0) * 3u;
+            a16 = a & ~(uint64_t)15;
+            const uint32_t sh = (uint32_t)(a - a16);
+            const uint32_t bytes = (sh + (uint32_t)span + 15u) & ~15u;
+            if (bytes > (uint32_t)p.pitch_words * 4u) __trap();   // frame larger than the descriptor says
+            rsh[sl * kCH + lane] = (int)sh;
+            bulk_bytes = bytes;
+            if (a16 + bytes > buf_end) {   // last bytes of the buffer: not a whole 16-byte granule, copied by hand
+              bulk_bytes = (uint32_t)((buf_end - a16) & ~(uint64_t)15);
+              for (uint64_t qq = a16 + bulk_bytes; qq < buf_end; ++qq) dst[qq - a16] = *reinterpret_cast<const uint8_t*>(qq);
+            }
+          }
+          uint32_t total = bulk_bytes;
+#pragma unroll
+          for (int o = 16; o; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+          if (lane == 0) mbar_arrive_expect_tx(&full[sl], total);
+          __syncwarp();
+          if (bulk_bytes) bulk_g2s(dst, reinterpret_cast<const void*>(a16), bulk_bytes, &full[sl]);
+        }
+        return;
+      }
       for (int j = warp; j < kCH; j += kWarps) {
         const int r = r0 + rb * kCH + j;
         if (r >= r1) break;
@@ -156,7 +215,7 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
         const int sh = (int)(a - a4);
         const int nwords = (sh + span + 3) >> 2;
         if (nwords > p.pitch_words) __trap();   // frame larger than the descriptor says
-        if (lane == 0) rsh[(q & 1) * kCH + j] = sh;
+        if (lane == 0) rsh[sl * kCH + j] = sh;
         uint32_t* dst = slot + (size_t)j * p.pitch_words;
         if (a4 + 4u * (uint64_t)nwords <= buf_end) {   // every row but the buffer's last: no per-word bound check
           const uint8_t* g = reinterpret_cast<const uint8_t*>(a4) + 4 * lane;
@@ -181,18 +240,21 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
       }
     };
 
-    issue(0, 0, 0);
+    issue((int)(gq & 1u), 0, 0);
     cp_async_commit();
     int next_emit = oy0;
     int rb = 0, seg = 0;               // chunk q = (row block rb, column segment seg), tracked without divisions
     int ring0 = r0 % p.ir;             // ring slot of the row block's first row
     for (int q = 0; q < nchunk; ++q) {
-      cp_async_wait0();
+      const int sl = (int)(gq & 1u);
+      if (p.bulk) mbar_wait(&full[sl], (gq >> 1) & 1u);
+      else cp_async_wait0();
+      ++gq;
       __syncthreads();   // chunk q landed (every thread's copies), rsh[] is visible; everyone is past chunk q-1:
                          // its slot may be refilled and the ring rows its vertical pass read may be overwritten
       if (q + 1 < nchunk) {               // overlaps the passes below
         const bool wrap = seg + 1 == p.nseg;
-        issue(q + 1, wrap ? rb + 1 : rb, wrap ? 0 : seg + 1);
+        issue(sl ^ 1, wrap ? rb + 1 : rb, wrap ? 0 : seg + 1);
       }
       cp_async_commit();
       const int xa = seg * xseg;
@@ -200,8 +262,8 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
       const int r = r0 + rb * kCH + lane;   // this lane's source row
       // ---- horizontal pass: lane = source row, warp = output column (weights are warp-uniform broadcasts)
       if (r < r1) {
-        const uint8_t* rowp = reinterpret_cast<const uint8_t*>(rows + ((size_t)(q & 1) * kCH + lane) * p.pitch_words) +
-                              rsh[(q & 1) * kCH + lane];
+        const uint8_t* rowp = reinterpret_cast<const uint8_t*>(rows + ((size_t)sl * kCH + lane) * p.pitch_words) +
+                              rsh[sl * kCH + lane];
         int rslot = ring0 + lane;
         if (rslot >= p.ir) rslot -= p.ir;   // kCH <= ir: one wrap at most
         uint32_t* irow = inter + (size_t)rslot * IP;
@@ -289,9 +351,9 @@ int pil_device(int* sms, int* max_smem) {
 
 }  // namespace
 
-extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge, int32_t max_height,
-                                   const lvc_video* videos, const int32_t* indices, const float* lut, void* out,
-                                   void* stream) {
+extern "C" int lvc_hf_clip_forward_ex(const lvc_clip_desc* d, int32_t shortest_edge, int32_t max_height, int32_t flags,
+                                      const lvc_video* videos, const int32_t* indices, const float* lut, void* out,
+                                      void* stream) {
   if (!d || !videos || !indices || !out) return lvc_fail(LVC_E_INVAL, "lvc_hf_clip_forward: NULL argument");
   if (d->out_size != S) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: out_size %d unsupported (224 only)", d->out_size);
   if (shortest_edge != 0 && shortest_edge < S) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: shortest_edge %d < crop %d (the processor would pad)", shortest_edge, S);
@@ -323,6 +385,7 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
   PilParams p{};
   p.videos = videos; p.indices = indices; p.lut = lut; p.out = out;
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype; p.bgr = d->src_order == LVC_SRC_BGR;
+  p.bulk = (flags & LVC_HF_SRC_HOST) != 0;
   p.edge = shortest_edge; p.kt_tok = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
   // a sample's window [int(c - s + .5), int(c + s + .5)) holds fewer than 2s + 1, i.e. at most ceil(2s), samples
   static const int kTapSteps[] = {2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 15, 17, 19, 21, 23};
@@ -332,7 +395,7 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
   p.ir = kCH + p.kt + 1;
   // Column segments: the fewest that keep a CTA under 128 KB -- tuned on B200 over 480p / 720p / 1080p at both
   // edges: bigger stages gain nothing, smaller ones add barriers and column overlap (LVC_PIL_NSEG overrides).
-  const size_t fixed = (size_t)(2 * p.kt * S + 4 * S + 2 * kCH + 768) * 4 + (size_t)p.ir * IP * 4;
+  const size_t fixed = (size_t)(2 * p.kt * S + 4 * S + 2 * kCH + 4 + 768) * 4 + (size_t)p.ir * IP * 4;
   static const int kSegs[] = {1, 2, 4, 7, 14, 28};
   size_t smem = 0;
   int pick = -1;
@@ -345,7 +408,8 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
       const int span_px = std::min((int)(xs * scale) + 2 * cs + 3, d->max_width);
       int pw = (span_px * 3 + 6) / 4 + 1;
       pw |= 1;
-      const size_t need = fixed + (size_t)2 * kCH * pw * 4 + 128;   // slack: padding taps read past the last staged row
+      if (p.bulk) pw = (((span_px * 3 + 15 + 15) & ~15) + 16) / 4;   // 16-byte granules for the bulk copies
+      const size_t need = fixed + (size_t)2 * kCH * pw * 4 + 144;   // slack: padding taps read past the last staged row
       if (need <= (pass == 0 ? (size_t)128 * 1024 : (size_t)max_smem)) {
         pick = i; p.nseg = kSegs[i]; p.pitch_words = pw; smem = need;
         break;
@@ -379,4 +443,10 @@ extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge
 #undef LVC_PIL_CASE
     default: return pil_launch<23>(p, grid, threads, smem, stream);
   }
+}
+
+extern "C" int lvc_hf_clip_forward(const lvc_clip_desc* d, int32_t shortest_edge, int32_t max_height,
+                                   const lvc_video* videos, const int32_t* indices, const float* lut, void* out,
+                                   void* stream) {
+  return lvc_hf_clip_forward_ex(d, shortest_edge, max_height, 0, videos, indices, lut, out, stream);
 }

@@ -208,6 +208,13 @@ int lvc_clip_forward_aug(const lvc_clip_desc* desc, const lvc_video* videos, con
 int lvc_hf_clip_forward(const lvc_clip_desc* desc, int32_t shortest_edge, int32_t max_height,
                         const lvc_video* videos, const int32_t* indices, const float* lut, void* out,
                         void* stream);
+/* Same, with flags.  LVC_HF_SRC_HOST: the frames live in PINNED HOST memory (what the reference's scripts hold: decoded
+ * numpy frames) and the kernel reads them directly over PCIe -- one 16-byte-granular bulk copy per source row, and only
+ * the rows and columns the centre crop needs (43 % of a 1080p frame at shortest_edge 256), no staging copy. */
+enum { LVC_HF_SRC_HOST = 1 };
+int lvc_hf_clip_forward_ex(const lvc_clip_desc* desc, int32_t shortest_edge, int32_t max_height, int32_t flags,
+                           const lvc_video* videos, const int32_t* indices, const float* lut, void* out,
+                           void* stream);
 
 /* Number of kernel launches lvc_clip_forward enqueues for this descriptor (for accounting). */
 int lvc_clip_launch_count(const lvc_clip_desc* desc);

@@ -25,7 +25,30 @@ def run(preset, shape, B=8, T=32, n=40, iters=20):
     alg = B * T * (side * side * 3 + 224 * 224 * 3 * 4)
     print(f"{preset:16s} {h}x{w} B={B} T={T}: {ms:.3f} ms  {B / ms * 1e3:.0f} clips/s  {alg / ms / 1e6:.0f} GB/s algorithmic")
 
-if len(sys.argv) > 1:   # one configuration (for ncu): preset H W
+def run_host(preset, shape, B=8, T=32, n=36, iters=5):
+    """frames in pinned host memory, read by the kernel over PCIe (zero-copy) vs upload-then-run"""
+    vids = [torch.randint(0, 256, (n,) + shape + (3,), dtype=torch.uint8).pin_memory() for _ in range(B)]
+    idx = torch.stack([torch.randperm(n)[:T].sort().values for _ in range(B)]).numpy()
+    cb = ClipBuilder(preset, num_frames=T)
+    out = torch.empty((B, T, 3, 224, 224), device="cuda")
+    for zc in (True, False):
+        for _ in range(2):
+            cb.build_from_host(vids, idx, out=out, zero_copy=zc)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            cb.build_from_host(vids, idx, out=out, zero_copy=zc)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        print(f"{preset:16s} {shape[0]}x{shape[1]} host frames, zero_copy={zc}: {ms:.2f} ms  {B / ms * 1e3:.0f} clips/s  "
+              f"{cb.last_h2d_bytes / ms / 1e6:.1f} GB/s over PCIe ({cb.last_h2d_bytes / 1e6:.0f} MB)")
+
+
+if len(sys.argv) > 1 and sys.argv[1] == "host":
+    run_host("vivit_raw", (1080, 1920))
+    run_host("vivit_raw", (720, 1280))
+elif len(sys.argv) > 1:   # one configuration (for ncu): preset H W
     run(sys.argv[1], (int(sys.argv[2]), int(sys.argv[3])), iters=2)
 else:
     for preset in ("vivit_raw", "timesformer_raw"):

@@ -168,3 +168,22 @@ def test_raw_frames_to_vivit_embeddings_graph_pipeline():
         err = (got - want).abs().max() / want.abs().max()
         l2 = (got - want).norm() / want.norm()
         assert err <= 1e-2 and l2 <= 1e-2, (float(err), float(l2))   # north_star: 1e-2 relative for the embeds (bf16 operands)
+
+
+@pytest.mark.parametrize("shape", [(360, 640), (231, 517), (1080, 1920), (300, 200)])
+def test_raw_frames_in_pinned_host_memory_zero_copy(shape):
+    """Decoded frames as the reference's scripts hold them (host memory): the kernel reads the pinned buffers over
+    PCIe with row-granular bulk copies -- same bytes out as from HBM; the last frame of the buffer exercises the
+    hand-copied tail (sizes that are not a multiple of 16 bytes)."""
+    from lvc_b200 import ClipBuilder
+    from oracle import processors as op
+
+    fr = _frames(shape, 3, seed=shape[1])
+    host = torch.from_numpy(fr).pin_memory()
+    idx = [[2, 0, 2, 1]]
+    cb = ClipBuilder("vivit_raw", num_frames=4)
+    got = cb.build_from_host([host], idx)
+    assert torch.equal(got[0].cpu(), torch.from_numpy(op.vivit_processor(fr[[2, 0, 2, 1]])))
+    assert 0 < cb.last_h2d_bytes <= 4 * fr[0].size
+    u8 = ClipBuilder("timesformer_raw", num_frames=4, layout="BTHWC", dtype=torch.uint8).build_from_host([host], idx)
+    assert np.array_equal(u8[0].cpu().numpy(), op.hf_shortest_edge_crop_u8(fr[[2, 0, 2, 1]], 224))
