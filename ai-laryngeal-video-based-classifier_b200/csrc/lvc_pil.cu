@@ -404,6 +404,7 @@ extern "C" int lvc_hf_clip_forward_ex(const lvc_clip_desc* d, int32_t shortest_e
   for (int pass = 0; pass < 2 && pick < 0; ++pass)
     for (int i = 0; i < 6; ++i) {
       if (force_seg > 0 && (kSegs[i] != force_seg || pass == 0)) continue;
+      if (p.bulk && pass == 0) continue;   // over PCIe: the fewest, largest row copies that fit at all
       const int xs = S / kSegs[i];
       const int span_px = std::min((int)(xs * scale) + 2 * cs + 3, d->max_width);
       int pw = (span_px * 3 + 6) / 4 + 1;
