@@ -17,15 +17,27 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdlib>
+#include <type_traits>
 
 #include "lvc_internal.h"
 
 namespace {
 
 constexpr int S = 224;                    // output width/height
-constexpr int kGroups = 2;                // consumer groups working on different rows of a stage
+#ifndef LVC_CLIP_GROUPS
+#define LVC_CLIP_GROUPS 2
+#endif
+constexpr int kGroups = LVC_CLIP_GROUPS;  // consumer groups working on different rows of a stage
 constexpr int kConsumers = kGroups * S;   // 448 threads = 14 warps
-constexpr int kThreads = 32 + kConsumers; // + 1 producer warp
+// Producer warps: stage n of a CTA's stream belongs to warp n % kProducers.  One warp issues a stage's bulk copies
+// lane by lane (UBLKCP is a uniform-datapath instruction: ELECT + 5 R2UR + UBLKCP per copy, ~160 cycles each,
+// measured 0.5 us + 0.165 us per output row and stage), which bounded the small-source configs; four warps
+// issue four stages' copies concurrently.
+#ifndef LVC_CLIP_PRODUCERS
+#define LVC_CLIP_PRODUCERS 4
+#endif
+constexpr int kProducers = LVC_CLIP_PRODUCERS;
+constexpr int kThreads = 32 * kProducers + kConsumers;
 constexpr int kMaxRPS = 8;                // output rows per stage (2*RPS source-row slots <= 32 lanes)
 constexpr int kMaxStages = 16;
 
@@ -42,6 +54,13 @@ struct StageHdr {
   int nw;         // PTV: width of the short-side-scaled image
   int left;       // PTV: centre-crop offset in the scaled image
   int rlo;        // VIVIT bands: first resized row held in the intermediate buffer (nw = first row the NEXT band owns)
+  // output addressing, worked out once per item by the producer (no divisions in the consumers)
+  unsigned long long obase;    // element offset of (frame, channel 0, row 0, column 0) -- tokens: of patch row 0
+  unsigned long long cstride;  // channel stride in elements
+  unsigned rowmul;             // planar layouts: elements per output row; tokens: Wo*K (per patch row)
+  int clip;                    // b = frame / T (stats slot)
+  int pad_[2];
+  unsigned roff[kMaxRPS];      // element offset of each output row of the stage inside the frame
   RowDesc rows[kMaxRPS];
 };
 enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
@@ -61,6 +80,7 @@ struct ClipParams {
   int ring_off;              // byte offset of the source-row ring in shared memory
   int total_items;           // B*T*bands
   int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
+  int producers;             // active producer warps (<= kProducers, <= stages)
   float mean[3], std[3];     // PTV normalisation
   int kt, kh, kw;            // LVC_LAYOUT_TOKENS: patch size; output is the GEMM operand A[M][K] (bf16)
   int kh_shift;              // log2(kh) when kh is a power of two, else -1
@@ -135,11 +155,12 @@ __device__ __forceinline__ int coef(float w) { return __float2int_rn(__fmul_rn(w
 
 namespace {
 
-// Shared memory map: [0,256) full/empty mbarriers | StageHdr[kMaxStages] | LUT 3x256 f32 |
+// Shared memory map: [0,256) full/empty mbarriers | StageHdr[kMaxStages] | LUT 3x256 f32 | LUT 3x256 bf16 |
 // (MODE_VIVIT: Pillow tap table, 2x2 row buffers, intermediate rows of one band x 672 B) | ring.
 constexpr int kHdrOff = 256;
 constexpr int kLutOff = kHdrOff + kMaxStages * (int)sizeof(StageHdr);
-constexpr int kAuxOff = (kLutOff + 3 * 256 * 4 + 127) / 128 * 128;
+constexpr int kLut16Off = kLutOff + 3 * 256 * 4;    // the same table rounded to bf16 (bf16 outputs skip the per-sample convert)
+constexpr int kAuxOff = (kLut16Off + 3 * 256 * 2 + 127) / 128 * 128;
 constexpr int kRowBytes = S * 4;                    // one resized row, a 32-bit word (R | G<<8 | B<<16) per pixel
 constexpr int kVivitTapOff = kAuxOff;               // int4[224]: ymin, k0, k1, k2
 constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][224 words]
@@ -231,16 +252,17 @@ __device__ __forceinline__ FrameOut frame_out(const ClipParams& p, int f, int b,
   }
   return o;
 }
-__device__ __forceinline__ size_t row_offset(const ClipParams& p, const FrameOut& o, int y) {
-  if (p.layout != LVC_LAYOUT_TOKENS) return o.base + (size_t)((unsigned)y * o.rowmul);   // < 2^32: one IMAD.WIDE
+// row term of the output offset (< 2^32 elements inside one frame)
+__device__ __forceinline__ unsigned row_part(const ClipParams& p, unsigned rowmul, int y) {
+  if (p.layout != LVC_LAYOUT_TOKENS) return (unsigned)y * rowmul;
   const unsigned ho = p.kh_shift >= 0 ? ((unsigned)y >> p.kh_shift) : ((unsigned)y / (unsigned)p.kh);
   const unsigned dy = (unsigned)y - ho * p.kh;
-  return o.base + (size_t)(ho * o.rowmul + dy * (unsigned)p.kw);
+  return ho * rowmul + dy * (unsigned)p.kw;
 }
-__device__ __forceinline__ size_t col_offset(const ClipParams& p, int x) {
-  if (p.layout == LVC_LAYOUT_BTHWC) return (size_t)x * 3;
-  if (p.layout == LVC_LAYOUT_TOKENS) return (size_t)(x / p.kw) * (3 * p.kt * p.kh * p.kw) + x % p.kw;
-  return (size_t)x;
+__device__ __forceinline__ unsigned col_offset(const ClipParams& p, int x) {
+  if (p.layout == LVC_LAYOUT_BTHWC) return (unsigned)x * 3u;
+  if (p.layout == LVC_LAYOUT_TOKENS) return (unsigned)(x / p.kw) * (unsigned)(3 * p.kt * p.kh * p.kw) + (unsigned)(x % p.kw);
+  return (unsigned)x;
 }
 
 template <int MODE>
@@ -250,6 +272,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   uint64_t* empty = full + kMaxStages;
   StageHdr* hdrs = reinterpret_cast<StageHdr*>(smem + kHdrOff);
   float* lut = reinterpret_cast<float*>(smem + kLutOff);
+  __nv_bfloat16* lut16 = reinterpret_cast<__nv_bfloat16*>(smem + kLut16Off);
   uint8_t* ring = smem + p.ring_off;
 
   // a kernel launched behind this one with programmatic stream serialization (the patch-embedding GEMM) may be
@@ -267,13 +290,22 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (p.lut)
-    for (int i = tid; i < 3 * 256; i += kThreads) lut[i] = p.lut[i];
+    for (int i = tid; i < 3 * 256; i += kThreads) {
+      const float w = p.lut[i];
+      lut[i] = w;
+      lut16[i] = __float2bfloat16_rn(w);
+    }
   if (MODE == MODE_VIVIT)
     for (int i = tid; i < S; i += kThreads) reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = pil_tap(i);
   __syncthreads();
 
-  if (warp == 0) {
-    // ================= producer warp: lane j fetches source row (j&1 ? y1 : y0) of output row j>>1
+  if (warp < kProducers) {
+    // ================= producer warps: lane j fetches source row (j&1 ? y1 : y0) of output row j>>1
+    // No more active producers than ring slots: a warp that finished stage n has seen stage n - np - stages consumed;
+    // its parity wait on the slot of stage n is unambiguous only if stage n - 2*stages is consumed too (np <= stages).
+    const int np = p.producers;
+    if (warp >= np) return;
+    int turn = 0;          // stage counter modulo np: this warp acts on the stages with turn == warp
     const uint64_t policy = policy_evict_first();
     const int nrows = 2 * p.rps;
     const unsigned lanes = nrows >= 32 ? 0xffffffffu : ((1u << nrows) - 1u);
@@ -282,6 +314,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       const int f = item / p.bands, band = item - f * p.bands;
       const int b = f / p.T;
+      const FrameOut fo = frame_out(p, f, b, f - b * p.T);
       const lvc_video v = p.videos[b];
       int idx = p.indices[f];
       idx = min(max(idx, 0), v.n_frames - 1);
@@ -331,16 +364,21 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
       const uint64_t buf_end = v.base + (uint64_t)v.nbytes;
       for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
+        const bool mine = (turn == warp);
+        turn = (turn + 1 == np) ? 0 : turn + 1;
+        if (!mine) continue;
         const int oy_first = MODE == MODE_VIVIT ? rlo + st * p.rps : band * p.rows_per_band + st * p.rps;
         if (lane == 0) mbar_wait(&empty[slot], phase ^ 1u);
         __syncwarp();
         uint32_t my_bytes = 0, bulk_bytes = 0;
         int my_off = 0, cb = 0;
+        unsigned roff = 0;
         uint64_t a = 0;
         bool leader = false;
         uint8_t* stage_base = ring + (size_t)slot * nrows * p.pitch;
         if (lane < nrows) {
           const int r = lane >> 1, oyr = min(oy_first + r, S - 1);   // VIVIT halo stages may run past the last row
+          if (MODE != MODE_VIVIT) roff = row_part(p, fo.rowmul, oyr);
           int ysrc;
           if (MODE == MODE_PTV) {
             int y0, y1; float l0, l1;
@@ -349,12 +387,13 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             cb = __float_as_int((lane & 1) ? l1 : l0);
           } else if (area) {
             ysrc = 2 * oyr + (lane & 1);
+            cb = (int)0x80000000u;   // with a0 = a1 = 32 the fixed-point blend below IS the 2x2 average (see the consumer)
           } else {
             int sy; float fr;
             if (p.f32src) cv_tap64(oyr, scale_y, sy, fr); else cv_tap(oyr, scale_y, sy, fr);
             ysrc = min(max(sy + (lane & 1), 0), sh - 1);
             if (p.f32src) cb = __float_as_int((lane & 1) ? fr : __fsub_rn(1.0f, fr));
-            else cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
+            else cb = ((lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr))) << 16;   // pre-shifted: the blend is a multiply-high
           }
           const uint64_t addr = frame_base + (uint64_t)(oy + ysrc) * row_bytes + (uint64_t)ox * 3u;
           a = addr & ~(uint64_t)15;
@@ -379,10 +418,12 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           RowDesc rd;
           rd.off0 = my_off; rd.off1 = off_next; rd.b0 = cb; rd.b1 = cb_next;
           h->rows[lane >> 1] = rd;
+          h->roff[lane >> 1] = roff;
         }
         if (lane == 0) {
           h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first; h->flags = (area ? 1 : 0) | (flip << 1);
           h->ox = ox; h->nw = (MODE == MODE_VIVIT) ? own_hi : nw; h->left = left; h->rlo = rlo;
+          h->obase = fo.base; h->cstride = fo.cstride; h->rowmul = fo.rowmul; h->clip = b;
         }
         if (leader && bulk_bytes < my_bytes) {
           // last bytes of the buffer: not a whole 16-byte granule, copy them by hand
@@ -402,11 +443,12 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   }
 
   // ================= consumer warps: thread -> output column x, group -> rows g, g+G, ...
-  const int ct = tid - 32;
+  const int ct = tid - 32 * kProducers;
   const int g = ct / S;
   const int x = ct - g * S;
-  int cached_sw = -1, cached_flags = -1, cached_ox = -1, cached_f = -1, cur_b = 0, cur_t = 0;
-  FrameOut fo = {0, 0, 0};
+  int cached_sw = -1, cached_flags = -1, cached_ox = -1;
+  unsigned long long obase = 0, cstride = 0;   // output addressing of the current item (from the stage header)
+  unsigned rowmul = 0;
   int xo = 0, d1 = 0, a0 = 0, a1 = 0;
   float lx0 = 0.f, lx1 = 0.f;
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
@@ -414,20 +456,38 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
   int acc_b = -1;
   int slot = 0;
   uint32_t phase = 0;
-  const size_t xoff = col_offset(p, x);
+  const unsigned xoff = col_offset(p, x);
   // MODE_VIVIT state: Pillow horizontal taps of this thread's column, row-buffer parity
   int4 hx = make_int4(0, 0, 0, 0);
   int parity = 0;
   uint8_t* inter = smem + kVivitInterOff;
   if (MODE == MODE_VIVIT) hx = reinterpret_cast<const int4*>(smem + kVivitTapOff)[x];
 
+  // LUT + store of one output sample per channel (element offset eoff of channel 0, channel stride cstride)
+  auto store_px = [&](auto ODT, const size_t eoff, const int (&v)[3]) {
+    constexpr int kOdt = decltype(ODT)::value;   // compile-time output dtype, or -1 = look at the descriptor
+    const int odt = kOdt >= 0 ? kOdt : p.out_dtype;
+    if (odt == LVC_DT_F32) {
+      float* o = reinterpret_cast<float*>(p.out) + eoff;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
+    } else if (odt == LVC_DT_BF16) {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c * cstride] = lut16[c * 256 + v[c]];
+    } else {
+      uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
+    }
+  };
+
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-    int f = 0;
     for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
       mbar_wait(&full[slot], phase);
       const StageHdr* h = &hdrs[slot];
       const int sw = h->sw, flags = h->flags, oy0 = h->oy0;
-      f = h->frame;
+      obase = h->obase; cstride = h->cstride; rowmul = h->rowmul;
       if (MODE == MODE_PTV) {
         const int hox = h->ox;
         const int geo = h->nw | (h->left << 12) | ((flags & 2) << 28);   // nw, left < 4096
@@ -441,7 +501,9 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
       } else if (sw != cached_sw || flags != cached_flags) {
         cached_sw = sw; cached_flags = flags;
-        if (flags & 1) { xo = 6 * x; d1 = 3; a0 = 1; a1 = 1; }
+        // exact 2x2 (INTER_AREA): a0 = a1 = 32 and b0 = b1 = 2^31 turn the fixed-point blend into
+        // (p00 + p01 + p10 + p11 + 2) >> 2: s >> 4 = 2 (p0 + p1), umulhi(2^31, 2 t) = t
+        if (flags & 1) { xo = 6 * x; d1 = 3; a0 = 32; a1 = 32; }
         else {
           int sx; float fr;
           if (p.f32src) cv_tap64(x, cv_scale(sw), sx, fr); else cv_tap(x, cv_scale(sw), sx, fr);
@@ -454,13 +516,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           d1 = (sx + 1 <= sw - 1) ? 3 : 0;
         }
       }
-      if (f != cached_f) {
-        cached_f = f;
-        cur_b = f / p.T;
-        cur_t = f - cur_b * p.T;
-        fo = frame_out(p, f, cur_b, cur_t);
-      }
-      const int b = cur_b;
+      const int b = h->clip;
       if (MODE != MODE_PTV && p.stats && b != acc_b) {
         if (acc_b >= 0) {
 #pragma unroll
@@ -469,13 +525,16 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
         acc = 0; acc_b = b;
       }
-      for (int r = g; r < p.rps; r += kGroups) {
+      unsigned acc32 = 0;   // this stage's share of the checksum (<= 4 rows x 765)
+      // F32SRC / ODT are compile-time copies of p.f32src / p.out_dtype: the row body has no branches, so the two
+      // rows of a trip are scheduled as one block (their shared-memory loads overlap)
+      auto do_row = [&](auto F32SRC, auto ODT, const int r) {
+        constexpr bool kF32Src = decltype(F32SRC)::value;
         const RowDesc rd = h->rows[r];
         const uint8_t* p0 = ring + rd.off0 + xo;
         const uint8_t* p1 = ring + rd.off1 + xo;
         const int oyr = oy0 + r;
-        const size_t cstride = fo.cstride;
-        const size_t eoff = row_offset(p, fo, oyr) + xoff;  // element offset of channel 0
+        const size_t eoff = (size_t)obase + (size_t)(h->roff[r] + xoff);  // element offset of channel 0
         if (MODE == MODE_PTV) {
           // torch CPU blend order: r = fma(p_x0, lx0, p_x1*lx1) per row, out = fma(r_y0, ly0, r_y1*ly1)
           const float ly0 = __int_as_float(rd.b0), ly1 = __int_as_float(rd.b1);
@@ -491,7 +550,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             if (p.out_dtype == LVC_DT_F32) __stcs(o + c * cstride, y);
             else ob[c * cstride] = __float2bfloat16_rn(y);
           }
-          continue;
+          return;
         }
         int v[3];
         {
@@ -509,7 +568,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
           const uint32_t a01 = (uint32_t)a0 | ((uint32_t)a1 << 16);
           // byte pairs (c of pixel 0, c of pixel 1) of the 8 source bytes; a BGR source swaps ends
           const uint32_t sel[3] = {p.bgr ? 0x4452u : 0x4430u, 0x4441u, p.bgr ? 0x4430u : 0x4452u};
-          if (p.f32src) {
+          if (kF32Src) {
             // float frames: two float products and an add per pass (no FMA contraction), truncation to uint8;
             // the exact 2x2 case is INTER_AREA = sum * 0.25f, truncated
             const float by0 = __int_as_float(rd.b0), by1 = __int_as_float(rd.b1);
@@ -529,12 +588,14 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             for (int c = 0; c < 3; ++c) {
               const int s0 = (int)__dp2a_lo(a01, __byte_perm(lo0, hi0, sel[c]), 0u);
               const int s1 = (int)__dp2a_lo(a01, __byte_perm(lo1, hi1, sel[c]), 0u);
-              v[c] = (flags & 1) ? ((s0 + s1 + 2) >> 2)
-                                 : ((((rd.b0 * (s0 >> 4)) >> 16) + ((rd.b1 * (s1 >> 4)) >> 16) + 2) >> 2);
+              // cv2's vertical pass ((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16): the coefficients arrive as b << 16,
+              // so each term is one multiply-high (all operands are non-negative)
+              v[c] = (int)((__umulhi((unsigned)rd.b0, (unsigned)s0 >> 4) + __umulhi((unsigned)rd.b1, (unsigned)s1 >> 4) + 2u) >> 2);
             }
           }
         }
-        if (want_stats && (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw))) acc += (unsigned)(v[0] + v[1] + v[2]);  // bands: owned rows only
+        // checksum share (dropped after the stage loop when no stats buffer was passed); bands: owned rows only
+        acc32 += (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw)) ? (unsigned)(v[0] + v[1] + v[2]) : 0u;
         if (MODE == MODE_VIVIT) {
           // Pillow horizontal pass of this row (224 -> cropped 224 of 256), rounded to uint8
           // (one word per pixel: a store and up to three loads per thread instead of 3 + 9 byte accesses)
@@ -551,22 +612,26 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
             packed |= (uint32_t)clip8(ss >> 22) << (8 * c);
           }
           reinterpret_cast<uint32_t*>(inter)[(oyr - h->rlo) * S + x] = packed;
-          continue;
+          return;
         }
-        if (p.out_dtype == LVC_DT_F32) {
-          float* o = reinterpret_cast<float*>(p.out) + eoff;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
-        } else if (p.out_dtype == LVC_DT_BF16) {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(lut[c * 256 + v[c]]);
+        store_px(ODT, eoff, v);
+      };
+      // two rows per trip (their shared-memory loads overlap) whenever the group has an even number of rows
+      auto do_rows = [&](auto F32SRC, auto ODT) {
+        if (MODE != MODE_VIVIT && (p.rps & (2 * kGroups - 1)) == 0) {
+          for (int r = g; r < p.rps; r += 2 * kGroups) { do_row(F32SRC, ODT, r); do_row(F32SRC, ODT, r + kGroups); }
         } else {
-          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
+          for (int r = g; r < p.rps; r += kGroups) do_row(F32SRC, ODT, r);
         }
-      }
+      };
+      using std::integral_constant;
+      if (MODE == MODE_PTV) do_rows(std::false_type{}, integral_constant<int, -1>{});        // stores by itself
+      else if (p.f32src) do_rows(std::true_type{}, integral_constant<int, -1>{});             // float frames: rare
+      else if (MODE == MODE_VIVIT) do_rows(std::false_type{}, integral_constant<int, -1>{});  // rows go to the intermediate buffer
+      else if (p.out_dtype == LVC_DT_BF16) do_rows(std::false_type{}, integral_constant<int, LVC_DT_BF16>{});
+      else if (p.out_dtype == LVC_DT_F32) do_rows(std::false_type{}, integral_constant<int, LVC_DT_F32>{});
+      else do_rows(std::false_type{}, integral_constant<int, LVC_DT_U8>{});
+      if (want_stats) acc += acc32;
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
     }
@@ -576,8 +641,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
       const int band = item % p.bands, ylo = band * p.rows_per_band, rlo = vt[ylo].x;
       for (int y = ylo + g; y < ylo + p.rows_per_band; y += kGroups) {
-        const size_t cstride = fo.cstride;
-        const size_t eoff = row_offset(p, fo, y) + xoff;
+        const size_t eoff = (size_t)obase + (size_t)(row_part(p, rowmul, y) + xoff);
         const int4 ty = vt[y];
         const uint32_t* tp = reinterpret_cast<const uint32_t*>(inter) + (ty.x - rlo) * S + x;
         const uint32_t w0 = tp[0], w1 = tp[S], w2 = ty.w ? tp[2 * S] : 0u;
@@ -588,19 +652,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
                          (int)((w2 >> (8 * c)) & 0xffu) * ty.w;
           v[c] = clip8(ss >> 22);
         }
-        if (p.out_dtype == LVC_DT_F32) {
-          float* o = reinterpret_cast<float*>(p.out) + eoff;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
-        } else if (p.out_dtype == LVC_DT_BF16) {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(lut[c * 256 + v[c]]);
-        } else {
-          uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) o[c * cstride] = (uint8_t)v[c];
-        }
+        store_px(std::integral_constant<int, -1>{}, eoff, v);
       }
       consumers_bar();  // the next frame's horizontal pass overwrites the intermediate
     }
@@ -733,29 +785,35 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
     const int budget0 = std::min(di.max_smem, 200 * 1024) - ring_base;
     p.rps = (budget0 / (16 * p.pitch) >= 3) ? 8 : 4;
   }
-  if (p.rps < kGroups || p.rps > kMaxRPS || (p.rps % kGroups) || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
+  if (p.rps < 2 || p.rps > kMaxRPS || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
   const int fixed = ring_base;
   const int smem_budget = std::min(di.max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, fixed + 64 * 1024));
   int stage_bytes = 2 * p.rps * p.pitch;
-  while ((smem_budget - fixed) / stage_bytes < 2 && p.rps > kGroups) {
-    p.rps -= kGroups;
-    while (S % p.rps) p.rps -= kGroups;
+  while ((smem_budget - fixed) / stage_bytes < 2 && p.rps > 2) {   // very wide sources: fewer rows per stage (groups beyond rps idle)
+    do --p.rps; while (S % p.rps);
     stage_bytes = 2 * p.rps * p.pitch;
   }
   p.stages = std::min(kMaxStages, (smem_budget - fixed) / stage_bytes);
   if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: max_width %d does not fit the shared-memory ring", d->max_width);
   const size_t smem = (size_t)fixed + (size_t)p.stages * stage_bytes;
+  p.producers = std::max(1, std::min(std::min(kProducers, p.stages), env_int("LVC_CLIP_NP", kProducers)));
 
   const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)di.max_smem / (smem + 1024)));
   const int grid_max = di.sms * ctas_per_sm;
   const int frames = d->batch * d->num_frames;
-  // band = output rows per work item: the largest divisor of 224 that still leaves >= 8 items per CTA
+  // band = output rows per work item.  A CTA walks its items round-robin, and every item boundary costs about
+  // four rows' worth of time (descriptor fetch, tap set-up, a partly drained ring; measured on cfg 3 / cfg 4 with
+  // scripts/clip_knobs.py): pick the divisor of 224 that minimises rounds x (rows + 4)
   static const int kBands[] = {224, 112, 56, 32, 28, 16, 8, 4, 2};
   p.rows_per_band = p.rps;
   const int forced = env_int("LVC_CLIP_BAND", 0);
+  long long band_cost = -1;
   for (int rb : kBands) {
     if (rb % p.rps) continue;
-    if (forced ? rb == forced : (int64_t)frames * (S / rb) >= 8LL * grid_max) { p.rows_per_band = rb; break; }
+    if (forced) { if (rb == forced) p.rows_per_band = rb; continue; }
+    const long long items = (long long)frames * (S / rb);
+    const long long cost = ((items + grid_max - 1) / grid_max) * (rb + 4);
+    if (band_cost < 0 || cost < band_cost) { band_cost = cost; p.rows_per_band = rb; }
   }
   p.bands = S / p.rows_per_band;
   if (mode == MODE_VIVIT) { p.bands = v_nb; p.rows_per_band = S / v_nb; p.v_stages = (v_res + p.rps - 1) / p.rps; }
