@@ -24,11 +24,11 @@
 namespace {
 
 constexpr int S = 224;                    // output width/height
-#ifndef LVC_CLIP_GROUPS
-#define LVC_CLIP_GROUPS 2
-#endif
-constexpr int kGroups = LVC_CLIP_GROUPS;  // consumer groups working on different rows of a stage
-constexpr int kConsumers = kGroups * S;   // 448 threads = 14 warps
+enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
+// Consumer groups work on different rows of a stage (224 threads each, thread = output column).  Two groups for the
+// cv2 / torch chains; the ViViT preset runs two Pillow passes on top of the resize and is bound by consumer issue,
+// so it gets four (measured with 2+ producer warps: 155 -> 135 us on config 2; the other modes lose with four).
+__host__ __device__ constexpr int groups_of(int mode) { return mode == MODE_VIVIT ? 4 : 2; }
 // Producer warps: stage n of a CTA's stream belongs to warp n % kProducers.  One warp issues a stage's bulk copies
 // lane by lane (UBLKCP is a uniform-datapath instruction: ELECT + 5 R2UR + UBLKCP per copy, ~160 cycles each,
 // measured 0.5 us + 0.165 us per output row and stage), which bounded the small-source configs; four warps
@@ -37,7 +37,7 @@ constexpr int kConsumers = kGroups * S;   // 448 threads = 14 warps
 #define LVC_CLIP_PRODUCERS 4
 #endif
 constexpr int kProducers = LVC_CLIP_PRODUCERS;
-constexpr int kThreads = 32 * kProducers + kConsumers;
+__host__ __device__ constexpr int threads_of(int mode) { return 32 * kProducers + groups_of(mode) * S; }
 constexpr int kMaxRPS = 8;                // output rows per stage (2*RPS source-row slots <= 32 lanes)
 constexpr int kMaxStages = 16;
 
@@ -63,8 +63,6 @@ struct StageHdr {
   unsigned roff[kMaxRPS];      // element offset of each output row of the stage inside the frame
   RowDesc rows[kMaxRPS];
 };
-enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
-
 struct ClipParams {
   const lvc_video* videos;
   const int32_t* indices;
@@ -164,7 +162,7 @@ constexpr int kAuxOff = (kLut16Off + 3 * 256 * 2 + 127) / 128 * 128;
 constexpr int kRowBytes = S * 4;                    // one resized row, a 32-bit word (R | G<<8 | B<<16) per pixel
 constexpr int kVivitTapOff = kAuxOff;               // int4[224]: ymin, k0, k1, k2
 constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][224 words]
-constexpr int kVivitInterOff = kVivitRowBufOff + kGroups * 2 * kRowBytes;
+constexpr int kVivitInterOff = kVivitRowBufOff + groups_of(MODE_VIVIT) * 2 * kRowBytes;
 
 // Pillow BILINEAR 224 -> 256 taps for cropped output coordinate d (source coordinate d + 16 of the
 // 256-wide image): precompute_coeffs + normalize_coeffs_8bpc in double, support 1 (up-scale).
@@ -218,8 +216,8 @@ __device__ __forceinline__ void ring_next(int& slot, uint32_t& phase, int stages
 __device__ __forceinline__ void group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(2 + g), "r"(S) : "memory");
 }
-__device__ __forceinline__ void consumers_bar() {
-  asm volatile("bar.sync 1, %0;" ::"r"(kConsumers) : "memory");
+__device__ __forceinline__ void consumers_bar(int consumers) {
+  asm volatile("bar.sync 1, %0;" ::"r"(consumers) : "memory");
 }
 
 }  // namespace
@@ -266,7 +264,8 @@ __device__ __forceinline__ unsigned col_offset(const ClipParams& p, int x) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
+__global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
+  constexpr int kGroups = groups_of(MODE), kConsumers = kGroups * S, kThreads = threads_of(MODE);
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty = full + kMaxStages;
@@ -637,7 +636,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
     }
     if (MODE == MODE_VIVIT) {
       // the whole frame went through the horizontal pass: Pillow vertical pass + LUT + store
-      consumers_bar();
+      consumers_bar(kConsumers);
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
       const int band = item % p.bands, ylo = band * p.rows_per_band, rlo = vt[ylo].x;
       for (int y = ylo + g; y < ylo + p.rows_per_band; y += kGroups) {
@@ -654,7 +653,7 @@ __global__ void __launch_bounds__(kThreads, 1) lvc_clip_kernel(const __grid_cons
         }
         store_px(std::integral_constant<int, -1>{}, eoff, v);
       }
-      consumers_bar();  // the next frame's horizontal pass overwrites the intermediate
+      consumers_bar(kConsumers);  // the next frame's horizontal pass overwrites the intermediate
     }
   }
   if (MODE != MODE_PTV && p.stats && acc_b >= 0) {
@@ -695,7 +694,7 @@ const DeviceInfo& device_info() {
 template <int MODE>
 int launch(const ClipParams& p, int grid, size_t smem, cudaStream_t st) {
   LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lvc_clip_kernel<MODE><<<grid, kThreads, smem, st>>>(p);
+  lvc_clip_kernel<MODE><<<grid, threads_of(MODE), smem, st>>>(p);
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;
 }
@@ -783,7 +782,11 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   p.rps = env_int("LVC_CLIP_RPS", 0);
   if (p.rps == 0) {
     const int budget0 = std::min(di.max_smem, 200 * 1024) - ring_base;
-    p.rps = (budget0 / (16 * p.pitch) >= 3) ? 8 : 4;
+    // full-frame sources keep the bus busy only with a finely sliced ring (a slot being consumed cannot be refilled:
+    // 3 stages leave a third of the ring idle, 6 a sixth; cfg 3: 60 -> 53 us with 4 producers); ROI rows are much
+    // shorter than their slots and the ViViT preset is consumer-bound: those prefer fewer, larger stages
+    const int want_stages = (boxes || mode == MODE_VIVIT) ? 3 : 6;
+    p.rps = (budget0 / (16 * p.pitch) >= want_stages) ? 8 : 4;
   }
   if (p.rps < 2 || p.rps > kMaxRPS || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
   const int fixed = ring_base;

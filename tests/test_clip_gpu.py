@@ -332,3 +332,36 @@ def test_float_frame_branch_of_cv2_resize():
     assert np.array_equal(f[0], want)
     with pytest.raises(ValueError):
         ClipBuilder("ptv_eval", num_frames=T, float_frames=True)
+
+
+def test_very_wide_frames_small_stages():
+    """Frames so wide that only 2 / 4 output rows fit a ring stage (rows per stage falls back 8 -> 4 -> 2):
+    same bytes as cv2.resize."""
+    from lvc_b200 import ClipBuilder
+
+    T = 3
+    specs = [(301, 3, 64, 7000, "noise"), (302, 3, 300, 4096, "ramp")]
+    for spec in specs:
+        host, dev = _videos([spec])
+        idx = [osm.dataset_indices("uniform", host[0].shape[0], T)]
+        out = ClipBuilder("dataset_u8", num_frames=T)(dev, idx).cpu().numpy()
+        want = op.resize_clip_cv2(host[0][idx[0]])
+        assert np.array_equal(out[0], want), spec
+
+
+@pytest.mark.parametrize("knobs", [{"LVC_CLIP_NP": "1"}, {"LVC_CLIP_NP": "2"}, {"LVC_CLIP_NP": "4", "LVC_CLIP_RPS": "4"},
+                                   {"LVC_CLIP_NP": "4", "LVC_CLIP_RPS": "2", "LVC_CLIP_BAND": "2"}])
+def test_producer_count_and_stage_knobs_do_not_change_bytes(knobs, monkeypatch):
+    """The launch geometry (producer warps, rows per stage, band size) is a performance choice: results are identical."""
+    from lvc_b200 import ClipBuilder
+
+    T = 5
+    host, dev = _videos(SHAPES[:6])
+    idx = [osm.dataset_indices("random", v.shape[0], T, __import__("random").Random(11)) for v in host]
+    base = ClipBuilder("resnet_infer", num_frames=T)(dev, idx).cpu().numpy()
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    got = ClipBuilder("resnet_infer", num_frames=T)(dev, idx).cpu().numpy()
+    assert np.array_equal(base, got)
+    want = op.manual_normalize(op.resize_clip_cv2(host[0][idx[0]]))
+    assert np.array_equal(got[0], want)
