@@ -516,7 +516,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
         }
       }
       const int b = h->clip;
-      if (MODE != MODE_PTV && p.stats && b != acc_b) {
+      if (MODE != MODE_PTV && want_stats && b != acc_b) {
         if (acc_b >= 0) {
 #pragma unroll
           for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -594,7 +594,8 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           }
         }
         // checksum share (dropped after the stage loop when no stats buffer was passed); bands: owned rows only
-        acc32 += (MODE != MODE_VIVIT || (oyr < S && oyr < h->nw)) ? (unsigned)(v[0] + v[1] + v[2]) : 0u;
+        if (MODE != MODE_VIVIT) acc32 += (unsigned)(v[0] + v[1] + v[2]);   // branch-free body: always counted
+        else if (want_stats && oyr < S && oyr < h->nw) acc32 += (unsigned)(v[0] + v[1] + v[2]);
         if (MODE == MODE_VIVIT) {
           // Pillow horizontal pass of this row (224 -> cropped 224 of 256), rounded to uint8
           // (one word per pixel: a store and up to three loads per thread instead of 3 + 9 byte accesses)
