@@ -54,7 +54,7 @@ for name in (sys.argv[1:] or ["swin_cfg4", "timesformer_cfg3", "vivit_cfg2"]):
             os.environ.pop(kk, None)
         os.environ.update(k)
         try:
-            print(f"{name:18s} {str(k):48s} {timeit(cb, batch, tok):8.1f} us", flush=True)
+            print(f"{name:18s} {str(k):72s} {timeit(cb, batch, tok):8.1f} us", flush=True)
         except Exception as e:  # a knob the shape does not admit
-            print(f"{name:18s} {str(k):48s} failed: {e}", flush=True)
+            print(f"{name:18s} {str(k):72s} failed: {e}", flush=True)
     del vids
