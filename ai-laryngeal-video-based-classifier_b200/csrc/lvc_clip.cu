@@ -5,12 +5,13 @@
 //   resnet50-2d-lstm/inference.py:158-178                               resize + /255 + mean/std + permute
 //   vivit_transformer/vivit_classifier/trainers/trainer.py:62-95        image processor + torch.cat
 //
-// Design (DESIGN.md "clip kernel"): a persistent CTA per SM; one producer warp streams the TAPPED
-// source rows (2 of every ~scale rows; duplicates inside a stage are fetched once) into a
+// Design (DESIGN.md "clip kernel"): a persistent CTA per SM; four producer warps (stage n -> warp n mod 4) stream
+// the TAPPED source rows (2 of every ~scale rows; duplicates inside a stage are fetched once) into a
 // shared-memory ring with 1-D bulk async copies (cp.async.bulk, the TMA engine) completing on
-// mbarriers; 14 consumer warps (2 groups x 224 threads, one thread per output column, x taps in
-// registers for the whole frame) do the horizontal + vertical fixed-point passes out of shared
-// memory, look the result up in the float LUT and write coalesced 128-byte rows.
+// mbarriers, and publish each stage's header (tap coefficients, ring offsets, output addressing);
+// 14 consumer warps (2 groups x 224 threads -- 4 groups for the ViViT preset -- one thread per output column,
+// x taps in registers for the whole frame) do the horizontal + vertical fixed-point passes out of shared
+// memory, look the result up in the LUT and write coalesced rows.
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
