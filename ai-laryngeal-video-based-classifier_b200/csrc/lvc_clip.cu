@@ -80,6 +80,7 @@ struct ClipParams {
   int total_items;           // B*T*bands
   int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
   int producers;             // active producer warps (<= kProducers, <= stages)
+  int merge_rows;            // fetch the (y, y+1) rows of a full-width tap pair with one copy
   float mean[3], std[3];     // PTV normalisation
   int kt, kh, kw;            // LVC_LAYOUT_TOKENS: patch size; output is the GEMM operand A[M][K] (bf16)
   int kh_shift;              // log2(kh) when kh is a power of two, else -1
@@ -304,6 +305,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
     // No more active producers than ring slots: a warp that finished stage n has seen stage n - np - stages consumed;
     // its parity wait on the slot of stage n is unambiguous only if stage n - 2*stages is consumed too (np <= stages).
     const int np = p.producers;
+    const bool env_merge = p.merge_rows != 0;
     if (warp >= np) return;
     int turn = 0;          // stage counter modulo np: this warp acts on the stages with turn == warp
     const uint64_t policy = policy_evict_first();
@@ -361,6 +363,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
       const bool area = MODE != MODE_PTV && (sw == 2 * S) && (sh == 2 * S);
       const double scale_y = cv_scale(sh);
       const uint64_t row_bytes = (uint64_t)v.width * 3u;
+      const bool full_width = MODE != MODE_PTV && ox == 0 && sw == v.width && env_merge;
       const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
       const uint64_t buf_end = v.base + (uint64_t)v.nbytes;
       for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
@@ -407,6 +410,20 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           bulk_bytes = my_bytes;
           if (a + my_bytes > buf_end) bulk_bytes = (uint32_t)((buf_end - a) & ~(uint64_t)15);
           if (!leader) bulk_bytes = 0;
+          // Full-width rows y and y+1 are contiguous in memory: when the two taps of an output row are such a pair
+          // (and neither row serves another lane) the even lane fetches both with ONE copy into its two slots --
+          // half as many UBLKCP issues per stage, twice the request size on the bus.
+          const unsigned peer_same = __shfl_xor_sync(lanes, same, 1);
+          const int y_peer = __shfl_xor_sync(lanes, ysrc, 1);
+          const uint32_t merged = (shift + 2u * (uint32_t)row_bytes + 15u) & ~15u;
+          int pair = !(lane & 1) && full_width && same == (1u << lane) && peer_same == (2u << lane) && y_peer == ysrc + 1 &&
+                     a + merged <= buf_end;
+          pair |= __shfl_xor_sync(lanes, pair, 1);
+          const int off_even = __shfl_xor_sync(lanes, my_off, 1);
+          if (pair) {
+            if (lane & 1) { leader = false; bulk_bytes = 0; my_off = off_even + (int)row_bytes; }
+            else bulk_bytes = merged;
+          }
         }
         uint32_t total = bulk_bytes;
 #pragma unroll
@@ -801,6 +818,7 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   p.stages = std::min(kMaxStages, (smem_budget - fixed) / stage_bytes);
   if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: max_width %d does not fit the shared-memory ring", d->max_width);
   const size_t smem = (size_t)fixed + (size_t)p.stages * stage_bytes;
+  p.merge_rows = env_int("LVC_CLIP_MERGE", 1);
   p.producers = std::max(1, std::min(std::min(kProducers, p.stages), env_int("LVC_CLIP_NP", kProducers)));
 
   const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)di.max_smem / (smem + 1024)));
