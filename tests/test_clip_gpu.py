@@ -350,6 +350,7 @@ def test_very_wide_frames_small_stages():
 
 
 @pytest.mark.parametrize("knobs", [{"LVC_CLIP_NP": "1"}, {"LVC_CLIP_NP": "2"}, {"LVC_CLIP_NP": "4", "LVC_CLIP_RPS": "4"},
+                                   {"LVC_CLIP_MERGE": "0"}, {"LVC_CLIP_MERGE": "0", "LVC_CLIP_NP": "1", "LVC_CLIP_RPS": "8"},
                                    {"LVC_CLIP_NP": "4", "LVC_CLIP_RPS": "2", "LVC_CLIP_BAND": "2"}])
 def test_producer_count_and_stage_knobs_do_not_change_bytes(knobs, monkeypatch):
     """The launch geometry (producer warps, rows per stage, band size) is a performance choice: results are identical."""
