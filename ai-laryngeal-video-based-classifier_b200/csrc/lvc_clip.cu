@@ -191,6 +191,7 @@ __device__ __forceinline__ int4 pil_tap(int d) {
   }
   return make_int4(xmin, k[0], k[1], k[2]);
 }
+// Channel c of a packed pixel word is taken with one PRMT (__byte_perm(w, 0, 0x4440 + c)) instead of shift + mask.
 // Pillow's clip8 is the identity here: bilinear weights are non-negative and their integer sum is within
 // 2^22 +- 2 (<= 3 taps, each rounded to nearest), so 2^21 + sum(p*k) >> 22 stays in [0, 255] for p in [0, 255].
 __device__ __forceinline__ int clip8(int v) { return v; }
@@ -625,8 +626,8 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           uint32_t packed = 0;
 #pragma unroll
           for (int c = 0; c < 3; ++c) {
-            const int ss = (1 << 21) + (int)((w0 >> (8 * c)) & 0xffu) * hx.y + (int)((w1 >> (8 * c)) & 0xffu) * hx.z +
-                           (int)((w2 >> (8 * c)) & 0xffu) * hx.w;
+            const int ss = (1 << 21) + (int)__byte_perm(w0, 0u, 0x4440u + c) * hx.y + (int)__byte_perm(w1, 0u, 0x4440u + c) * hx.z +
+                           (int)__byte_perm(w2, 0u, 0x4440u + c) * hx.w;
             packed |= (uint32_t)clip8(ss >> 22) << (8 * c);
           }
           reinterpret_cast<uint32_t*>(inter)[(oyr - h->rlo) * S + x] = packed;
@@ -666,8 +667,8 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
         int v[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          const int ss = (1 << 21) + (int)((w0 >> (8 * c)) & 0xffu) * ty.y + (int)((w1 >> (8 * c)) & 0xffu) * ty.z +
-                         (int)((w2 >> (8 * c)) & 0xffu) * ty.w;
+          const int ss = (1 << 21) + (int)__byte_perm(w0, 0u, 0x4440u + c) * ty.y + (int)__byte_perm(w1, 0u, 0x4440u + c) * ty.z +
+                         (int)__byte_perm(w2, 0u, 0x4440u + c) * ty.w;
           v[c] = clip8(ss >> 22);
         }
         store_px(std::integral_constant<int, -1>{}, eoff, v);
