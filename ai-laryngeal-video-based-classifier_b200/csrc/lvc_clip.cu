@@ -30,10 +30,9 @@ enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
 // cv2 / torch chains; the ViViT preset runs two Pillow passes on top of the resize and is bound by consumer issue,
 // so it gets four (measured with 2+ producer warps: 155 -> 135 us on config 2; the other modes lose with four).
 __host__ __device__ constexpr int groups_of(int mode) { return mode == MODE_VIVIT ? 4 : 2; }
-// Producer warps: stage n of a CTA's stream belongs to warp n % kProducers.  One warp issues a stage's bulk copies
-// lane by lane (UBLKCP is a uniform-datapath instruction: ELECT + 5 R2UR + UBLKCP per copy, ~160 cycles each,
-// measured 0.5 us + 0.165 us per output row and stage), which bounded the small-source configs; four warps
-// issue four stages' copies concurrently.
+// Producer warps: stage n of a CTA's stream belongs to warp n % kProducers.  One warp needs 0.5 us + 0.165 us per
+// output row to set up and issue a stage (serial tap / address / header chain, then UBLKCP lane by lane: it is a
+// uniform-datapath instruction), which bounded the small-source configs; four warps work on four stages concurrently.
 #ifndef LVC_CLIP_PRODUCERS
 #define LVC_CLIP_PRODUCERS 4
 #endif
