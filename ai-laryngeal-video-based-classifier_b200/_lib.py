@@ -14,6 +14,8 @@ SAMPLE = {"uniform": 0, "random_window": 1, "random": 2}
 VARIANT_DATASET, VARIANT_CLAMPED, VARIANT_NUMPY_INFER = 0, 1, 2
 LUT_DIV, LUT_MUL64 = 0, 1
 HF_SRC_HOST = 1
+DEVERR_FRAME_TOO_WIDE, DEVERR_FRAME_TOO_LARGE = 1, 2
+B200_SMS, B200_MAX_SMEM = 148, 232448
 RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL, RESAMPLE_PIL_SHORT = 0, 1, 2, 3
 LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC, LAYOUT_TOKENS = 0, 1, 2, 3
 DT_F32, DT_BF16, DT_U8 = 0, 1, 2
@@ -35,6 +37,12 @@ class ClipDesc(C.Structure):
                 ("out_size", C.c_int32), ("batch", C.c_int32), ("num_frames", C.c_int32),
                 ("max_width", C.c_int32), ("tok_kt", C.c_int32), ("tok_kh", C.c_int32), ("tok_kw", C.c_int32),
                 ("mean", C.c_float * 3), ("std", C.c_float * 3), ("src_order", C.c_int32), ("src_float", C.c_int32)]
+
+
+class ClipPlan(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("rows_per_stage", "ring_bytes", "ring_offset", "slot_pitch", "stages_of_widest",
+                                          "bands", "rows_per_band", "producers", "grid", "threads", "smem_bytes")] + \
+               [("reserved", C.c_int32 * 5)]
 
 
 class LetterboxGeom(C.Structure):
@@ -74,6 +82,9 @@ _SIGS = {
                                       C.c_void_p, C.c_void_p]),
     "lvc_hf_clip_forward_ex": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lvc_clip_validate": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_void_p]),
+    "lvc_device_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.c_int32]),
+    "lvc_clip_plan_query": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_int32, C.c_int32, C.POINTER(ClipPlan)]),
     "lvc_torch_randint": (C.c_int, [C.POINTER(Rng), C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "lvc_torch_rand": (C.c_float, [C.POINTER(Rng)]),
     "lvc_train_aug_draw": (C.c_int, [C.POINTER(Rng), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double,

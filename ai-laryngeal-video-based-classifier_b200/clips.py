@@ -12,6 +12,7 @@ normalisation of a reference recipe, in a single fused kernel launch.  Presets:
   vivit_raw     RAW frames -> VivitImageProcessor (Pillow shortest edge 256, crop 224)   vivit_transformer/data_preprocessing.py:16
   timesformer_raw  RAW frames -> VideoMAE-class processor (shortest edge 224, crop 224)  timesformer_transformer/data_preprocessing_timesformer.py:16
 """
+import collections
 import ctypes as C
 
 import numpy as np
@@ -48,6 +49,28 @@ def build_lut(kind, scale, offset, mean, std):
     _lib.check(_lib.lib().lvc_build_lut(kind, float(scale), int(bool(offset)), m, s,
                                         out.ctypes.data_as(C.POINTER(C.c_float))), "build_lut")
     return torch.from_numpy(out).view(3, 256)
+
+
+def device_status(clear=True, device=None):
+    """Contract violations the kernels found on the device since the last call (``lvc_device_status``): a set of
+    names, empty when all is well.  Synchronises the current stream.  The Python face validates every batch on the
+    host before launching (``lvc_clip_validate``), so a non-empty answer means a caller bypassed it."""
+    dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+    with torch.cuda.device(dev):
+        flags = C.c_uint32(0)
+        _lib.check(_lib.lib().lvc_device_status(torch.cuda.current_stream(dev).cuda_stream, C.byref(flags), int(clear)),
+                   "lvc_device_status")
+    names = {_lib.DEVERR_FRAME_TOO_WIDE: "frame_too_wide", _lib.DEVERR_FRAME_TOO_LARGE: "frame_too_large"}
+    return {n for bit, n in names.items() if flags.value & bit}
+
+
+def clip_plan(desc, has_boxes=False, sm_count=0, max_smem=0):
+    """Launch geometry ``lvc_clip_forward`` derives from a descriptor (host arithmetic; pass sm_count / max_smem to
+    ask without a device, e.g. ``_lib.B200_SMS, _lib.B200_MAX_SMEM``)."""
+    plan = _lib.ClipPlan()
+    _lib.check(_lib.lib().lvc_clip_plan_query(C.byref(desc), int(bool(has_boxes)), int(sm_count), int(max_smem),
+                                              C.byref(plan)), "lvc_clip_plan_query")
+    return {n: getattr(plan, n) for n, _ in _lib.ClipPlan._fields_ if n != "reserved"}
 
 
 def tapped_row_bytes(videos, indices, boxes, T, S=224):
@@ -142,11 +165,13 @@ class ClipBuilder:
             self.lut = build_lut(kind, scale, offset, self.mean, self.std).to(self.device)
         _lib.lib()  # fail now, loudly, if the CUDA library is missing
         self.launches = 0
-        self.allow_pinned_host = False
         self.last_h2d_bytes = 0
+        # batches whose kernels may still be running: (event, batch).  A batch keeps its tables AND its videos alive
+        # (zero-copy launches read the caller's pinned host frames over PCIe for as long as the kernel runs)
+        self._inflight = collections.deque()
 
     # -- host-side packing of the small per-batch tables into ONE pinned upload ------------------
-    def _tables(self, videos, indices, boxes, aug=None):
+    def _tables(self, videos, indices, boxes, aug=None, allow_pinned_host=False):
         B, T = len(videos), self.num_frames
         idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int32).reshape(B, T))
         # boxes already on the device (yolo.best_boxes): consumed in place, no host round trip
@@ -168,7 +193,7 @@ class ClipBuilder:
         max_w = self._max_h = 0
         self._host_src = False
         for i, v in enumerate(videos):
-            resident = v.is_cuda or (self.allow_pinned_host and v.is_pinned())
+            resident = v.is_cuda or (allow_pinned_host and v.is_pinned())
             if v.dtype != torch.uint8 or v.dim() != 4 or v.shape[-1] != 3 or not resident or not v.is_contiguous():
                 raise ValueError("each video must be a contiguous CUDA uint8 tensor of shape (N, H, W, 3)")
             if min(v.shape[:3]) < 1:   # the reference raises on a video without frames (vivit .../dataset.py:217)
@@ -196,7 +221,7 @@ class ClipBuilder:
         p_box = dev_boxes.data_ptr() if dev_boxes is not None else (p + off_box if boxes is not None else None)
         return dev, host, p, p + off_idx, p_box, max_w
 
-    def prepare(self, videos, indices, boxes=None, aug=None):
+    def prepare(self, videos, indices, boxes=None, aug=None, allow_pinned_host=False):
         """Upload the per-batch tables (video descriptors, indices, boxes, augmentation draws: a few KB,
         one pinned copy) and return a ``ClipBatch`` that ``run`` can launch any number of times.
         ``aug``: (B, 4) int {short-side size, crop top, crop left, flip} per clip -- the train chain of the
@@ -206,9 +231,13 @@ class ClipBuilder:
             raise ValueError("aug belongs to the pytorchvideo chain (preset 'ptv_eval')")
         if boxes is not None and self.resample == _lib.RESAMPLE_PIL_SHORT:
             raise ValueError("the *_raw presets take whole frames (no ROI boxes)")
-        tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes, aug)
+        tables, host, p_vid, p_idx, p_box, max_w = self._tables(videos, indices, boxes, aug, allow_pinned_host)
         d = _lib.ClipDesc(self.resample, _LAYOUTS[self.layout], _DTYPES[self.dtype], 224, B, T, max_w, *self.patch,
                           (C.c_float * 3)(*self.mean), (C.c_float * 3)(*self.std), self.src_order, int(self.float_frames))
+        # the video table sits at offset 0 of the pinned staging buffer: the C side checks it against the descriptor
+        # on the host (a video wider than max_width etc. is LVC_E_SHAPE -> ValueError here, not a device fault)
+        max_h = self._max_h if self.resample == _lib.RESAMPLE_PIL_SHORT else 0
+        _lib.check(_lib.lib().lvc_clip_validate(C.byref(d), max_h, host.data_ptr()), "lvc_clip_validate")
         cb = ClipBatch(d, tables, host, p_vid, p_idx, p_box, list(videos),
                        _shape(self.layout, B, T, patch=self.patch))
         cb.p_aug = self._p_aug
@@ -243,7 +272,11 @@ class ClipBuilder:
         self.launches += _lib.lib().lvc_clip_launch_count(C.byref(batch.desc))
         return out
 
-    def __call__(self, videos, indices, boxes=None, out=None, stats=None, aug=None):
+    def _retire(self):
+        while self._inflight and self._inflight[0][0].query():
+            self._inflight.popleft()
+
+    def __call__(self, videos, indices, boxes=None, out=None, stats=None, aug=None, allow_pinned_host=False):
         """videos: list of B CUDA uint8 (N,H,W,3) tensors; indices: (B,T) ints; boxes: (B,T,4) int
         xyxy or None (a box with x1 < 0 = no detection = full frame); out: optional preallocated
         output; stats: optional CUDA int64 (B,) checksum accumulator.  Returns the clip tensor
@@ -251,10 +284,16 @@ class ClipBuilder:
         if len(videos) == 0:
             return torch.empty(_shape(self.layout, 0, self.num_frames, patch=self.patch), dtype=self.dtype,
                                device=self.device)
-        batch = self.prepare(videos, indices, boxes, aug)
+        batch = self.prepare(videos, indices, boxes, aug, allow_pinned_host)
         out = self.run(batch, out, stats)
-        batch.tables.record_stream(torch.cuda.current_stream(self.device))
-        self._keep = batch  # staging buffers must outlive the enqueued work
+        stream = torch.cuda.current_stream(self.device)
+        batch.tables.record_stream(stream)
+        # tables, staging buffer and the videos themselves must outlive the enqueued work: park the batch behind an
+        # event and drop it only once the event has completed
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        self._inflight.append((ev, batch))
+        self._retire()
         return out
 
 
@@ -271,11 +310,7 @@ class ClipBuilder:
         if zero_copy is None:
             zero_copy = all((not v.is_cuda) and v.is_pinned() for v in host_videos) and self.resample != _lib.RESAMPLE_PTV_EVAL
         if zero_copy:
-            self.allow_pinned_host = True
-            try:
-                res = self(host_videos, indices, boxes=boxes, out=out, stats=stats)
-            finally:
-                self.allow_pinned_host = False
+            res = self(host_videos, indices, boxes=boxes, out=out, stats=stats, allow_pinned_host=True)
             if self.resample == _lib.RESAMPLE_PIL_SHORT:
                 self.last_h2d_bytes = raw_crop_bytes(host_videos, T, self.shortest_edge)
             else:

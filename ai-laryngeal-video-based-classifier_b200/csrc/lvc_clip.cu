@@ -49,7 +49,8 @@ struct StageHdr {
   int frame;      // output frame id b*T + t
   int sw;         // source window width (pixels); PTV: full frame width
   int oy0;        // first output row of this stage
-  int flags;      // bit 0: exact 2x2 down-scale (cv::resize switches to INTER_AREA)
+  int flags;      // bit 0: exact 2x2 down-scale (cv::resize switches to INTER_AREA); bit 1: hflip (PTV train chain);
+                  // bit 2: the item's rows do not fit the ring (contract violation): nothing was fetched, skip the rows
   int ox;         // PTV: first source column held in the row slots
   int nw;         // PTV: width of the short-side-scaled image
   int left;       // PTV: centre-crop offset in the scaled image
@@ -77,7 +78,9 @@ struct ClipParams {
   int v_stages;              // VIVIT: stages per band (resized rows incl. the Pillow halo, rounded up to rps)
   int ring_off;              // byte offset of the source-row ring in shared memory
   int total_items;           // B*T*bands
-  int rps, stages, pitch;    // rows per stage, ring depth, bytes per source-row slot
+  int rps, stages, pitch;    // rows per stage, barrier slots in use (= kMaxStages), bytes per row slot of the WIDEST video
+  int ring_bytes;            // size of the byte-granular source-row ring
+  unsigned* err;             // device error word (LVC_DEVERR_*), never NULL
   int producers;             // active producer warps (<= kProducers, <= stages)
   int merge_rows;            // fetch the (y, y+1) rows of a full-width tap pair with one copy
   float mean[3], std[3];     // PTV normalisation
@@ -284,7 +287,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   const int stages_per_item = MODE == MODE_VIVIT ? p.v_stages : p.rows_per_band / p.rps;
 
   if (tid == 0) {
-    for (int s = 0; s < p.stages; ++s) {
+    for (int s = 0; s < kMaxStages; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], kConsumers / 32);
     }
@@ -311,8 +314,15 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
     const uint64_t policy = policy_evict_first();
     const int nrows = 2 * p.rps;
     const unsigned lanes = nrows >= 32 ? 0xffffffffu : ((1u << nrows) - 1u);
-    int slot = 0;          // ring position and phase advance incrementally (no per-stage div / mod)
-    uint32_t phase = 0;
+    // Byte-granular ring: a stage takes 2*rps row slots of THIS item's row size (an ROI row is a third of a frame
+    // row: the same shared memory then holds 2-3x as many stages in flight), placed by a bump allocator that wraps
+    // when the stage does not fit before the end.  Every producer warp runs the allocator for every stage (sizes
+    // depend only on the item), so all warps agree on the offsets without talking to each other.  Stage n uses
+    // barrier slot n % 16; before filling it the owner waits for the YOUNGEST earlier stage whose bytes overlap the
+    // new range, or stage n - 16 (the slot's previous user) -- consumers release stages in order, so that one wait
+    // covers every older stage.  Lane l < 16 remembers the byte range of the latest stage with n % 16 == l.
+    int n = 0, head = 0;   // stage sequence number, allocator position
+    int hs = 0, he = 0;    // lane's remembered byte range
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       const int f = item / p.bands, band = item - f * p.bands;
       const int b = f / p.T;
@@ -366,19 +376,38 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
       const bool full_width = MODE != MODE_PTV && ox == 0 && sw == v.width && env_merge;
       const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
       const uint64_t buf_end = v.base + (uint64_t)v.nbytes;
-      for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
+      // row slot of this item: the window's bytes + alignment slack, rounded to 16 (+16 to stagger banks)
+      const int item_pitch = ((sw * 3 + 15 + 15) & ~15) + 16;
+      const int stage_bytes = nrows * item_pitch;
+      // a window that does not fit the ring even alone (a video much wider than desc.max_width, which sized the ring):
+      // fetch nothing, tell the consumers to skip the rows and raise the device error word (lvc_device_status)
+      const bool bad = stage_bytes > p.ring_bytes;
+      if (bad && warp == 0 && lane == 0) atomicOr(p.err, (unsigned)LVC_DEVERR_FRAME_TOO_WIDE);
+      for (int st = 0; st < stages_per_item; ++st, ++n) {
+        const int slot = n & (kMaxStages - 1);
+        const int sbytes = bad ? 0 : stage_bytes;
+        int start = head;
+        if (start + sbytes > p.ring_bytes) start = 0;
+        head = start + sbytes;
         const bool mine = (turn == warp);
         turn = (turn + 1 == np) ? 0 : turn + 1;
+        if (mine) {
+          int m = n - ((n - lane) & (kMaxStages - 1));   // latest stage < n with m % 16 == lane ...
+          if (m == n) m -= kMaxStages;                   // ... which for lane == slot is the slot's previous user
+          const bool dep_l = lane < kMaxStages && m >= 0 && (lane == slot || (hs < start + sbytes && start < he));
+          const int dep = __reduce_max_sync(0xffffffffu, dep_l ? m : -1);
+          if (dep >= 0 && lane == 0) mbar_wait(&empty[dep & (kMaxStages - 1)], (uint32_t)(dep >> 4) & 1u);
+          __syncwarp();
+        }
+        if (lane == slot) { hs = start; he = start + sbytes; }
         if (!mine) continue;
         const int oy_first = MODE == MODE_VIVIT ? rlo + st * p.rps : band * p.rows_per_band + st * p.rps;
-        if (lane == 0) mbar_wait(&empty[slot], phase ^ 1u);
-        __syncwarp();
         uint32_t my_bytes = 0, bulk_bytes = 0;
         int my_off = 0, cb = 0;
         unsigned roff = 0;
         uint64_t a = 0;
         bool leader = false;
-        uint8_t* stage_base = ring + (size_t)slot * nrows * p.pitch;
+        uint8_t* stage_base = ring + start;
         if (lane < nrows) {
           const int r = lane >> 1, oyr = min(oy_first + r, S - 1);   // VIVIT halo stages may run past the last row
           if (MODE != MODE_VIVIT) roff = row_part(p, fo.rowmul, oyr);
@@ -401,13 +430,12 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           const uint64_t addr = frame_base + (uint64_t)(oy + ysrc) * row_bytes + (uint64_t)ox * 3u;
           a = addr & ~(uint64_t)15;
           const uint32_t shift = (uint32_t)(addr - a);
-          my_bytes = (shift + (uint32_t)sw * 3u + 15u) & ~15u;
-          if (my_bytes > (uint32_t)p.pitch) __trap();  // video wider than desc.max_width
+          my_bytes = (shift + (uint32_t)sw * 3u + 15u) & ~15u;   // <= item_pitch - 16 by construction
           const unsigned same = __match_any_sync(lanes, ysrc);
           const int lead = __ffs(same) - 1;
-          leader = (lead == lane);
-          my_off = (int)(stage_base - ring) + lead * p.pitch + (int)shift;
-          bulk_bytes = my_bytes;
+          leader = (lead == lane) && !bad;
+          my_off = start + lead * item_pitch + (int)shift;
+          bulk_bytes = bad ? 0u : my_bytes;
           if (a + my_bytes > buf_end) bulk_bytes = (uint32_t)((buf_end - a) & ~(uint64_t)15);
           if (!leader) bulk_bytes = 0;
           // Full-width rows y and y+1 are contiguous in memory: when the two taps of an output row are such a pair
@@ -416,7 +444,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           const unsigned peer_same = __shfl_xor_sync(lanes, same, 1);
           const int y_peer = __shfl_xor_sync(lanes, ysrc, 1);
           const uint32_t merged = (shift + 2u * (uint32_t)row_bytes + 15u) & ~15u;
-          int pair = !(lane & 1) && full_width && same == (1u << lane) && peer_same == (2u << lane) && y_peer == ysrc + 1 &&
+          int pair = !(lane & 1) && full_width && !bad && same == (1u << lane) && peer_same == (2u << lane) && y_peer == ysrc + 1 &&
                      a + merged <= buf_end;
           pair |= __shfl_xor_sync(lanes, pair, 1);
           const int off_even = __shfl_xor_sync(lanes, my_off, 1);
@@ -438,13 +466,14 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           h->roff[lane >> 1] = roff;
         }
         if (lane == 0) {
-          h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first; h->flags = (area ? 1 : 0) | (flip << 1);
+          h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first;
+          h->flags = (area ? 1 : 0) | (flip << 1) | (bad ? 4 : 0);
           h->ox = ox; h->nw = (MODE == MODE_VIVIT) ? own_hi : nw; h->left = left; h->rlo = rlo;
           h->obase = fo.base; h->cstride = fo.cstride; h->rowmul = fo.rowmul; h->clip = b;
         }
         if (leader && bulk_bytes < my_bytes) {
           // last bytes of the buffer: not a whole 16-byte granule, copy them by hand
-          uint8_t* slot_ptr = stage_base + (size_t)lane * p.pitch;
+          uint8_t* slot_ptr = stage_base + (size_t)lane * item_pitch;
           for (uint64_t q = a + bulk_bytes; q < buf_end && q < a + my_bytes; ++q)
             slot_ptr[q - a] = *reinterpret_cast<const uint8_t*>(q);
         }
@@ -452,7 +481,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
         if (lane == 0) mbar_arrive_expect_tx(&full[slot], total);
         __syncwarp();
         if (leader && bulk_bytes)
-          bulk_g2s(stage_base + (size_t)lane * p.pitch, reinterpret_cast<const void*>(a), bulk_bytes,
+          bulk_g2s(stage_base + (size_t)lane * item_pitch, reinterpret_cast<const void*>(a), bulk_bytes,
                    &full[slot], policy);
       }
     }
@@ -500,7 +529,8 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   };
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-    for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, p.stages)) {
+    bool item_bad = false;
+    for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages)) {
       mbar_wait(&full[slot], phase);
       const StageHdr* h = &hdrs[slot];
       const int sw = h->sw, flags = h->flags, oy0 = h->oy0;
@@ -643,7 +673,8 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
         }
       };
       using std::integral_constant;
-      if (MODE == MODE_PTV) do_rows(std::false_type{}, integral_constant<int, -1>{});        // stores by itself
+      if (flags & 4) item_bad = true;                                                          // nothing was fetched
+      else if (MODE == MODE_PTV) do_rows(std::false_type{}, integral_constant<int, -1>{});        // stores by itself
       else if (p.f32src) do_rows(std::true_type{}, integral_constant<int, -1>{});             // float frames: rare
       else if (MODE == MODE_VIVIT) do_rows(std::false_type{}, integral_constant<int, -1>{});  // rows go to the intermediate buffer
       else if (p.out_dtype == LVC_DT_BF16) do_rows(std::false_type{}, integral_constant<int, LVC_DT_BF16>{});
@@ -658,7 +689,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
       consumers_bar(kConsumers);
       const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
       const int band = item % p.bands, ylo = band * p.rows_per_band, rlo = vt[ylo].x;
-      for (int y = ylo + g; y < ylo + p.rows_per_band; y += kGroups) {
+      for (int y = ylo + g; y < ylo + p.rows_per_band && !item_bad; y += kGroups) {
         const size_t eoff = (size_t)obase + (size_t)(row_part(p, rowmul, y) + xoff);
         const int4 ty = vt[y];
         const uint32_t* tp = reinterpret_cast<const uint32_t*>(inter) + (ty.x - rlo) * S + x;
@@ -687,10 +718,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
 // ------------------------------------------------------------------------------------------
 namespace {
 
-int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
+int env_int(const char* name, int dflt) { return lvc_knob_int(name, dflt); }   // gated profiling knobs (lvc_internal.h)
 
 struct DeviceInfo {
   int sms = 0, max_smem = 0;
@@ -710,6 +738,9 @@ const DeviceInfo& device_info() {
   return di;
 }
 
+// Contract violations found on the device (sticky until read): lvc_device_status()
+__device__ unsigned g_dev_error;
+
 template <int MODE>
 int launch(const ClipParams& p, int grid, size_t smem, cudaStream_t st) {
   LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -718,20 +749,7 @@ int launch(const ClipParams& p, int grid, size_t smem, cudaStream_t st) {
   return LVC_OK;
 }
 
-}  // namespace
-
-extern "C" int lvc_clip_launch_count(const lvc_clip_desc* d) { return d ? 1 : 0; }
-
-extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
-                                const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
-                                void* stream) {
-  return lvc_clip_forward_aug(d, videos, indices, boxes, nullptr, lut, out, stats, stream);
-}
-
-extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
-                                    const int32_t* boxes, const int32_t* aug, const float* lut, void* out,
-                                    uint64_t* stats, void* stream) {
-  if (!d || !videos || !indices || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: NULL argument");
+int check_desc(const lvc_clip_desc* d, bool boxes, bool aug, bool lut) {
   if (d->out_size != S) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: out_size %d unsupported (224 only)", d->out_size);
   if (d->batch <= 0 || d->num_frames <= 0 || d->max_width <= 0)
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: batch, num_frames and max_width must be positive");
@@ -755,74 +773,73 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   } else if (d->out_dtype != LVC_DT_U8 && !lut) {
     return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: float output needs a LUT (lvc_build_lut)");
   }
-  if (boxes && (reinterpret_cast<uintptr_t>(boxes) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: boxes must be 16-byte aligned");
   if (aug && !ptv) return lvc_fail(LVC_E_NOTSUP, "lvc_clip_forward: the augmentation table belongs to the pytorchvideo chain (LVC_RESAMPLE_PTV_EVAL)");
-  if (aug && (reinterpret_cast<uintptr_t>(aug) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: aug must be 16-byte aligned");
   if ((int64_t)d->batch * d->num_frames > (1 << 24)) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: too many frames in one call");
+  return LVC_OK;
+}
 
-  const DeviceInfo& di = device_info();
-  if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "lvc_clip_forward: no usable CUDA device: %s", cudaGetErrorString(di.err));
-
+// Launch geometry for a descriptor on a device with `sms` SMs and `max_smem` bytes of opt-in shared memory per CTA.
+// Pure host arithmetic (lvc_clip_plan_query runs it without a device).
+int make_plan(const lvc_clip_desc* d, bool boxes, int sms, int max_smem, ClipParams& p, size_t& smem, int& grid) {
+  const bool ptv = d->resample == LVC_RESAMPLE_PTV_EVAL;
   const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
-  ClipParams p{};
-  p.videos = videos; p.indices = indices; p.boxes = boxes; p.aug = aug; p.lut = lut; p.out = out;
-  p.stats = reinterpret_cast<unsigned long long*>(stats);
-  p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
-  for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
-  p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
-  p.bgr = d->src_order == LVC_SRC_BGR;
-  p.f32src = d->src_float != 0 && !ptv;
-  p.kh_shift = -1;
-  for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
-  // ring geometry: slot = widest row + alignment slack, rounded to 16 (+16 to stagger banks)
+  // row slot of the widest video: window bytes + alignment slack, rounded to 16 (+16 to stagger banks)
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
-  // 8 output rows per stage amortise the per-stage bookkeeping when the row slots are small enough
-  // to keep >= 3 stages in flight; wide sources (1080p) use 4 rows per stage and a deeper ring
+  const int budget_all = std::min(max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, 96 * 1024));
   // MODE_VIVIT: the Pillow stage needs its vertical window on chip.  A band of R output rows spans at most
   // floor((R-1)*7/8) + 4 resized rows (halo included); pick the band count that minimises rounds x rows per
-  // item (whole frames when the batch is large enough that quantisation does not matter).  Fewer rows in
-  // the intermediate buffer also leave more shared memory for the source-row ring.
+  // item (whole frames when the batch is large enough that quantisation does not matter) AMONG the candidates whose
+  // intermediate buffer leaves the source-row ring three 4-row stages of the widest video (a large batch of 1080p
+  // frames would otherwise pick whole-frame items and starve -- or not fit -- the ring); when none does, the
+  // smallest buffer.
   int v_nb = 1, v_res = S;
+  auto vivit_ring_base = [](int res) { return (kVivitInterOff + (res + 7) / 8 * 8 * kRowBytes + 127) / 128 * 128; };
   if (mode == MODE_VIVIT) {
     static const int kVB[] = {1, 2, 4, 7, 8, 14};
     const long long nframes = (long long)d->batch * d->num_frames;
     const int forced_nb = env_int("LVC_CLIP_VBANDS", 0);
     long long best_cost = -1;
+    bool best_ok = false;
     for (int nb : kVB) {
       const int R = S / nb;
       const int res = ((R - 1) * 7) / 8 + 4;   // nb == 1: rows 13..210, the crop never reads the rest
-      const long long rounds = (nframes * nb + di.sms - 1) / di.sms;
+      const long long rounds = (nframes * nb + sms - 1) / sms;
       const long long cost = rounds * ((res + 7) / 8 * 8 + R / 2 + 6);   // resize rows + Pillow vertical rows + per-item fixed
-      if (forced_nb ? nb == forced_nb : (best_cost < 0 || cost < best_cost)) { best_cost = cost; v_nb = nb; v_res = res; }
+      const bool ok = budget_all - vivit_ring_base(res) >= 3 * 8 * p.pitch;
+      bool take;
+      if (forced_nb) take = nb == forced_nb;
+      else take = best_cost < 0 || (ok && !best_ok) || (ok == best_ok && (ok ? cost < best_cost : true));
+      if (take) { best_cost = cost; best_ok = ok; v_nb = nb; v_res = res; }
     }
   }
-  const int ring_base = mode == MODE_VIVIT ? (kVivitInterOff + (v_res + 7) / 8 * 8 * kRowBytes + 127) / 128 * 128 : kAuxOff;
-  p.ring_off = ring_base;
+  const int fixed = mode == MODE_VIVIT ? vivit_ring_base(v_res) : kAuxOff;
+  p.ring_off = fixed;
+  const int budget = budget_all - fixed;
   p.rps = env_int("LVC_CLIP_RPS", 0);
   if (p.rps == 0) {
-    const int budget0 = std::min(di.max_smem, 200 * 1024) - ring_base;
-    // full-frame sources keep the bus busy only with a finely sliced ring (a slot being consumed cannot be refilled:
+    // full-frame sources keep the bus busy only with a finely sliced ring (a stage being consumed cannot be refilled:
     // 3 stages leave a third of the ring idle, 6 a sixth; cfg 3: 60 -> 53 us with 4 producers); ROI rows are much
-    // shorter than their slots and the ViViT preset is consumer-bound: those prefer fewer, larger stages
+    // shorter than a frame row (the ring is byte-granular: their stages take what they need) and the ViViT preset is
+    // consumer-bound: those prefer fewer, larger stages
     const int want_stages = (boxes || mode == MODE_VIVIT) ? 3 : 6;
-    p.rps = (budget0 / (16 * p.pitch) >= want_stages) ? 8 : 4;
+    p.rps = (budget / (16 * p.pitch) >= want_stages) ? 8 : 4;
   }
   if (p.rps < 2 || p.rps > kMaxRPS || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
-  const int fixed = ring_base;
-  const int smem_budget = std::min(di.max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, fixed + 64 * 1024));
   int stage_bytes = 2 * p.rps * p.pitch;
-  while ((smem_budget - fixed) / stage_bytes < 2 && p.rps > 2) {   // very wide sources: fewer rows per stage (groups beyond rps idle)
+  while (budget / stage_bytes < 2 && p.rps > 2) {   // very wide sources: fewer rows per stage (groups beyond rps idle)
     do --p.rps; while (S % p.rps);
     stage_bytes = 2 * p.rps * p.pitch;
   }
-  p.stages = std::min(kMaxStages, (smem_budget - fixed) / stage_bytes);
-  if (p.stages < 2) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: max_width %d does not fit the shared-memory ring", d->max_width);
-  const size_t smem = (size_t)fixed + (size_t)p.stages * stage_bytes;
+  if (budget / stage_bytes < 2) return lvc_fail(LVC_E_SHAPE, "lvc_clip_forward: max_width %d does not fit the shared-memory ring", d->max_width);
+  p.stages = kMaxStages;
+  // the ring never needs more than 16 stages of the widest rows (small sources then leave room for two CTAs per SM)
+  p.ring_bytes = (int)std::min<long long>((long long)budget, (long long)kMaxStages * stage_bytes) & ~127;
+  smem = (size_t)fixed + (size_t)p.ring_bytes;
   p.merge_rows = env_int("LVC_CLIP_MERGE", 1);
-  p.producers = std::max(1, std::min(std::min(kProducers, p.stages), env_int("LVC_CLIP_NP", kProducers)));
+  p.producers = std::max(1, std::min(kProducers, env_int("LVC_CLIP_NP", kProducers)));
 
-  const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)di.max_smem / (smem + 1024)));
-  const int grid_max = di.sms * ctas_per_sm;
+  const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)max_smem / (smem + 1024)));
+  const int grid_max = sms * ctas_per_sm;
   const int frames = d->batch * d->num_frames;
   // band = output rows per work item.  A CTA walks its items round-robin, and every item boundary costs about
   // four rows' worth of time (descriptor fetch, tap set-up, a partly drained ring; measured on cfg 3 / cfg 4 with
@@ -841,7 +858,114 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   p.bands = S / p.rows_per_band;
   if (mode == MODE_VIVIT) { p.bands = v_nb; p.rows_per_band = S / v_nb; p.v_stages = (v_res + p.rps - 1) / p.rps; }
   p.total_items = frames * p.bands;
-  const int grid = std::min(p.total_items, grid_max);
+  grid = std::min(p.total_items, grid_max);
+  return LVC_OK;
+}
+
+}  // namespace
+
+extern "C" int lvc_clip_launch_count(const lvc_clip_desc* d) { return d ? 1 : 0; }
+
+extern "C" int lvc_clip_plan_query(const lvc_clip_desc* d, int32_t has_boxes, int32_t sm_count, int32_t max_smem,
+                                   lvc_clip_plan* out) {
+  if (!d || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_plan_query: NULL argument");
+  if (int rc = check_desc(d, has_boxes != 0, false, true)) return rc;
+  if (sm_count <= 0 || max_smem <= 0) {
+    const DeviceInfo& di = device_info();
+    if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "lvc_clip_plan_query: no usable CUDA device: %s", cudaGetErrorString(di.err));
+    sm_count = di.sms; max_smem = di.max_smem;
+  }
+  ClipParams p{};
+  size_t smem = 0;
+  int grid = 0;
+  if (int rc = make_plan(d, has_boxes != 0, sm_count, max_smem, p, smem, grid)) return rc;
+  const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (d->resample == LVC_RESAMPLE_PTV_EVAL ? MODE_PTV : MODE_VIVIT);
+  *out = lvc_clip_plan{};
+  out->rows_per_stage = p.rps; out->ring_bytes = p.ring_bytes; out->ring_offset = p.ring_off; out->slot_pitch = p.pitch;
+  out->stages_of_widest = p.ring_bytes / (2 * p.rps * p.pitch);
+  out->bands = p.bands; out->rows_per_band = p.rows_per_band; out->producers = p.producers; out->grid = grid;
+  out->threads = mode == MODE_VIVIT ? threads_of(MODE_VIVIT) : threads_of(MODE_CV2);
+  out->smem_bytes = (int32_t)smem;
+  return LVC_OK;
+}
+
+extern "C" int lvc_clip_validate(const lvc_clip_desc* d, int32_t max_height, const lvc_video* host_videos) {
+  if (!d || !host_videos) return lvc_fail(LVC_E_INVAL, "lvc_clip_validate: NULL argument");
+  for (int b = 0; b < d->batch; ++b) {
+    const lvc_video& v = host_videos[b];
+    if (max_height > 0 && v.height > max_height)
+      return lvc_fail(LVC_E_SHAPE, "video %d is %d pixels high, higher than max_height = %d (which sizes the shared-memory buffers)", b, v.height, max_height);
+    if (v.n_frames <= 0 || v.height <= 0 || v.width <= 0)
+      return lvc_fail(LVC_E_INVAL, "video %d: n_frames, height and width must be positive (%d, %d, %d)", b, v.n_frames, v.height, v.width);
+    if (v.width > d->max_width)
+      return lvc_fail(LVC_E_SHAPE, "video %d is %d pixels wide, wider than desc.max_width = %d (which sizes the shared-memory ring)", b, v.width, d->max_width);
+    if (v.base == 0 || (v.base & 15)) return lvc_fail(LVC_E_ALIGN, "video %d: base must be a 16-byte aligned device-readable address", b);
+    if (v.nbytes < (int64_t)v.n_frames * v.height * v.width * 3)
+      return lvc_fail(LVC_E_INVAL, "video %d: nbytes %lld is smaller than n_frames*height*width*3", b, (long long)v.nbytes);
+  }
+  return LVC_OK;
+}
+
+extern "C" int lvc_device_status(void* stream, uint32_t* flags, int32_t clear) {
+  if (!flags) return lvc_fail(LVC_E_INVAL, "lvc_device_status: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned* dptr = nullptr;
+  LVC_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&dptr), g_dev_error));
+  unsigned h = 0;
+  LVC_CUDA_TRY(cudaMemcpyAsync(&h, dptr, sizeof h, cudaMemcpyDeviceToHost, st));
+  if (clear) LVC_CUDA_TRY(cudaMemsetAsync(dptr, 0, sizeof h, st));
+  LVC_CUDA_TRY(cudaStreamSynchronize(st));
+  *flags = h;
+  return LVC_OK;
+}
+
+// device address of the error word for the other translation units' kernels
+unsigned* lvc_dev_error_word() {
+  static thread_local unsigned* ptr = nullptr;
+  static thread_local int dev_of = -1;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  if (dev != dev_of) {
+    if (cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_dev_error) != cudaSuccess) return nullptr;
+    dev_of = dev;
+  }
+  return ptr;
+}
+
+extern "C" int lvc_clip_forward(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
+                                const int32_t* boxes, const float* lut, void* out, uint64_t* stats,
+                                void* stream) {
+  return lvc_clip_forward_aug(d, videos, indices, boxes, nullptr, lut, out, stats, stream);
+}
+
+extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices,
+                                    const int32_t* boxes, const int32_t* aug, const float* lut, void* out,
+                                    uint64_t* stats, void* stream) {
+  if (!d || !videos || !indices || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_forward: NULL argument");
+  if (int rc = check_desc(d, boxes != nullptr, aug != nullptr, lut != nullptr)) return rc;
+  if (boxes && (reinterpret_cast<uintptr_t>(boxes) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: boxes must be 16-byte aligned");
+  if (aug && (reinterpret_cast<uintptr_t>(aug) & 15)) return lvc_fail(LVC_E_ALIGN, "lvc_clip_forward: aug must be 16-byte aligned");
+
+  const DeviceInfo& di = device_info();
+  if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "lvc_clip_forward: no usable CUDA device: %s", cudaGetErrorString(di.err));
+
+  const bool ptv = d->resample == LVC_RESAMPLE_PTV_EVAL;
+  const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
+  ClipParams p{};
+  p.videos = videos; p.indices = indices; p.boxes = boxes; p.aug = aug; p.lut = lut; p.out = out;
+  p.stats = reinterpret_cast<unsigned long long*>(stats);
+  p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
+  for (int c = 0; c < 3; ++c) { p.mean[c] = d->mean[c]; p.std[c] = d->std[c]; }
+  p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
+  p.bgr = d->src_order == LVC_SRC_BGR;
+  p.f32src = d->src_float != 0 && !ptv;
+  p.kh_shift = -1;
+  for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
+  p.err = lvc_dev_error_word();
+  if (!p.err) return lvc_fail(LVC_E_CUDA, "lvc_clip_forward: cannot resolve the device error word");
+  size_t smem = 0;
+  int grid = 0;
+  if (int rc = make_plan(d, boxes != nullptr, di.sms, di.max_smem, p, smem, grid)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (mode == MODE_CV2) return launch<MODE_CV2>(p, grid, smem, st);
   if (mode == MODE_VIVIT) return launch<MODE_VIVIT>(p, grid, smem, st);

@@ -1078,10 +1078,7 @@ int make_out_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t N, bool f
   return LVC_OK;
 }
 
-int env_i(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
+int env_i(const char* name, int dflt) { return lvc_knob_int(name, dflt); }   // gated: lvc_internal.h
 
 // Launch with programmatic stream serialization: the grid may be scheduled while the previous kernel in the stream
 // (the clip kernel of a pipeline, the im2col pass) drains; the kernels call griddep_wait() before touching global data.
@@ -1178,7 +1175,7 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
     const int bcthw = d->x_layout == LVC_LAYOUT_BCTHW;
     const size_t esz = d->x_dtype == LVC_DT_F32 ? 4 : 2;
     const bool vec_ok = g.T % g.kt == 0 && g.H % g.kh == 0 && g.W % g.kw == 0 && (g.W * esz) % 16 == 0 &&
-                        (reinterpret_cast<uintptr_t>(x) & 15) == 0 && runs < (1LL << 31) && !getenv("LVC_IM2COL_SCALAR");
+                        (reinterpret_cast<uintptr_t>(x) & 15) == 0 && runs < (1LL << 31) && !lvc_knob_set("LVC_IM2COL_SCALAR");
     __nv_bfloat16* A = static_cast<__nv_bfloat16*>(workspace);
     if (vec_ok && g.kw == 16) {
       const int nb = (int)((runs + 255) / 256);
@@ -1210,7 +1207,7 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
   p.out = out;
   // Directed-experiment knobs (scripts/gemm_probe.py): results are WRONG with any bit set and some combinations
   // (2 | 4 with the embeddings epilogue) never terminate, so they need a second, explicit opt-in.
-  p.diag = env_i("LVC_PROFILING_KNOBS", 0) ? env_i("LVC_GEMM_DIAG", 0) : 0;
+  p.diag = env_i("LVC_GEMM_DIAG", 0);
   p.diag_a = workspace;
   p.cls = et.cls; p.pos = et.pos; p.temb = et.temb; p.emb_mode = et.mode;
   p.emb_P = g.Ho * g.Wo * (et.mode == 1 ? g.To : 1);   // tokens per batch entry (ViViT) / per frame (TimeSformer)
@@ -1221,7 +1218,7 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
   const int fixed_bytes = 1024 + 2048 + (g.N + 2 * p.BN) * 4 + 16384;  // alignment, barriers, params, store staging
   // two CTAs per SM when TMEM (2 x <=256 columns) and shared memory allow: doubles the epilogue warps,
   // which is what bounds the HBM-bound Swin shape
-  int per_sm = (p.tmem_cols <= 256 && !getenv("LVC_GEMM_ONE_PER_SM")) ? 2 : 1;
+  int per_sm = (p.tmem_cols <= 256 && !lvc_knob_set("LVC_GEMM_ONE_PER_SM")) ? 2 : 1;
   int sm_smem = 0;
   LVC_CUDA_TRY(cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
   for (;; per_sm = 1) {
@@ -1233,7 +1230,7 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
   const size_t smem = (size_t)fixed_bytes + (size_t)p.stages * stage_bytes;
 
   // tensor-bound shapes (no LayerNorm, 128B-swizzle K blocks, even tile split): CTA-pair kernel
-  const bool two_cta = !p.do_ln && p.BK == 64 && p.BN % 128 == 0 && !getenv("LVC_GEMM_1CTA") && sms >= 2;
+  const bool two_cta = !p.do_ln && p.BK == 64 && p.BN % 128 == 0 && !lvc_knob_set("LVC_GEMM_1CTA") && sms >= 2;
   if (et.mode && !two_cta) return lvc_fail(LVC_E_NOTSUP, "embeddings_forward: needs K %% 64 == 0 and embed_dim %% 128 == 0");
   if (two_cta) {
     const int stage2 = (BM + p.BN / 2) * p.BK * 2;
@@ -1261,7 +1258,7 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
     return LVC_OK;
   }
   // short-K shapes with N = 128 (Video Swin-B): weights resident in shared memory, row-in-registers LayerNorm
-  if (g.N == 128 && g.K <= 256 && !getenv("LVC_GEMM_GENERIC")) {
+  if (g.N == 128 && g.K <= 256 && !lvc_knob_set("LVC_GEMM_GENERIC")) {
     const int a_tile = BM * g.K * 2, b_all = g.N * g.K * 2;
     const int fixed3 = 1024 + 4 * kSwinGroups * 4096 + b_all + (BM + g.N) * 64 + 512 + 3 * g.N * 4 + 64;
     p.stages = std::min(env_i("LVC_GEMM_STAGES", 8), (max_smem - fixed3) / a_tile);

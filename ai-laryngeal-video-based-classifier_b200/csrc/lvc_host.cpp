@@ -1,6 +1,7 @@
 // Error reporting and the host-side normalisation look-up table.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "lvc_internal.h"
 
@@ -15,6 +16,20 @@ int lvc_fail(int code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
+
+bool lvc_knobs_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("LVC_PROFILING_KNOBS");
+    return v && v[0] == '1' && v[1] == 0;
+  }();
+  return on;
+}
+int lvc_knob_int(const char* name, int dflt) {
+  if (!lvc_knobs_enabled()) return dflt;
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+bool lvc_knob_set(const char* name) { return lvc_knobs_enabled() && getenv(name) != nullptr; }
 
 extern "C" {
 

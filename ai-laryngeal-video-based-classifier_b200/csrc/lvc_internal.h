@@ -5,6 +5,19 @@
 // Records a thread-local message (printf-style) and returns `code`.
 int lvc_fail(int code, const char* fmt, ...);
 
+// Profiling knobs (LVC_CLIP_*, LVC_GEMM_*, LVC_PIL_*, LVC_NO_PDL, ...): environment variables that change the launch
+// geometry or pick a diagnostic kernel variant.  They are honoured ONLY when LVC_PROFILING_KNOBS=1 was in the environment
+// the first time the library looked (the gate is read once per process); otherwise no launch path reads the environment at all and a
+// stray variable cannot change which kernel runs.  With the gate on, a knob is re-read at every launch (sweep scripts
+// change them between launches).
+bool lvc_knobs_enabled();
+int lvc_knob_int(const char* name, int dflt);   // value of the knob, `dflt` when unset or the gate is off
+bool lvc_knob_set(const char* name);            // knob present (any value) and the gate on
+
+// Device address (current device) of the sticky error word the kernels OR contract violations into (LVC_DEVERR_*);
+// read by lvc_device_status.  NULL when no device is usable.
+unsigned* lvc_dev_error_word();
+
 #ifdef __CUDACC__
 #define LVC_CUDA_TRY(expr)                                                                  \
   do {                                                                                      \

@@ -40,6 +40,8 @@ struct PilParams {
   int ir;                       // rows in the intermediate ring: kCH + kt + 1
   int kt_tok, kh, kw;           // LVC_LAYOUT_TOKENS: patch size (output = GEMM operand A[M][K], bf16)
   int bulk;                     // rows staged with 16-byte-granular bulk copies (frames in pinned HOST memory, read over PCIe)
+  int max_w, max_h;             // the frame size the tables and buffers were sized for (desc.max_width, max_height)
+  unsigned* err;                // device error word (lvc_device_status)
 };
 
 struct Taps { int xmin, n; };
@@ -57,7 +59,7 @@ __device__ Taps pil_taps(int xx, int in_size, int out_size, int* kk, int stride,
   int xmax = (int)__dadd_rn(__dadd_rn(center, support), 0.5);
   if (xmax > in_size) xmax = in_size;
   const int n = xmax - xmin;
-  if (n > kt) __trap();   // frame larger than the descriptor says
+  // n <= kt: the kernel skips frames larger than the descriptor's max_width / max_height before it gets here
   double w[KT];
   double ww = 0.0;
   for (int x = 0; x < n; ++x) {
@@ -150,6 +152,10 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
     const lvc_video v = p.videos[b];
     const int idx = min(max(p.indices[f], 0), v.n_frames - 1);
     const int H = v.height, W = v.width;
+    if (W > p.max_w || H > p.max_h) {   // contract violation (CTA-uniform): leave the frame unwritten, raise the error word
+      if (tid == 0) atomicOr(p.err, (unsigned)LVC_DEVERR_FRAME_TOO_LARGE);
+      continue;
+    }
     __syncthreads();   // previous item is done with the tables and buffers
     if (W != cw || H != ch_) {
       int nh, nw;
@@ -190,7 +196,6 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
             a16 = a & ~(uint64_t)15;
             const uint32_t sh = (uint32_t)(a - a16);
             const uint32_t bytes = (sh + (uint32_t)span + 15u) & ~15u;
-            if (bytes > (uint32_t)p.pitch_words * 4u) __trap();   // frame larger than the descriptor says
             rsh[sl * kCH + lane] = (int)sh;
             bulk_bytes = bytes;
             if (a16 + bytes > buf_end) {   // last bytes of the buffer: not a whole 16-byte granule, copied by hand
@@ -214,7 +219,6 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
         const uint64_t a4 = a & ~(uint64_t)3;
         const int sh = (int)(a - a4);
         const int nwords = (sh + span + 3) >> 2;
-        if (nwords > p.pitch_words) __trap();   // frame larger than the descriptor says
         if (lane == 0) rsh[sl * kCH + j] = sh;
         uint32_t* dst = slot + (size_t)j * p.pitch_words;
         if (a4 + 4u * (uint64_t)nwords <= buf_end) {   // every row but the buffer's last: no per-word bound check
@@ -386,6 +390,9 @@ extern "C" int lvc_hf_clip_forward_ex(const lvc_clip_desc* d, int32_t shortest_e
   p.videos = videos; p.indices = indices; p.lut = lut; p.out = out;
   p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype; p.bgr = d->src_order == LVC_SRC_BGR;
   p.bulk = (flags & LVC_HF_SRC_HOST) != 0;
+  p.max_w = d->max_width; p.max_h = max_height;
+  p.err = lvc_dev_error_word();
+  if (!p.err) return lvc_fail(LVC_E_CUDA, "lvc_hf_clip_forward: cannot resolve the device error word");
   p.edge = shortest_edge; p.kt_tok = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
   // a sample's window [int(c - s + .5), int(c + s + .5)) holds fewer than 2s + 1, i.e. at most ceil(2s), samples
   static const int kTapSteps[] = {2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 15, 17, 19, 21, 23};
@@ -399,8 +406,7 @@ extern "C" int lvc_hf_clip_forward_ex(const lvc_clip_desc* d, int32_t shortest_e
   static const int kSegs[] = {1, 2, 4, 7, 14, 28};
   size_t smem = 0;
   int pick = -1;
-  const char* env_seg = std::getenv("LVC_PIL_NSEG");   // tuning override
-  const int force_seg = env_seg ? std::atoi(env_seg) : 0;
+  const int force_seg = lvc_knob_int("LVC_PIL_NSEG", 0);   // tuning override (gated: lvc_internal.h)
   for (int pass = 0; pass < 2 && pick < 0; ++pass)
     for (int i = 0; i < 6; ++i) {
       if (force_seg > 0 && (kSegs[i] != force_seg || pass == 0)) continue;
@@ -418,7 +424,7 @@ extern "C" int lvc_hf_clip_forward_ex(const lvc_clip_desc* d, int32_t shortest_e
     }
   if (pick < 0) return lvc_fail(LVC_E_SHAPE, "lvc_hf_clip_forward: frames too large for shared memory");
   int threads = 512;
-  if (const char* env_t = std::getenv("LVC_PIL_THREADS")) threads = std::max(256, std::min(kMaxThreads, std::atoi(env_t) / 32 * 32));
+  if (const int env_t = lvc_knob_int("LVC_PIL_THREADS", 0)) threads = std::max(256, std::min(kMaxThreads, env_t / 32 * 32));
   const int per_sm = std::max(1, std::min(std::min(2, 2048 / threads), (int)((size_t)max_smem / (smem + 1024))));
   const int slots = sms * per_sm;
   // Bands per frame: minimise rounds x source rows per item (each band re-reads a halo of ~kt rows)
@@ -430,8 +436,7 @@ extern "C" int lvc_hf_clip_forward_ex(const lvc_clip_desc* d, int32_t shortest_e
     const double cost = std::ceil((double)frames * nb / slots) * (R * scale + p.kt + 16);
     if (cost < best * 0.97) { best = cost; p.bands = nb; p.R = R; }
   }
-  if (const char* env_b = std::getenv("LVC_PIL_BANDS")) {   // tuning override
-    const int nb = std::atoi(env_b);
+  if (const int nb = lvc_knob_int("LVC_PIL_BANDS", 0)) {   // tuning override
     if (nb > 0 && S % nb == 0) { p.bands = nb; p.R = S / nb; }
   }
   p.total_items = frames * p.bands;

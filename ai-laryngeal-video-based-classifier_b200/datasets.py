@@ -193,6 +193,75 @@ class SwinVideoDataset(_BaseDataset):
         return clips[0], labels[0]
 
 
+def crc32_video_seed(basename):
+    """Stable stand-in for the reference's ``hash(os.path.basename(video_path)) % 10000000``: CPython salts ``hash``
+    of str per process (PYTHONHASHSEED), so the reference's per-video seed is only reproducible inside one process.
+    Pass ``seed_fn=lambda n: hash(n) % 10000000`` to get the reference's own values under a fixed PYTHONHASHSEED."""
+    import zlib
+
+    return zlib.crc32(basename.encode("utf-8")) % 10000000
+
+
+class Resnet3dVideoDataset(SwinVideoDataset):
+    """The ``resnet50-3d-video`` copy (resnet50-3d-video/video_classifier/data_config/dataset.py:22-289): same
+    constructor and transforms as the Swin copy, but its sampler (:79-169) returns a plain list and
+      * seeds the stream PER VIDEO with ``hash(basename) % 10000000`` (:95-98) -> ``seed_fn(basename)`` here,
+      * caches the indices per video path (``cached_indices``, :91-93, :166-167): a second epoch reuses them,
+      * re-seeds the global stream to 42 after every draw (:163-164),
+      * can dump the cache as CSV (``save_sampled_indices``, :241-289)."""
+
+    def __init__(self, root_dir=None, mode="train", sampling_method="uniform", num_frames=32, fps=30, stride=0.5,
+                 logger=None, log_dir=None, frame_source=None, augment=None, aug_seed=0, seed_fn=None):
+        super().__init__(root_dir, mode, sampling_method, num_frames, fps, stride, logger, log_dir, frame_source,
+                         augment, aug_seed)
+        self.log_dir = log_dir
+        self.seed_fn = seed_fn or crc32_video_seed
+        self.cached_indices = {}
+
+    def set_random_seed(self, seed):
+        self.rng.seed(seed)
+
+    def get_sampling_indices(self, video_path, total_frames):
+        video_path = str(video_path)
+        if video_path in self.cached_indices:
+            return self.cached_indices[video_path]
+        self.rng.seed(int(self.seed_fn(os.path.basename(video_path))))
+        indices = sampling.get_sampling_indices(self.sampling_method, total_frames, self.num_frames, self.rng)
+        self.set_random_seed(42)
+        self.cached_indices[video_path] = indices
+        return indices
+
+    def get_batch(self, indices):
+        vids = [self.source.frames(i) for i in indices]
+        fidx = [window_subsample(self.get_sampling_indices(self.video_paths[i], v.shape[0]), self.num_frames)
+                for i, v in zip(indices, vids)]
+        aug = None
+        if self.augment:
+            aug = [sampling.train_aug_params(v.shape[1], v.shape[2], self.aug_rng) for v in vids]
+        self.last_aug = aug
+        clips = self.builder(vids, fidx, aug=aug)  # (B, C, T, 224, 224)
+        return clips.unsqueeze(1), torch.tensor([[self.labels[i]] for i in indices], dtype=torch.long)
+
+    def save_sampled_indices(self):
+        """CSV ``video_filename,total_frames,sampled_frames`` of every video's cached indices (:241-289); videos not
+        sampled yet are sampled now.  Returns the path, or None without a ``log_dir`` (the reference only warns)."""
+        import csv
+
+        if not self.log_dir:
+            return None
+        totals = {}
+        for i, vp in enumerate(self.video_paths):
+            totals[str(vp)] = self.source.num_frames(i)
+            self.get_sampling_indices(vp, totals[str(vp)])
+        path = os.path.join(str(self.log_dir), f"sampled_frames_{self.mode}_{self.sampling_method}.csv")
+        with open(path, "w", newline="") as f:
+            w = csv.writer(f)
+            w.writerow(["video_filename", "total_frames", "sampled_frames"])
+            for vp in sorted(str(v) for v in self.video_paths):
+                w.writerow([os.path.basename(vp), totals[vp], ",".join(map(str, self.cached_indices[vp]))])
+        return path
+
+
 class LstmVideoDataset(_BaseDataset):
     """``VideoDataset(root_dir, split='train', sampling_method='uniform', sequence_length=32, transform=None,
     logger=None)`` -> ``((C, T, 224, 224) float, float label)``; the sampler re-seeds 42 on every call."""
@@ -226,5 +295,5 @@ class LstmVideoDataset(_BaseDataset):
 
 VideoDataset = VivitVideoDataset  # the name every reference package uses
 __all__ = ["FrameSource", "TensorFrameSource", "SyntheticFrameSource", "VideoDataset", "VivitVideoDataset",
-           "TimesformerVideoDataset", "SwinVideoDataset", "LstmVideoDataset", "window_subsample", "scan_split",
+           "TimesformerVideoDataset", "SwinVideoDataset", "LstmVideoDataset", "Resnet3dVideoDataset", "crc32_video_seed", "window_subsample", "scan_split",
            "KINETICS", "_lib"]

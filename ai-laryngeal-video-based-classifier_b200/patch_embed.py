@@ -32,7 +32,30 @@ class _EmbedBase(nn.Module):
         self._packed = None
         self._packed_key = None
         self._ws = None
+        self._f32 = {}
         self.launches = 0
+
+    def _fp32(self, name, t):
+        """fp32 contiguous view/copy of a parameter that OUTLIVES the launch (a raw pointer taken from a temporary
+        would dangle for bf16 / half modules: the caching allocator hands the block to the next temporary).  Cached
+        per parameter on (data_ptr, version, device, dtype)."""
+        if t is None:
+            return None
+        key = (t.data_ptr(), t._version, t.device, t.dtype, tuple(t.shape))
+        hit = self._f32.get(name)
+        if hit is None or hit[0] != key:
+            hit = (key, t.detach().float().contiguous().view(-1))
+            self._f32[name] = hit
+        return hit[1]
+
+    def _check_no_grad(self, *extra):
+        """Forward only: the reference FINE-TUNES these layers (vivit .../trainers/trainer.py:145-146), and a silent
+        no_grad forward would freeze them without a word.  Raise when autograd is recording and any parameter of
+        the module wants a gradient; wrap the call in torch.no_grad() / inference_mode(), or freeze the module."""
+        if torch.is_grad_enabled() and any(q.requires_grad for q in list(self.parameters()) + [e for e in extra if e is not None]):
+            raise RuntimeError(
+                f"{type(self).__name__}: forward-only kernel (no autograd).  Call it under torch.no_grad() or freeze its "
+                "parameters (requires_grad_(False)); to fine-tune this layer keep the reference's torch module.")
 
     def _conv(self):
         raise NotImplementedError
@@ -61,6 +84,11 @@ class _EmbedBase(nn.Module):
     def _run(self, x, B, T, H, W, out_shape, layout=None, emb=None):
         if not x.is_cuda:
             raise RuntimeError(f"{type(self).__name__}: input must be on a CUDA device (no CPU fallback)")
+        self._check_no_grad(x, *(emb or ()))
+        with torch.no_grad():
+            return self._launch(x, B, T, H, W, out_shape, layout, emb)
+
+    def _launch(self, x, B, T, H, W, out_shape, layout, emb):
         if x.dtype not in _DT:
             x = x.float()
         x = x.contiguous()
@@ -76,7 +104,7 @@ class _EmbedBase(nn.Module):
         key = (w.data_ptr(), w._version, tuple(w.shape))
         if self._packed is None or self._packed_key != key:
             self._packed = torch.empty(w.numel(), dtype=torch.bfloat16, device=x.device)
-            _lib.check(lib.lvc_patch_embed_pack_weights(C.byref(d), w.detach().float().contiguous().data_ptr(),
+            _lib.check(lib.lvc_patch_embed_pack_weights(C.byref(d), self._fp32("weight", w).data_ptr(),
                                                         self._packed.data_ptr(), stream), "pack_weights")
             self._packed_key = key
             self.launches += 1
@@ -89,22 +117,23 @@ class _EmbedBase(nn.Module):
             self._ws = torch.empty(max(need, 256), dtype=torch.uint8, device=x.device)
         out = torch.empty(out_shape, dtype=self.out_dtype, device=x.device)
         if bias is None:
-            bias = torch.zeros(conv.out_channels, device=x.device)
+            if getattr(self, "_zero_bias", None) is None or self._zero_bias.device != x.device:
+                self._zero_bias = torch.zeros(conv.out_channels, device=x.device)
+            bias = self._zero_bias
         lw, lb, _ = self._ln()
+        bias_f, lw_f, lb_f = self._fp32("bias", bias), self._fp32("ln_w", lw), self._fp32("ln_b", lb)
         if emb is not None:  # fused cls / position / time embeddings
-            cls, pos, temb = (None if t is None else t.detach().float().contiguous().view(-1) for t in emb)
-            self._emb_keep = (cls, pos, temb)
+            cls, pos, temb = (self._fp32(n, t) for n, t in zip(("cls", "pos", "temb"), emb))
             st = lib.lvc_embeddings_forward(C.byref(d), x.data_ptr(), self._packed.data_ptr(),
-                                            bias.detach().float().contiguous().data_ptr(), cls.data_ptr(), pos.data_ptr(),
+                                            bias_f.data_ptr(), cls.data_ptr(), pos.data_ptr(),
                                             temb.data_ptr() if temb is not None else None, out.data_ptr(),
                                             self._ws.data_ptr(), stream)
             _lib.check(st, type(self).__name__)
             self.launches += lib.lvc_patch_embed_launch_count(C.byref(d))
             return out
-        st = lib.lvc_patch_embed(C.byref(d), x.data_ptr(), self._packed.data_ptr(),
-                                 bias.detach().float().contiguous().data_ptr(),
-                                 lw.detach().float().contiguous().data_ptr() if lw is not None else None,
-                                 lb.detach().float().contiguous().data_ptr() if lb is not None else None,
+        st = lib.lvc_patch_embed(C.byref(d), x.data_ptr(), self._packed.data_ptr(), bias_f.data_ptr(),
+                                 lw_f.data_ptr() if lw_f is not None else None,
+                                 lb_f.data_ptr() if lb_f is not None else None,
                                  out.data_ptr(), self._ws.data_ptr(), stream)
         _lib.check(st, type(self).__name__)
         self.launches += lib.lvc_patch_embed_launch_count(C.byref(d))
@@ -137,7 +166,6 @@ class VivitTubeletEmbeddings(_EmbedBase):
     def _conv(self):
         return self.projection
 
-    @torch.no_grad()
     def forward(self, pixel_values, interpolate_pos_encoding=False):
         B, T, Cc, H, W = pixel_values.shape
         if not interpolate_pos_encoding and (H != self.image_size[0] or W != self.image_size[1]):
@@ -170,7 +198,6 @@ class TimesformerPatchEmbeddings(_EmbedBase):
     def _conv(self):
         return self.projection
 
-    @torch.no_grad()
     def forward(self, pixel_values):
         B, T, Cc, H, W = pixel_values.shape
         if Cc != 3:
@@ -204,7 +231,6 @@ class PatchEmbed3d(_EmbedBase):
     def _ln(self):
         return self.norm.weight, self.norm.bias, self.norm.eps
 
-    @torch.no_grad()
     def forward(self, x):
         B, Cc, T, H, W = x.shape
         if Cc != 3:
@@ -226,7 +252,6 @@ class VivitEmbeddings(nn.Module):
         self.cls_token = nn.Parameter(torch.zeros(1, 1, E))
         self.position_embeddings = nn.Parameter(torch.zeros(1, P + 1, E))
 
-    @torch.no_grad()
     def forward(self, pixel_values=None, interpolate_pos_encoding=False, tokens=None, batch=None):
         pe = self.patch_embeddings
         if interpolate_pos_encoding:
@@ -259,7 +284,6 @@ class TimesformerEmbeddings(nn.Module):
         self.position_embeddings = nn.Parameter(torch.zeros(1, self.num_patches + 1, E))
         self.time_embeddings = nn.Parameter(torch.zeros(1, self.num_frames, E))
 
-    @torch.no_grad()
     def forward(self, pixel_values=None, tokens=None, batch=None):
         pe = self.patch_embeddings
         E = pe.projection.out_channels

@@ -290,6 +290,7 @@ def run_secondary(dev, iters=10):
     from lvc_b200 import patch_embed as pe
     from lvc_b200.synth import synth_boxes
 
+    torch.set_grad_enabled(False)   # forward-only path (the patch-embedding modules refuse to run under autograd)
     _, tf_peak, _ = peaks()
     hbm, _, _ = peaks()
     out = {}

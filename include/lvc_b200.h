@@ -150,8 +150,10 @@ typedef struct {
   int32_t batch;      /* B clips, one per video entry */
   int32_t num_frames; /* T */
   int32_t max_width;  /* largest frame width (pixels) among the B videos: sizes the shared-memory
-                         row slots.  A wider video in `videos` is a contract violation (the kernel
-                         traps). */
+                         ring.  A wider video in `videos` is a contract violation: lvc_clip_validate
+                         reports it on the host before the launch (LVC_E_SHAPE); a launch that still
+                         carries one never faults -- frames whose rows do not fit the ring are left
+                         unwritten and LVC_DEVERR_FRAME_TOO_WIDE is raised in lvc_device_status. */
   int32_t tok_kt, tok_kh, tok_kw; /* LVC_LAYOUT_TOKENS: patch size, e.g. (2,16,16); else ignored */
   float mean[3];      /* PTV_EVAL only */
   float std[3];
@@ -201,7 +203,9 @@ int lvc_clip_forward_aug(const lvc_clip_desc* desc, const lvc_video* videos, con
  *                  `size={"height": 224, "width": 224}` (timesformer .../trainers/trainer.py:91-98): both axes are
  *                  resized to 224 independently (aspect not kept), the crop is the identity
  *   max_height     largest frame height among the B videos (with desc->max_width it sizes the shared-memory
- *                  buffers; a larger video is a contract violation and traps).  Down-scales up to 11.5x.
+ *                  buffers; a larger video is a contract violation: lvc_clip_validate reports it on the host,
+ *                  the kernel leaves its frames unwritten and raises LVC_DEVERR_FRAME_TOO_LARGE).  Down-scales
+ *                  up to 11.5x.
  * desc->resample is ignored (LVC_RESAMPLE_PIL_SHORT implied), desc->src_float must be 0; no ROI boxes, no stats.
  * Output size is (int(E*W/H)|E) x (E|int(E*H/W)) as get_resize_output_image_size computes it, cropped at
  * ((nh-224)//2, (nw-224)//2).  Bit-exact against the processor (tests/test_hfraw_gpu.py). */
@@ -218,6 +222,39 @@ int lvc_hf_clip_forward_ex(const lvc_clip_desc* desc, int32_t shortest_edge, int
 
 /* Number of kernel launches lvc_clip_forward enqueues for this descriptor (for accounting). */
 int lvc_clip_launch_count(const lvc_clip_desc* desc);
+
+/* Host-side check of the `videos` table against the descriptor BEFORE a launch, from a host copy of the table (the
+ * device entry points only see a device pointer and never synchronise): every video has frames, a 16-byte aligned
+ * base, nbytes >= n_frames*height*width*3, width <= desc->max_width and -- max_height > 0, the lvc_hf_clip_forward
+ * contract -- height <= max_height.  LVC_E_SHAPE / LVC_E_INVAL / LVC_E_ALIGN with the offending entry in
+ * lvc_last_error().  The reference's seam raises ValueError for unusable videos (vivit .../dataset.py:217). */
+int lvc_clip_validate(const lvc_clip_desc* desc, int32_t max_height, const lvc_video* host_videos);
+
+/* Contract violations a kernel found on the device (it skips the offending frames instead of faulting): a sticky
+ * bit mask per device, OR-ed by the kernels.  Synchronises `stream`, returns the mask and (clear != 0) resets it. */
+enum {
+  LVC_DEVERR_FRAME_TOO_WIDE = 1,  /* lvc_clip_forward: a source window does not fit the ring sized by max_width */
+  LVC_DEVERR_FRAME_TOO_LARGE = 2  /* lvc_hf_clip_forward: a video exceeds max_width x max_height */
+};
+int lvc_device_status(void* stream, uint32_t* flags, int32_t clear);
+
+/* Launch geometry lvc_clip_forward derives from a descriptor (pure host arithmetic; for tests and tuning reports).
+ * sm_count / max_smem: the device's SM count and opt-in shared memory per CTA; <= 0 = query the current device
+ * (B200: 148, 232448). */
+typedef struct {
+  int32_t rows_per_stage;   /* output rows per ring stage (2 source rows each) */
+  int32_t ring_bytes;       /* byte-granular source-row ring */
+  int32_t ring_offset;      /* where the ring starts in shared memory (tables, LUTs, ViViT intermediate before it) */
+  int32_t slot_pitch;       /* bytes per row slot of the widest video */
+  int32_t stages_of_widest; /* stages of max_width rows the ring holds (narrower windows: proportionally more, <= 16) */
+  int32_t bands;            /* work items per frame */
+  int32_t rows_per_band;
+  int32_t producers;        /* bulk-copy producer warps */
+  int32_t grid, threads, smem_bytes;
+  int32_t reserved[5];
+} lvc_clip_plan;
+int lvc_clip_plan_query(const lvc_clip_desc* desc, int32_t has_boxes, int32_t sm_count, int32_t max_smem,
+                        lvc_clip_plan* out);
 
 /* ------------------------------------------------------------ patch / tubelet embedding ---- */
 

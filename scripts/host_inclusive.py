@@ -8,6 +8,8 @@ import time
 import numpy as np
 import torch
 
+torch.set_grad_enabled(False)  # forward-only kernels
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 from lvc_b200 import ClipBuilder, sampling  # noqa: E402

@@ -8,6 +8,8 @@ from functools import partial
 
 import torch
 
+torch.set_grad_enabled(False)  # forward-only kernels
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from lvc_b200 import patch_embed as pe  # noqa: E402
 from gemm_probe import timed  # noqa: E402

@@ -6,6 +6,8 @@ from functools import partial
 
 import numpy as np
 import torch
+
+torch.set_grad_enabled(False)  # forward-only kernels
 import torch.nn.functional as F
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

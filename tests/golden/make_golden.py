@@ -7,6 +7,7 @@ What each fixture pins:
   samplers.npz    a1  VideoDataset.get_sampling_indices of the vivit, swin and 2d-lstm copies,
                   a2  data_handling.sample_frame_indices, a3 resnet50-2d-lstm/inference.py samplers,
                       visualize_sampling.py pure functions
+  samplers3d.npz  a1  the resnet50-3d-video copy: per-video seed (hash pinned to crc32), index cache, re-seed to 42
   resize.npz      a6  cv2.resize(.,(224,224)) and Pillow BILINEAR on seeded images
   pixels.npz      a7  VivitImageProcessor, a8 VideoMAEImageProcessorPil, a9 the real
                       EnhancedVideoInference.predict_video of resnet50-2d-lstm/inference.py run on a fake
@@ -329,8 +330,58 @@ def make_embed():
     print("embed.npz", {k: v.shape for k, v in out.items()})
 
 
+def make_samplers3d():
+    """a1, resnet50-3d-video copy: per-video seed hash(basename) % 1e7 (with `hash` replaced by a FIXED function in
+    the reference module's namespace -- CPython salts str hashes per process), index cache, re-seed to 42.  For every
+    (method, N, T): a sequence of calls [a.mp4, b.mp4, a.mp4 (cached), c.mp4 after 3 stray draws on the global stream]
+    -- the stray draws must not matter (per-video seed) and the cached call must return the first answer."""
+    import zlib
+
+    stub("pytorchvideo.data.encoded_video", "pytorchvideo.data.clip_sampling", "pytorchvideo.transforms", "av")
+    ref = load("resnet50-3d-video/video_classifier/data_config/dataset.py", "ref_r3d_ds")
+    ref.hash = lambda name: zlib.crc32(name.encode("utf-8"))   # the module-level name shadows the builtin
+
+    class _Cap:   # the short-video branch reads the file's fps for a log line only (:119-123)
+        def __init__(self, path):
+            pass
+
+        def get(self, prop):
+            return 30.0
+
+        def release(self):
+            pass
+
+    ref.cv2 = types.SimpleNamespace(VideoCapture=_Cap, CAP_PROP_FPS=5)
+    names = ["a.mp4", "b.mp4", "a.mp4", "c.mp4"]
+    rows, outs = [], []
+    for mi, m in enumerate(METHODS):
+        for N in N_GRID:
+            for T in T_GRID:
+                ds = object.__new__(ref.VideoDataset)
+                ds.logger, ds.sampling_method, ds.num_frames, ds.fps, ds.cached_indices = _Log(), m, T, 30, {}
+                random.seed(42)
+                for call, name in enumerate(names):
+                    if call == 3:
+                        for _ in range(3):
+                            random.random()
+                    idx = ds.get_sampling_indices("/data/train/referral/" + name, N)
+                    rows.append((mi, N, T, call))
+                    a = np.full(32, -1, np.int64)
+                    a[: len(idx)] = idx
+                    outs.append(a)
+                # after any call the global stream is random.seed(42) again
+                assert random.random() == random.Random(42).random()
+    np.savez_compressed(os.path.join(HERE, "samplers3d.npz"), rows=np.array(rows, np.int64), indices=np.array(outs),
+                        names=np.array(names))
+    print("samplers3d.npz", len(rows))
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["samplers3d"]:
+        make_samplers3d()
+        sys.exit(0)
     make_samplers()
+    make_samplers3d()
     make_resize()
     make_pixels()
     make_embed()

@@ -10,7 +10,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 STRUCTS = {"lvc_rng": "Rng", "lvc_video": "Video", "lvc_clip_desc": "ClipDesc", "lvc_letterbox_geom": "LetterboxGeom",
-           "lvc_embed_desc": "EmbedDesc"}
+           "lvc_embed_desc": "EmbedDesc", "lvc_clip_plan": "ClipPlan"}
 
 
 def _c_layout(tmp_path):

@@ -152,3 +152,32 @@ def test_clip_embed_pipeline_graph_replay_matches_eager():
     assert pipe.replays == 4
     with pytest.raises(ValueError):
         pipe.set_videos([torch.zeros(2, 100, 100, 3, dtype=torch.uint8, device="cuda")] * 3)
+
+
+def test_pipeline_back_to_back_calls_while_the_gpu_is_behind():
+    """the host rewrote the single pinned table for call k+1 while replay k's own upload node had not run
+    yet (GPU busy), so batch k was built with batch k+1's indices.  Two graphs with private tables alternate now: with
+    the device held back, back-to-back calls with different index tables must each produce their own batch."""
+    import numpy as np
+    import torch
+
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.patch_embed import TimesformerPatchEmbeddings
+    from lvc_b200.pipeline import ClipEmbedPipeline
+    from lvc_b200.synth import synth_video
+
+    T = 4
+    vids = [torch.from_numpy(synth_video(60 + i, 16, 120, 160)).cuda() for i in range(2)]
+    cb = ClipBuilder("timesformer", num_frames=T, layout="TOKENS", patch=(1, 16, 16))
+    m = TimesformerPatchEmbeddings(out_dtype=torch.float32).cuda()
+    pipe = ClipEmbedPipeline(cb, m, vids, T)
+    tables = [np.array([[k, k + 1, k + 2, k + 3], [15 - k, 14 - k, 13 - k, 12 - k]], np.int32) for k in range(6)]
+    want = [m.forward_tokens(cb(vids, t), 2, T).clone() for t in tables]
+    torch.cuda.synchronize()
+    got = []
+    torch.cuda._sleep(int(2e8))            # ~0.1 s of device time: every replay below is enqueued behind it
+    for t in tables:
+        got.append(pipe(t).clone())        # clone is stream-ordered: taken before the slot's buffer is reused
+    torch.cuda.synchronize()
+    for k in range(6):
+        assert torch.equal(got[k], want[k]), k
