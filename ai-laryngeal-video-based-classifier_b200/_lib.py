@@ -7,13 +7,15 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblvc_b200.so")
+# LVC_B200_LIB: an alternative build of the same library (A/B experiments of compile-time variants; profiling only)
+LIB_PATH = os.environ.get("LVC_B200_LIB") or os.path.join(_HERE, "liblvc_b200.so")
 
 OK, E_INVAL, E_SHAPE, E_CUDA, E_ALIGN, E_NOTSUP = 0, -1, -2, -3, -4, -5
 SAMPLE = {"uniform": 0, "random_window": 1, "random": 2}
 VARIANT_DATASET, VARIANT_CLAMPED, VARIANT_NUMPY_INFER = 0, 1, 2
 LUT_DIV, LUT_MUL64 = 0, 1
 HF_SRC_HOST = 1
+HOST_WRITE_COMBINED = 1
 DEVERR_FRAME_TOO_WIDE, DEVERR_FRAME_TOO_LARGE = 1, 2
 B200_SMS, B200_MAX_SMEM = 148, 232448
 RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL, RESAMPLE_PIL_SHORT = 0, 1, 2, 3
@@ -85,6 +87,9 @@ _SIGS = {
     "lvc_clip_validate": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_void_p]),
     "lvc_device_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.c_int32]),
     "lvc_clip_plan_query": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_int32, C.c_int32, C.POINTER(ClipPlan)]),
+    "lvc_device_bytes_fetched": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32]),
+    "lvc_host_alloc": (C.c_int, [C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
+    "lvc_host_free": (C.c_int, [C.c_void_p]),
     "lvc_torch_randint": (C.c_int, [C.POINTER(Rng), C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "lvc_torch_rand": (C.c_float, [C.POINTER(Rng)]),
     "lvc_train_aug_draw": (C.c_int, [C.POINTER(Rng), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double,

@@ -64,11 +64,22 @@ def device_status(clear=True, device=None):
     return {n for bit, n in names.items() if flags.value & bit}
 
 
-def clip_plan(desc, has_boxes=False, sm_count=0, max_smem=0):
+def device_bytes_fetched(clear=True, device=None):
+    """Bytes the clip kernels' bulk-copy producers requested from the source buffers (HBM, or pinned host memory over
+    PCIe) since the last cleared read: a device-side counter (``lvc_device_bytes_fetched``).  Synchronises."""
+    dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+    with torch.cuda.device(dev):
+        n = C.c_uint64(0)
+        _lib.check(_lib.lib().lvc_device_bytes_fetched(torch.cuda.current_stream(dev).cuda_stream, C.byref(n), int(clear)),
+                   "lvc_device_bytes_fetched")
+    return int(n.value)
+
+
+def clip_plan(desc, has_boxes=False, sm_count=0, max_smem=0, has_stats=False):
     """Launch geometry ``lvc_clip_forward`` derives from a descriptor (host arithmetic; pass sm_count / max_smem to
     ask without a device, e.g. ``_lib.B200_SMS, _lib.B200_MAX_SMEM``)."""
     plan = _lib.ClipPlan()
-    _lib.check(_lib.lib().lvc_clip_plan_query(C.byref(desc), int(bool(has_boxes)), int(sm_count), int(max_smem),
+    _lib.check(_lib.lib().lvc_clip_plan_query(C.byref(desc), int(bool(has_boxes)) | 2 * int(bool(has_stats)), int(sm_count), int(max_smem),
                                               C.byref(plan)), "lvc_clip_plan_query")
     return {n: getattr(plan, n) for n, _ in _lib.ClipPlan._fields_ if n != "reserved"}
 
@@ -297,7 +308,7 @@ class ClipBuilder:
         return out
 
 
-    def build_from_host(self, host_videos, indices, boxes=None, out=None, stats=None, zero_copy=None):
+    def build_from_host(self, host_videos, indices, boxes=None, out=None, stats=None, zero_copy=None, aug=None):
         """End-to-end entry for decoded frames that live in HOST memory (pinned uint8 ``(N,H,W,3)``
         tensors, what a decoder hands over).
 
@@ -310,7 +321,7 @@ class ClipBuilder:
         if zero_copy is None:
             zero_copy = all((not v.is_cuda) and v.is_pinned() for v in host_videos) and self.resample != _lib.RESAMPLE_PTV_EVAL
         if zero_copy:
-            res = self(host_videos, indices, boxes=boxes, out=out, stats=stats, allow_pinned_host=True)
+            res = self(host_videos, indices, boxes=boxes, out=out, stats=stats, aug=aug, allow_pinned_host=True)
             if self.resample == _lib.RESAMPLE_PIL_SHORT:
                 self.last_h2d_bytes = raw_crop_bytes(host_videos, T, self.shortest_edge)
             else:
@@ -330,7 +341,7 @@ class ClipBuilder:
             staged.append(dv)
             remap.append(inv.astype(np.int32))
         self.last_h2d_bytes = h2d
-        return self(staged, np.stack(remap), boxes=boxes, out=out, stats=stats)
+        return self(staged, np.stack(remap), boxes=boxes, out=out, stats=stats, aug=aug)
 
 
 class ClipBatch:

@@ -29,7 +29,10 @@ enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
 // Consumer groups work on different rows of a stage (224 threads each, thread = output column).  Two groups for the
 // cv2 / torch chains; the ViViT preset runs two Pillow passes on top of the resize and is bound by consumer issue,
 // so it gets four (measured with 2+ producer warps: 155 -> 135 us on config 2; the other modes lose with four).
-__host__ __device__ constexpr int groups_of(int mode) { return mode == MODE_VIVIT ? 4 : 2; }
+#ifndef LVC_CLIP_GROUPS_CV2
+#define LVC_CLIP_GROUPS_CV2 2
+#endif
+__host__ __device__ constexpr int groups_of(int mode) { return mode == MODE_VIVIT ? 4 : LVC_CLIP_GROUPS_CV2; }
 // Producer warps: stage n of a CTA's stream belongs to warp n % kProducers.  One warp needs 0.5 us + 0.165 us per
 // output row to set up and issue a stage (serial tap / address / header chain, then UBLKCP lane by lane: it is a
 // uniform-datapath instruction), which bounded the small-source configs; four warps work on four stages concurrently.
@@ -38,7 +41,7 @@ __host__ __device__ constexpr int groups_of(int mode) { return mode == MODE_VIVI
 #endif
 constexpr int kProducers = LVC_CLIP_PRODUCERS;
 __host__ __device__ constexpr int threads_of(int mode) { return 32 * kProducers + groups_of(mode) * S; }
-constexpr int kMaxRPS = 8;                // output rows per stage (2*RPS source-row slots <= 32 lanes)
+constexpr int kMaxRPS = 16;               // output rows per stage (2*RPS source-row slots <= 32 lanes)
 constexpr int kMaxStages = 16;
 
 struct RowDesc {  // one output row of a stage
@@ -80,7 +83,10 @@ struct ClipParams {
   int total_items;           // B*T*bands
   int rps, stages, pitch;    // rows per stage, barrier slots in use (= kMaxStages), bytes per row slot of the WIDEST video
   int ring_bytes;            // size of the byte-granular source-row ring
+  int lut4_off;              // lean cv2 consumer: byte offset of the 3 x 1024 table indexed by the unrounded vertical sum
   unsigned* err;             // device error word (LVC_DEVERR_*), never NULL
+  unsigned long long* fetched;  // device counter: bytes the producers requested from the source buffers (bulk copies)
+  unsigned long long* trace;    // profiling (LVC_CLIP_TRACE=1 under the knob gate): CTA 0 logs 4 timestamps per stage, else NULL
   int producers;             // active producer warps (<= kProducers, <= stages)
   int merge_rows;            // fetch the (y, y+1) rows of a full-width tap pair with one copy
   float mean[3], std[3];     // PTV normalisation
@@ -124,6 +130,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
       ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
+}
+constexpr int kTraceStages = 4096;
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
 }
 __device__ __forceinline__ uint64_t policy_evict_first() {
   uint64_t p;
@@ -268,7 +280,178 @@ __device__ __forceinline__ unsigned col_offset(const ClipParams& p, int x) {
   return (unsigned)x;
 }
 
-template <int MODE>
+
+// ---- lean consumer of the cv2 chain with a compile-time output type -----------------------------------------------
+// Same arithmetic as the general consumer below (it stays for float frames, the ViViT and the torch chains), built for
+// instruction count: the consumers of the small-source configs are issue-bound (ncu: 114 warp instructions per output
+// row per warp, 0.5 IPC per scheduler, data always waiting in the ring), so every instruction removed from the row body
+// is time.  Against the general path: output type / stats / source type are template parameters (no per-stage dispatch);
+// shared addresses are 32-bit window addresses with the ring base folded into the per-frame column offset (add, and,
+// shift per source row instead of five instructions); one PRMT serves two channels (DP2A on the low and on the high
+// byte pair); float outputs without a checksum index a 1024-entry table by the unrounded vertical sum t0 + t1, which
+// folds cv2's (+2) >> 2 into the table; the layout's channel stride is a per-launch constant, not a header field.
+__device__ __forceinline__ void lds3(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c) {
+  asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+               : "=r"(a), "=r"(b), "=r"(c) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t shf_r_wrap(uint32_t lo, uint32_t hi, uint32_t s) {
+  uint32_t d;
+  asm("shf.r.wrap.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(lo), "r"(hi), "r"(s));
+  return d;
+}
+
+template <int ODT, bool STATS>
+__device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* smem, uint64_t* full, uint64_t* empty,
+                                                  const StageHdr* hdrs, const int ct, const int lane) {
+  constexpr int kGroups = groups_of(MODE_CV2);
+  constexpr int kEsz = ODT == LVC_DT_F32 ? 4 : (ODT == LVC_DT_BF16 ? 2 : 1);
+  constexpr bool kT4 = !STATS && ODT != LVC_DT_U8;   // table indexed by the unrounded vertical sum
+  const int g = ct / S, x = ct - g * S;
+  const uint32_t ring_s = smem_u32(smem) + (uint32_t)p.ring_off;
+  const unsigned xoff = col_offset(p, x);
+  // channel stride of the layout in bytes (a per-launch constant)
+  unsigned cs;
+  switch (p.layout) {
+    case LVC_LAYOUT_BTCHW: cs = S * S; break;
+    case LVC_LAYOUT_BCTHW: cs = (unsigned)p.T * S * S; break;
+    case LVC_LAYOUT_BTHWC: cs = 1; break;
+    default: cs = (unsigned)(p.kt * p.kh * p.kw);
+  }
+  cs *= kEsz;
+  const float* lutf = reinterpret_cast<const float*>(smem + (kT4 ? p.lut4_off : kLutOff));
+  const __nv_bfloat16* luth = reinterpret_cast<const __nv_bfloat16*>(smem + (kT4 ? p.lut4_off : kLut16Off));
+  constexpr int kLutStride = kT4 ? 1024 : 256;
+  const uint32_t selA = p.bgr ? 0x4152u : 0x4130u;   // (c0 of pixel 0, c0 of pixel 1, c1 of pixel 0, c1 of pixel 1)
+  const uint32_t selB = p.bgr ? 0x4430u : 0x4452u;   // (c2 of pixel 0, c2 of pixel 1, -, -); BGR sources swap c0 / c2
+  int cached_sw = -1, cached_flags = -1;
+  uint32_t xo_s = 0, a01 = 0;
+  unsigned long long acc = 0;
+  int acc_b = -1;
+  int slot = 0, cn = 0;
+  uint32_t phase = 0;
+  const int stages_per_item = p.rows_per_band / p.rps;
+  const bool pair_rows = (p.rps & (2 * kGroups - 1)) == 0;
+
+  for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+    for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
+      const bool tr = p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
+      if (tr) p.trace[cn * 4 + 1] = globaltimer_ns();
+      mbar_wait(&full[slot], phase);
+      if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();
+      const StageHdr* h = &hdrs[slot];
+      const int sw = h->sw, flags = h->flags;
+      if (sw != cached_sw || flags != cached_flags) {
+        cached_sw = sw; cached_flags = flags;
+        // exact 2x2 (INTER_AREA): a0 = a1 = 32 and b0 = b1 = 2^31 turn the fixed-point blend into
+        // (p00 + p01 + p10 + p11 + 2) >> 2: s >> 4 = 2 (p0 + p1), umulhi(2^31, 2 t) = t
+        int xo, a0, a1;
+        if (flags & 1) { xo = 6 * x; a0 = 32; a1 = 32; }
+        else {
+          int sx; float fr;
+          cv_tap(x, cv_scale(sw), sx, fr);
+          if (sx < 0) { sx = 0; fr = 0.f; }
+          if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }   // clamped edge: a1 == 0, the bytes read at +3 do not matter
+          a0 = coef(__fsub_rn(1.0f, fr));
+          a1 = coef(fr);
+          xo = 3 * sx;
+        }
+        xo_s = ring_s + (uint32_t)xo;
+        a01 = (uint32_t)a0 | ((uint32_t)a1 << 16);
+      }
+      if (STATS) {
+        const int b = h->clip;
+        if (b != acc_b) {
+          if (acc_b >= 0 && p.stats) {
+#pragma unroll
+            for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
+          }
+          acc = 0; acc_b = b;
+        }
+      }
+      char* const obase = reinterpret_cast<char*>(p.out) + (size_t)h->obase * kEsz;
+      unsigned acc32 = 0;
+      // one output row: 2 x 3 aligned shared words + funnel shift, exact 11-bit horizontal pass (PRMT + DP2A), cv2's
+      // vertical pass as two multiply-highs, table, three stores
+      auto vert = [&](const RowDesc& rd, uint32_t a, uint32_t b, uint32_t c, uint32_t o, uint32_t d, uint32_t e, uint32_t f,
+                      uint32_t o1, unsigned (&t)[3]) {
+        const uint32_t sh0 = o << 3, sh1 = o1 << 3;   // shf wraps at 32: (o & 3) * 8
+        const uint32_t lo0 = shf_r_wrap(a, b, sh0), hi0 = shf_r_wrap(b, c, sh0);
+        const uint32_t lo1 = shf_r_wrap(d, e, sh1), hi1 = shf_r_wrap(e, f, sh1);
+        const uint32_t wa0 = __byte_perm(lo0, hi0, selA), wb0 = __byte_perm(lo0, hi0, selB);
+        const uint32_t wa1 = __byte_perm(lo1, hi1, selA), wb1 = __byte_perm(lo1, hi1, selB);
+        const unsigned s00 = __dp2a_lo(a01, wa0, 0u), s01 = __dp2a_hi(a01, wa0, 0u), s02 = __dp2a_lo(a01, wb0, 0u);
+        const unsigned s10 = __dp2a_lo(a01, wa1, 0u), s11 = __dp2a_hi(a01, wa1, 0u), s12 = __dp2a_lo(a01, wb1, 0u);
+        // ((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16): the coefficients arrive as b << 16, each term is one multiply-high
+        t[0] = __umulhi((unsigned)rd.b0, s00 >> 4) + __umulhi((unsigned)rd.b1, s10 >> 4);
+        t[1] = __umulhi((unsigned)rd.b0, s01 >> 4) + __umulhi((unsigned)rd.b1, s11 >> 4);
+        t[2] = __umulhi((unsigned)rd.b0, s02 >> 4) + __umulhi((unsigned)rd.b1, s12 >> 4);
+      };
+      auto emit = [&](const unsigned eo, unsigned (&t)[3]) {
+        char* q = obase + (size_t)eo * kEsz;
+        if (!kT4) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) t[c] = (t[c] + 2u) >> 2;
+          if (STATS) acc32 += t[0] + t[1] + t[2];
+        }
+        if (ODT == LVC_DT_F32) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) __stcs(reinterpret_cast<float*>(q + (size_t)c * cs), lutf[c * kLutStride + t[c]]);
+        } else if (ODT == LVC_DT_BF16) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) *reinterpret_cast<__nv_bfloat16*>(q + (size_t)c * cs) = luth[c * kLutStride + t[c]];
+        } else {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) *reinterpret_cast<uint8_t*>(q + (size_t)c * cs) = (uint8_t)t[c];
+        }
+      };
+      if (!(flags & 4)) {
+        if (pair_rows) {
+          for (int r = g; r < p.rps; r += 2 * kGroups) {
+            const RowDesc ra = h->rows[r], rb = h->rows[r + kGroups];
+            const unsigned ea = h->roff[r] + xoff, eb = h->roff[r + kGroups] + xoff;
+            const uint32_t oa0 = (uint32_t)ra.off0 + xo_s, oa1 = (uint32_t)ra.off1 + xo_s;
+            const uint32_t ob0 = (uint32_t)rb.off0 + xo_s, ob1 = (uint32_t)rb.off1 + xo_s;
+            uint32_t w[12];
+            lds3(oa0 & ~3u, w[0], w[1], w[2]);
+            lds3(oa1 & ~3u, w[3], w[4], w[5]);
+            lds3(ob0 & ~3u, w[6], w[7], w[8]);
+            lds3(ob1 & ~3u, w[9], w[10], w[11]);
+            unsigned ta[3], tb[3];
+            vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, ta);
+            vert(rb, w[6], w[7], w[8], ob0, w[9], w[10], w[11], ob1, tb);
+            emit(ea, ta);
+            emit(eb, tb);
+          }
+        } else {
+          for (int r = g; r < p.rps; r += kGroups) {
+            const RowDesc ra = h->rows[r];
+            const unsigned ea = h->roff[r] + xoff;
+            const uint32_t oa0 = (uint32_t)ra.off0 + xo_s, oa1 = (uint32_t)ra.off1 + xo_s;
+            uint32_t w[6];
+            lds3(oa0 & ~3u, w[0], w[1], w[2]);
+            lds3(oa1 & ~3u, w[3], w[4], w[5]);
+            unsigned ta[3];
+            vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, ta);
+            emit(ea, ta);
+          }
+        }
+      }
+      if (STATS) acc += acc32;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (tr) p.trace[cn * 4 + 3] = globaltimer_ns();
+    }
+  }
+  if (STATS && p.stats && acc_b >= 0) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
+  }
+}
+
+// ODT: compile-time output type of the lean cv2 consumer (LVC_DT_*), or -1 = the general consumer (type from the descriptor)
+template <int MODE, int ODT, bool STATS>
 __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
   constexpr int kGroups = groups_of(MODE), kConsumers = kGroups * S, kThreads = threads_of(MODE);
   extern __shared__ __align__(128) uint8_t smem[];
@@ -301,6 +484,14 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
     }
   if (MODE == MODE_VIVIT)
     for (int i = tid; i < S; i += kThreads) reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = pil_tap(i);
+  if (MODE == MODE_CV2 && ODT >= 0 && ODT != LVC_DT_U8 && !STATS && p.lut) {
+    // table of the lean consumer: entry t = LUT[(t + 2) >> 2], t = unrounded sum of the two vertical terms (<= 1020)
+    for (int i = tid; i < 3 * 1024; i += kThreads) {
+      const float w = p.lut[(i >> 10) * 256 + min(((i & 1023) + 2) >> 2, 255)];
+      if (ODT == LVC_DT_F32) reinterpret_cast<float*>(smem + p.lut4_off)[i] = w;
+      else reinterpret_cast<__nv_bfloat16*>(smem + p.lut4_off)[i] = __float2bfloat16_rn(w);
+    }
+  }
   __syncthreads();
 
   if (warp < kProducers) {
@@ -323,6 +514,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
     // covers every older stage.  Lane l < 16 remembers the byte range of the latest stage with n % 16 == l.
     int n = 0, head = 0;   // stage sequence number, allocator position
     int hs = 0, he = 0;    // lane's remembered byte range
+    unsigned long long fetched = 0;   // bytes this warp asked the copy engine for (lane 0)
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       const int f = item / p.bands, band = item - f * p.bands;
       const int b = f / p.T;
@@ -478,18 +670,24 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
             slot_ptr[q - a] = *reinterpret_cast<const uint8_t*>(q);
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive_expect_tx(&full[slot], total);
+        if (lane == 0) { mbar_arrive_expect_tx(&full[slot], total); fetched += total; }
+        if (p.trace && blockIdx.x == 0 && lane == 0 && n < kTraceStages) p.trace[n * 4 + 0] = globaltimer_ns();
         __syncwarp();
         if (leader && bulk_bytes)
           bulk_g2s(stage_base + (size_t)lane * item_pitch, reinterpret_cast<const void*>(a), bulk_bytes,
                    &full[slot], policy);
       }
     }
+    if (lane == 0 && fetched) atomicAdd(p.fetched, fetched);
     return;
   }
 
   // ================= consumer warps: thread -> output column x, group -> rows g, g+G, ...
   const int ct = tid - 32 * kProducers;
+  if constexpr (MODE == MODE_CV2 && ODT >= 0) {
+    lean_cv2_consumer<ODT, STATS>(p, smem, full, empty, hdrs, ct, lane);
+    return;
+  }
   const int g = ct / S;
   const int x = ct - g * S;
   int cached_sw = -1, cached_flags = -1, cached_ox = -1;
@@ -500,7 +698,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   unsigned long long acc = 0;  // checksum of resized bytes for the clip being processed
   const bool want_stats = p.stats != nullptr;
   int acc_b = -1;
-  int slot = 0;
+  int slot = 0, cn = 0;
   uint32_t phase = 0;
   const unsigned xoff = col_offset(p, x);
   // MODE_VIVIT state: Pillow horizontal taps of this thread's column, row-buffer parity
@@ -510,8 +708,8 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   if (MODE == MODE_VIVIT) hx = reinterpret_cast<const int4*>(smem + kVivitTapOff)[x];
 
   // LUT + store of one output sample per channel (element offset eoff of channel 0, channel stride cstride)
-  auto store_px = [&](auto ODT, const size_t eoff, const int (&v)[3]) {
-    constexpr int kOdt = decltype(ODT)::value;   // compile-time output dtype, or -1 = look at the descriptor
+  auto store_px = [&](auto ODT_, const size_t eoff, const int (&v)[3]) {
+    constexpr int kOdt = decltype(ODT_)::value;   // compile-time output dtype, or -1 = look at the descriptor
     const int odt = kOdt >= 0 ? kOdt : p.out_dtype;
     if (odt == LVC_DT_F32) {
       float* o = reinterpret_cast<float*>(p.out) + eoff;
@@ -530,8 +728,11 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     bool item_bad = false;
-    for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages)) {
+    for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
+      const bool tr = p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
+      if (tr) p.trace[cn * 4 + 1] = globaltimer_ns();   // consumer starts waiting
       mbar_wait(&full[slot], phase);
+      if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();   // stage landed (or had landed)
       const StageHdr* h = &hdrs[slot];
       const int sw = h->sw, flags = h->flags, oy0 = h->oy0;
       obase = h->obase; cstride = h->cstride; rowmul = h->rowmul;
@@ -575,7 +776,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
       unsigned acc32 = 0;   // this stage's share of the checksum (<= 4 rows x 765)
       // F32SRC / ODT are compile-time copies of p.f32src / p.out_dtype: the row body has no branches, so the two
       // rows of a trip are scheduled as one block (their shared-memory loads overlap)
-      auto do_row = [&](auto F32SRC, auto ODT, const int r) {
+      auto do_row = [&](auto F32SRC, auto ODT_, const int r) {
         constexpr bool kF32Src = decltype(F32SRC)::value;
         const RowDesc rd = h->rows[r];
         const uint8_t* p0 = ring + rd.off0 + xo;
@@ -662,14 +863,14 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
           reinterpret_cast<uint32_t*>(inter)[(oyr - h->rlo) * S + x] = packed;
           return;
         }
-        store_px(ODT, eoff, v);
+        store_px(ODT_, eoff, v);
       };
       // two rows per trip (their shared-memory loads overlap) whenever the group has an even number of rows
-      auto do_rows = [&](auto F32SRC, auto ODT) {
+      auto do_rows = [&](auto F32SRC, auto ODT_) {
         if (MODE != MODE_VIVIT && (p.rps & (2 * kGroups - 1)) == 0) {
-          for (int r = g; r < p.rps; r += 2 * kGroups) { do_row(F32SRC, ODT, r); do_row(F32SRC, ODT, r + kGroups); }
+          for (int r = g; r < p.rps; r += 2 * kGroups) { do_row(F32SRC, ODT_, r); do_row(F32SRC, ODT_, r + kGroups); }
         } else {
-          for (int r = g; r < p.rps; r += kGroups) do_row(F32SRC, ODT, r);
+          for (int r = g; r < p.rps; r += kGroups) do_row(F32SRC, ODT_, r);
         }
       };
       using std::integral_constant;
@@ -683,6 +884,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
       if (want_stats) acc += acc32;
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
+      if (tr) p.trace[cn * 4 + 3] = globaltimer_ns();   // this warp is done with the stage
     }
     if (MODE == MODE_VIVIT) {
       // the whole frame went through the horizontal pass: Pillow vertical pass + LUT + store
@@ -740,11 +942,13 @@ const DeviceInfo& device_info() {
 
 // Contract violations found on the device (sticky until read): lvc_device_status()
 __device__ unsigned g_dev_error;
+// Bytes the clip kernels' producers fetched from the source buffers since the last read: lvc_device_bytes_fetched()
+__device__ unsigned long long g_bytes_fetched;
 
-template <int MODE>
+template <int MODE, int ODT = -1, bool STATS = true>
 int launch(const ClipParams& p, int grid, size_t smem, cudaStream_t st) {
-  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lvc_clip_kernel<MODE><<<grid, threads_of(MODE), smem, st>>>(p);
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE, ODT, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lvc_clip_kernel<MODE, ODT, STATS><<<grid, threads_of(MODE), smem, st>>>(p);
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;
 }
@@ -780,7 +984,7 @@ int check_desc(const lvc_clip_desc* d, bool boxes, bool aug, bool lut) {
 
 // Launch geometry for a descriptor on a device with `sms` SMs and `max_smem` bytes of opt-in shared memory per CTA.
 // Pure host arithmetic (lvc_clip_plan_query runs it without a device).
-int make_plan(const lvc_clip_desc* d, bool boxes, int sms, int max_smem, ClipParams& p, size_t& smem, int& grid) {
+int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_smem, ClipParams& p, size_t& smem, int& grid) {
   const bool ptv = d->resample == LVC_RESAMPLE_PTV_EVAL;
   const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
   // row slot of the widest video: window bytes + alignment slack, rounded to 16 (+16 to stagger banks)
@@ -812,7 +1016,12 @@ int make_plan(const lvc_clip_desc* d, bool boxes, int sms, int max_smem, ClipPar
       if (take) { best_cost = cost; best_ok = ok; v_nb = nb; v_res = res; }
     }
   }
-  const int fixed = mode == MODE_VIVIT ? vivit_ring_base(v_res) : kAuxOff;
+  int fixed = mode == MODE_VIVIT ? vivit_ring_base(v_res) : kAuxOff;
+  p.lut4_off = 0;
+  if (mode == MODE_CV2 && !stats && !d->src_float && d->out_dtype != LVC_DT_U8) {   // the lean consumer's 3 x 1024 table
+    p.lut4_off = fixed;
+    fixed += 3 * 1024 * (d->out_dtype == LVC_DT_F32 ? 4 : 2);
+  }
   p.ring_off = fixed;
   const int budget = budget_all - fixed;
   p.rps = env_int("LVC_CLIP_RPS", 0);
@@ -864,12 +1073,21 @@ int make_plan(const lvc_clip_desc* d, bool boxes, int sms, int max_smem, ClipPar
 
 }  // namespace
 
+namespace { unsigned long long* g_trace_buf = nullptr; }
+// Profiling aid (not part of the public header): copies the last traced launch's timeline, 4 timestamps (ns) per stage of
+// CTA 0 -- producer issued, consumer warp 0 began waiting, stage landed, consumer warp 0 done.
+extern "C" int lvc_clip_trace_read(unsigned long long* out, int stages) {
+  if (!g_trace_buf || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_trace_read: no trace (LVC_PROFILING_KNOBS=1 LVC_CLIP_TRACE=1)");
+  LVC_CUDA_TRY(cudaMemcpy(out, g_trace_buf, (size_t)std::min(stages, kTraceStages) * 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return LVC_OK;
+}
+
 extern "C" int lvc_clip_launch_count(const lvc_clip_desc* d) { return d ? 1 : 0; }
 
-extern "C" int lvc_clip_plan_query(const lvc_clip_desc* d, int32_t has_boxes, int32_t sm_count, int32_t max_smem,
+extern "C" int lvc_clip_plan_query(const lvc_clip_desc* d, int32_t flags, int32_t sm_count, int32_t max_smem,
                                    lvc_clip_plan* out) {
   if (!d || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_plan_query: NULL argument");
-  if (int rc = check_desc(d, has_boxes != 0, false, true)) return rc;
+  if (int rc = check_desc(d, (flags & LVC_PLAN_BOXES) != 0, false, true)) return rc;
   if (sm_count <= 0 || max_smem <= 0) {
     const DeviceInfo& di = device_info();
     if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "lvc_clip_plan_query: no usable CUDA device: %s", cudaGetErrorString(di.err));
@@ -878,7 +1096,7 @@ extern "C" int lvc_clip_plan_query(const lvc_clip_desc* d, int32_t has_boxes, in
   ClipParams p{};
   size_t smem = 0;
   int grid = 0;
-  if (int rc = make_plan(d, has_boxes != 0, sm_count, max_smem, p, smem, grid)) return rc;
+  if (int rc = make_plan(d, (flags & LVC_PLAN_BOXES) != 0, (flags & LVC_PLAN_STATS) != 0, sm_count, max_smem, p, smem, grid)) return rc;
   const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (d->resample == LVC_RESAMPLE_PTV_EVAL ? MODE_PTV : MODE_VIVIT);
   *out = lvc_clip_plan{};
   out->rows_per_stage = p.rps; out->ring_bytes = p.ring_bytes; out->ring_offset = p.ring_off; out->slot_pitch = p.pitch;
@@ -916,6 +1134,31 @@ extern "C" int lvc_device_status(void* stream, uint32_t* flags, int32_t clear) {
   if (clear) LVC_CUDA_TRY(cudaMemsetAsync(dptr, 0, sizeof h, st));
   LVC_CUDA_TRY(cudaStreamSynchronize(st));
   *flags = h;
+  return LVC_OK;
+}
+
+extern "C" int lvc_device_bytes_fetched(void* stream, uint64_t* bytes, int32_t clear) {
+  if (!bytes) return lvc_fail(LVC_E_INVAL, "lvc_device_bytes_fetched: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned long long* dptr = nullptr;
+  LVC_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&dptr), g_bytes_fetched));
+  unsigned long long h = 0;
+  LVC_CUDA_TRY(cudaMemcpyAsync(&h, dptr, sizeof h, cudaMemcpyDeviceToHost, st));
+  if (clear) LVC_CUDA_TRY(cudaMemsetAsync(dptr, 0, sizeof h, st));
+  LVC_CUDA_TRY(cudaStreamSynchronize(st));
+  *bytes = h;
+  return LVC_OK;
+}
+
+extern "C" int lvc_host_alloc(int64_t nbytes, int32_t flags, void** out) {
+  if (!out || nbytes <= 0) return lvc_fail(LVC_E_INVAL, "lvc_host_alloc: bad argument");
+  unsigned f = cudaHostAllocPortable | cudaHostAllocMapped;
+  if (flags & LVC_HOST_WRITE_COMBINED) f |= cudaHostAllocWriteCombined;
+  LVC_CUDA_TRY(cudaHostAlloc(out, (size_t)nbytes, f));
+  return LVC_OK;
+}
+extern "C" int lvc_host_free(void* p) {
+  if (p) LVC_CUDA_TRY(cudaFreeHost(p));
   return LVC_OK;
 }
 
@@ -963,11 +1206,35 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
   p.err = lvc_dev_error_word();
   if (!p.err) return lvc_fail(LVC_E_CUDA, "lvc_clip_forward: cannot resolve the device error word");
+  {
+    static thread_local unsigned long long* fptr = nullptr;
+    static thread_local int fdev = -1;
+    int dev = -1;
+    LVC_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev != fdev) {
+      LVC_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&fptr), g_bytes_fetched));
+      fdev = dev;
+    }
+    p.fetched = fptr;
+  }
   size_t smem = 0;
   int grid = 0;
-  if (int rc = make_plan(d, boxes != nullptr, di.sms, di.max_smem, p, smem, grid)) return rc;
+  if (int rc = make_plan(d, boxes != nullptr, stats != nullptr, di.sms, di.max_smem, p, smem, grid)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (mode == MODE_CV2) return launch<MODE_CV2>(p, grid, smem, st);
+  if (env_int("LVC_CLIP_TRACE", 0)) {   // profiling only: per-stage timeline of CTA 0 (lvc_clip_trace_read)
+    if (!g_trace_buf) LVC_CUDA_TRY(cudaMalloc(&g_trace_buf, kTraceStages * 4 * sizeof(unsigned long long)));
+    LVC_CUDA_TRY(cudaMemsetAsync(g_trace_buf, 0, kTraceStages * 4 * sizeof(unsigned long long), st));
+    p.trace = g_trace_buf;
+  }
+  if (mode == MODE_CV2) {
+    if (p.f32src) return launch<MODE_CV2>(p, grid, smem, st);   // float frames: the general consumer
+    const bool st8 = stats != nullptr;
+    switch (d->out_dtype) {
+      case LVC_DT_F32: return st8 ? launch<MODE_CV2, LVC_DT_F32, true>(p, grid, smem, st) : launch<MODE_CV2, LVC_DT_F32, false>(p, grid, smem, st);
+      case LVC_DT_BF16: return st8 ? launch<MODE_CV2, LVC_DT_BF16, true>(p, grid, smem, st) : launch<MODE_CV2, LVC_DT_BF16, false>(p, grid, smem, st);
+      default: return st8 ? launch<MODE_CV2, LVC_DT_U8, true>(p, grid, smem, st) : launch<MODE_CV2, LVC_DT_U8, false>(p, grid, smem, st);
+    }
+  }
   if (mode == MODE_VIVIT) return launch<MODE_VIVIT>(p, grid, smem, st);
-  return launch<MODE_PTV>(p, grid, smem, st);
+  return launch<MODE_PTV, -1, false>(p, grid, smem, st);
 }

@@ -58,8 +58,10 @@ __device__ Taps pil_taps(int xx, int in_size, int out_size, int* kk, int stride,
   if (xmin < 0) xmin = 0;
   int xmax = (int)__dadd_rn(__dadd_rn(center, support), 0.5);
   if (xmax > in_size) xmax = in_size;
+  // n <= kt always: the kernel clamps frames larger than the descriptor's max_width / max_height before it gets here.
+  // (Stated for the compiler: its register allocation of the unrolled passes depends on knowing these bounds.)
   const int n = xmax - xmin;
-  // n <= kt: the kernel skips frames larger than the descriptor's max_width / max_height before it gets here
+  __builtin_assume(n <= kt);
   double w[KT];
   double ww = 0.0;
   for (int x = 0; x < n; ++x) {
@@ -112,8 +114,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
+// Two CTAs per SM (64 registers) for the tap counts of down-scales up to ~4.5x (1080p -> 256).  ptxas lands there on its
+// own only by a hair (unrelated edits moved NT = 8, 9 to 95 registers and cost 15 % at 1080p), so it is stated.
 template <int NT>   // taps per sample held in the tables (>= 2*ceil(scale) + 1), fully unrolled in both passes
-__global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_constant__ PilParams p) {
+__global__ void __launch_bounds__(kMaxThreads, (NT <= 9 ? 2 : 1)) lvc_pil_kernel(const __grid_constant__ PilParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
   constexpr int kt = NT;
   int* hk = reinterpret_cast<int*>(smem);                 // [kt][S]  horizontal weights, tap-major
@@ -151,11 +155,12 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
     const int b = f / p.T, t = f - b * p.T;
     const lvc_video v = p.videos[b];
     const int idx = min(max(p.indices[f], 0), v.n_frames - 1);
-    const int H = v.height, W = v.width;
-    if (W > p.max_w || H > p.max_h) {   // contract violation (CTA-uniform): leave the frame unwritten, raise the error word
-      if (tid == 0) atomicOr(p.err, (unsigned)LVC_DEVERR_FRAME_TOO_LARGE);
-      continue;
-    }
+    // A video larger than the descriptor's max_width x max_height (which sized the tap tables and the staging buffers) is
+    // a contract violation: it is processed AS IF it had the maximum size -- every access stays inside its buffer and
+    // inside shared memory, its output frames are meaningless -- and the device error word is raised.  (Skipping the
+    // item instead costs the kernel its two-CTAs-per-SM register budget: 63 -> 95 registers.)
+    const int H = min(v.height, p.max_h), W = min(v.width, p.max_w);
+    if ((v.width > p.max_w || v.height > p.max_h) && tid == 0) atomicOr(p.err, (unsigned)LVC_DEVERR_FRAME_TOO_LARGE);
     __syncthreads();   // previous item is done with the tables and buffers
     if (W != cw || H != ch_) {
       int nh, nw;
@@ -196,6 +201,7 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
             a16 = a & ~(uint64_t)15;
             const uint32_t sh = (uint32_t)(a - a16);
             const uint32_t bytes = (sh + (uint32_t)span + 15u) & ~15u;
+            __builtin_assume(bytes <= (uint32_t)p.pitch_words * 4u);
             rsh[sl * kCH + lane] = (int)sh;
             bulk_bytes = bytes;
             if (a16 + bytes > buf_end) {   // last bytes of the buffer: not a whole 16-byte granule, copied by hand
@@ -219,6 +225,7 @@ __global__ void __launch_bounds__(kMaxThreads) lvc_pil_kernel(const __grid_const
         const uint64_t a4 = a & ~(uint64_t)3;
         const int sh = (int)(a - a4);
         const int nwords = (sh + span + 3) >> 2;
+        __builtin_assume(nwords <= p.pitch_words);
         if (lane == 0) rsh[sl * kCH + j] = sh;
         uint32_t* dst = slot + (size_t)j * p.pitch_words;
         if (a4 + 4u * (uint64_t)nwords <= buf_end) {   // every row but the buffer's last: no per-word bound check

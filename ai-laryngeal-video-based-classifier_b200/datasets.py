@@ -120,6 +120,32 @@ class _BaseDataset(torch.utils.data.Dataset):
     def get_sampling_indices(self, video_path, total_frames):
         return self._indices(total_frames)
 
+    # -- frames of a batch: resident videos, or (index-directed sources) only the sampled frames, decoded into pinned
+    #    host memory that the kernel reads in place -- the reference decodes just the sampled indices too
+    #    (vivit .../dataset.py:316-341)
+    def _build(self, indices, pick, **kw):
+        """``pick(i, total_frames)`` -> (frame indices the clip uses, what to report as frame_indices).  Returns
+        (clips, reported indices, list of per-video frame arrays' shapes)."""
+        src = self.source
+        if getattr(src, "index_directed", False):
+            frames, remaps, reported, shapes = [], [], [], []
+            for i in indices:
+                use, rep = pick(i, src.num_frames(i))
+                fr, rm = src.read_frames(i, use)
+                frames.append(fr)
+                remaps.append(rm)
+                reported.append(rep)
+                shapes.append(tuple(fr.shape[1:3]))
+            clips = self.builder.build_from_host(frames, np.stack(remaps), **kw)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.builder.device))
+            src.fence(ev)   # the pinned ring reuses these frames' space only after the kernel has read them
+            return clips, reported, shapes
+        vids = [src.frames(i) for i in indices]
+        picks = [pick(i, v.shape[0]) for i, v in zip(indices, vids)]
+        clips = self.builder(vids, [u for u, _ in picks], **kw)
+        return clips, [r for _, r in picks], [tuple(v.shape[1:3]) for v in vids]
+
 
 class VivitVideoDataset(_BaseDataset):
     """``VideoDataset(root_dir, mode='train', sampling_method='uniform', num_frames=32, logger=None)``."""
@@ -134,9 +160,11 @@ class VivitVideoDataset(_BaseDataset):
                     float_frames=float_frames)
 
     def get_batch(self, indices):
-        vids = [self.source.frames(i) for i in indices]
-        fidx = [self.get_sampling_indices(self.video_paths[i], v.shape[0]) for i, v in zip(indices, vids)]
-        clips = self.builder(vids, fidx)  # (B, T, 224, 224, 3) uint8, one launch
+        def pick(i, total):
+            fi = self.get_sampling_indices(self.video_paths[i], total)
+            return fi, fi
+
+        clips, fidx, _ = self._build(indices, pick)  # (B, T, 224, 224, 3) uint8, one launch
         return {"pixel_values": list(clips), "labels": torch.tensor([self.labels[i] for i in indices], dtype=torch.long),
                 "video_paths": [str(self.video_paths[i]) for i in indices], "frame_indices": fidx}
 
@@ -178,14 +206,30 @@ class SwinVideoDataset(_BaseDataset):
         i = self.video_paths.index(video_path) if video_path in self.video_paths else 0
         return self._indices(total_frames), sampling.dynamic_fps(total_frames, self.num_frames, self.source.fps(i))
 
-    def get_batch(self, indices):
-        vids = [self.source.frames(i) for i in indices]
-        fidx = [window_subsample(self._indices(v.shape[0]), self.num_frames) for v in vids]
+    def _frame_size(self, i):
+        src = self.source
+        if getattr(src, "index_directed", False):
+            _, _, w, h = src.properties(i)
+            return h, w
+        return tuple(src.frames(i).shape[1:3])
+
+    def _ptv_batch(self, indices, sample):
+        """Shared by the pytorchvideo-style copies: ``sample(i, total)`` -> raw sampler indices; the clip uses
+        UniformTemporalSubsample inside the decoded window (``window_subsample``)."""
         aug = None
-        if self.augment:
-            aug = [sampling.train_aug_params(v.shape[1], v.shape[2], self.aug_rng) for v in vids]
+        if self.augment:   # drawn per clip in item order, before the frames are touched (needs only the frame size)
+            aug = [sampling.train_aug_params(*self._frame_size(i), self.aug_rng) for i in indices]
         self.last_aug = aug
-        clips = self.builder(vids, fidx, aug=aug)  # (B, C, T, 224, 224)
+
+        def pick(i, total):
+            use = window_subsample(sample(i, total), self.num_frames)
+            return use, use
+
+        clips, _, _ = self._build(indices, pick, **({"aug": aug} if aug is not None else {}))
+        return clips
+
+    def get_batch(self, indices):
+        clips = self._ptv_batch(indices, lambda i, total: self._indices(total))  # (B, C, T, 224, 224)
         return clips.unsqueeze(1), torch.tensor([[self.labels[i]] for i in indices], dtype=torch.long)
 
     def __getitem__(self, idx):
@@ -232,14 +276,7 @@ class Resnet3dVideoDataset(SwinVideoDataset):
         return indices
 
     def get_batch(self, indices):
-        vids = [self.source.frames(i) for i in indices]
-        fidx = [window_subsample(self.get_sampling_indices(self.video_paths[i], v.shape[0]), self.num_frames)
-                for i, v in zip(indices, vids)]
-        aug = None
-        if self.augment:
-            aug = [sampling.train_aug_params(v.shape[1], v.shape[2], self.aug_rng) for v in vids]
-        self.last_aug = aug
-        clips = self.builder(vids, fidx, aug=aug)  # (B, C, T, 224, 224)
+        clips = self._ptv_batch(indices, lambda i, total: self.get_sampling_indices(self.video_paths[i], total))
         return clips.unsqueeze(1), torch.tensor([[self.labels[i]] for i in indices], dtype=torch.long)
 
     def save_sampled_indices(self):
@@ -279,14 +316,12 @@ class LstmVideoDataset(_BaseDataset):
         self.aug_rng = sampling.TorchRng(aug_seed)
         self.last_aug = None
 
+    _frame_size = SwinVideoDataset._frame_size
+    _ptv_batch = SwinVideoDataset._ptv_batch
+
     def get_batch(self, indices):
-        vids = [self.source.frames(i) for i in indices]
-        fidx = [window_subsample(self._indices(v.shape[0]), self.num_frames) for v in vids]
-        aug = None
-        if self.augment:
-            aug = [sampling.train_aug_params(v.shape[1], v.shape[2], self.aug_rng) for v in vids]
-        self.last_aug = aug
-        return self.builder(vids, fidx, aug=aug), torch.tensor([self.labels[i] for i in indices], dtype=torch.float32)
+        clips = self._ptv_batch(indices, lambda i, total: self._indices(total))
+        return clips, torch.tensor([self.labels[i] for i in indices], dtype=torch.float32)
 
     def __getitem__(self, idx):
         clips, labels = self.get_batch([idx])

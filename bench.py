@@ -110,6 +110,22 @@ def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
+def config_of(args, wl, world):
+    """The `config` object of the JSON line -- the SAME for both arms (the driver compares them)."""
+    return {"workload": args.workload, "source": wl["cfg"], "videos_per_gpu": wl["videos"],
+            "frame": [wl["h"], wl["w"]], "frames_per_video": wl["frames"], "T": wl["T"],
+            "sampling": wl["sampling"], "preset": wl["preset"], "out": wl["layout"] + " fp32",
+            "parallelism": f"videos sharded over {world} GPU(s), no collective on the path",
+            "l2": "inputs (19 GB) and outputs (1.2 GB) per step exceed L2; no flush needed"}
+
+
+def ref_clips_per_worker(videos, cores):
+    """Clips each CPU worker builds per step of the reference arm: the arm's config is `videos` clips per step; with more
+    cores than that would keep busy for long (one clip is ~50 ms) every worker gets at least 5, so the pool is not
+    measured through a barrier every clip (1 clip per worker under-measured the CPU by 16 %)."""
+    return max(5, -(-videos // cores))
+
+
 def run_reference(args, wl):
     """--impl reference: the reference's CPU recipe on all host cores (oracle/cpu_baseline.py; the
     reference is pure Python, so there is nothing to compile into oracle/_ref).  Rank 0 only."""
@@ -119,13 +135,14 @@ def run_reference(args, wl):
     from oracle import cpu_baseline as cb
 
     cores = cb.host_cores()
+    per = ref_clips_per_worker(wl["videos"], cores)
     pool = cb.Pool(wl["h"], wl["w"], wl["frames"], wl["T"], cores)
     try:
-        for _ in range(args.warmup):
+        for _ in range(max(1, min(args.warmup, 2))):
             pool.step(1)
         clips, secs = 0, 0.0
         for _ in range(args.steps):
-            n, dt = pool.step(1)
+            n, dt = pool.step(per)
             clips += n
             secs += dt
     finally:
@@ -134,10 +151,12 @@ def run_reference(args, wl):
     line = {"impl": "reference", "metric": "clips_per_sec_224", "value": v, "unit": "clips/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "source": wl["cfg"], "frame": [wl["h"], wl["w"]], "T": wl["T"],
-                       "recipe": "resnet50-2d-lstm/inference.py:158-178 (cv2.resize + /255 + mean/std + permute)"},
+            "config": config_of(args, wl, world),
             "cpu_baseline": {"value": v, "unit": "clips/s", "cores": cores, "kind": "port",
-                             "sample": f"{cores} single-thread workers x 1 clip per step, {args.steps} steps"},
+                             "recipe": "resnet50-2d-lstm/inference.py:158-178 (cv2.resize + /255 + mean/std + permute)",
+                             "sample": f"{cores} single-thread workers, {cores * per} clips per step from a shared queue "
+                                       f"({per} per worker), {args.steps} steps; config's 64 videos/step stand for the "
+                                       "same per-clip work"},
             "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -148,11 +167,14 @@ def run_b200(args, wl):
     import torch
     import torch.distributed as dist
 
-    from lvc_b200 import ClipBuilder, sampling
+    from lvc_b200 import ClipBuilder, hostmem, sampling
+    from lvc_b200.clips import device_bytes_fetched, device_status
 
     rank, local, world = dist_env()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # before any pinned allocation: CPUs (hence first-touch pages) next to this rank's GPU, where the box says which
+    numa = hostmem.bind_rank_to_gpu(local)
     if world > 1:
         # NCCL prints its version banner on stdout at communicator creation: point fd 1 at stderr while the
         # communicator comes up, so stdout carries exactly one JSON line
@@ -191,6 +213,7 @@ def run_b200(args, wl):
     barrier()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     launches0 = cb.launches
+    device_bytes_fetched(clear=True)
     with ClockSampler(local) as clk:
         barrier()
         ev[0].record()
@@ -201,29 +224,40 @@ def run_b200(args, wl):
     total_ms = ev[0].elapsed_time(ev[-1])
     launch_ms = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
     launches = cb.launches - launches0
+    fetched_per_launch = device_bytes_fetched(clear=True) // max(1, args.steps)
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms = float(t.item())
     ms_per_step = total_ms / args.steps
     value = B * world / (ms_per_step * 1e-3)
-
+    res = dict(rank=rank, world=world, ms_per_step=ms_per_step, value=value, launch_ms=launch_ms, launches=launches,
+               clocks=clk.summary(), e2e=None, numa=numa, fetched_per_launch=int(fetched_per_launch),
+               checksum=int(stats.sum().item()))
     if args.no_e2e:
-        return dict(rank=rank, world=world, ms_per_step=ms_per_step, value=value, launch_ms=launch_ms, launches=launches,
-                    clocks=clk.summary(), e2e=None, e2e_steps=0, h2d=0, d2h=0, checksum=int(stats.sum().item()))
+        return res
     # ---- e2e: host (pinned) frames -> fused kernel pulls the tapped rows over PCIe -> D2H of the checksum
     e2e_steps = max(2, min(args.steps, 5))
     # (16 distinct pinned host videos stand in for the rank's 64: every entry still uploads its own
     # frames, so bytes per step are those of 64 videos while the pinned footprint stays at 4.8 GB/rank)
-    distinct = [torch.empty((N, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(min(B, 16))]
+    nd = min(B, 16)
+    wc = args.host_mem == "wc"
+    distinct = [hostmem.pinned_empty((N, H, W, 3), write_combined=wc) for _ in range(nd)]
     for hv, dv in zip(distinct, vids):
         hv.copy_(dv)
-    host = [distinct[i % len(distinct)] for i in range(B)]
+    host = [distinct[i % nd] for i in range(B)]
+    # the same batch built from the device-resident copies of those videos: the checksum the e2e result must equal
+    ref_stats = torch.zeros(B, dtype=torch.int64, device=dev)
+    cb([vids[i % nd] for i in range(B)], idx, out=out, stats=ref_stats)
+    ref_stats = ref_stats.cpu()
+    cb._retire()   # drop the parked batch (it holds the device videos)
     del vids, batch
     torch.cuda.empty_cache()
-    d2h = 0
+    d2h, match = 0, True
+    device_bytes_fetched(clear=True)
     for k in range(1 + e2e_steps):
         if k == 1:
+            device_bytes_fetched(clear=True)
             barrier()
             t0 = torch.cuda.Event(enable_timing=True)
             t1 = torch.cuda.Event(enable_timing=True)
@@ -232,15 +266,19 @@ def run_b200(args, wl):
         cb.build_from_host(host, idx, out=out, stats=stats)
         chk = stats.cpu()  # device -> host read of the step's result (per-clip checksums)
         d2h = chk.numel() * chk.element_size()
+        match = match and bool(torch.equal(chk, ref_stats))
     t1.record()
     barrier()
+    h2d = device_bytes_fetched(clear=True) // e2e_steps      # counted by the kernel's producers, not estimated
     e = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
+    ok = torch.tensor([1.0 if (match and not device_status()) else 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     e2e = B * world / (float(e.item()) / e2e_steps * 1e-3)
-    return dict(rank=rank, world=world, ms_per_step=ms_per_step, value=value, launch_ms=launch_ms, launches=launches,
-                clocks=clk.summary(), e2e=e2e, e2e_steps=e2e_steps, h2d=cb.last_h2d_bytes, d2h=d2h,
-                checksum=int(chk.sum().item()))
+    res.update(e2e=e2e, e2e_steps=e2e_steps, h2d=int(h2d), h2d_estimate=cb.last_h2d_bytes, d2h=d2h,
+               e2e_match=bool(ok.item() == 1.0), checksum=int(chk.sum().item()), host_mem=args.host_mem)
+    return res
 
 
 SECONDARY = {
@@ -438,6 +476,102 @@ def run_secondary(dev, iters=10):
     return out
 
 
+def run_cfg1(dev, iters=10):
+    """BASELINE.json configs[0] on the GPU: the resnet50-2d-lstm inference recipe (resnet50-2d-lstm/inference.py:132-195) --
+    4 videos of 300 720p frames, 32 uniformly sampled frames each, cv2-exact resize, /255, mean/std, (4,3,32,224,224) fp32.
+    Device-resident kernel time (L2 flushed) and the end-to-end call from pinned host frames, checksums compared."""
+    import numpy as np
+    import torch
+
+    from lvc_b200 import ClipBuilder, hostmem, sampling
+
+    wl = WORKLOADS["cfg1_720p"]
+    B, N, H, W, T = wl["videos"], wl["frames"], wl["h"], wl["w"], wl["T"]
+    g = torch.Generator(device=dev).manual_seed(1)
+    vids = [torch.randint(0, 256, (N, H, W, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(B)]
+    idx = np.array([sampling.get_sampling_indices("uniform", N, T) for _ in range(B)], dtype=np.int32)
+    cb = ClipBuilder(wl["preset"], num_frames=T, layout=wl["layout"])
+    batch = cb.prepare(vids, idx)
+    out = torch.empty(batch.shape, dtype=torch.float32, device=dev)
+    stats = torch.zeros(B, dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ts = []
+    for _ in range(3 + iters):
+        flush.zero_()
+        torch.cuda._sleep(400000)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        cb.run(batch, out)
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ms = statistics.median(ts[3:])
+    cb.run(batch, out, stats)
+    want = stats.cpu()
+    # end to end: only the 32 sampled frames of each video are in pinned host memory (what an index-directed decoder
+    # hands over, lvc_b200.decode), the kernel reads them in place
+    host = []
+    for b in range(B):
+        hv = hostmem.pinned_empty((T, H, W, 3))
+        hv.copy_(vids[b][torch.from_numpy(idx[b]).long().to(dev)])
+        host.append(hv)
+    torch.cuda.synchronize()
+    hidx = np.tile(np.arange(T, dtype=np.int32), (B, 1))
+    es, match = [], True
+    for _ in range(2 + 5):
+        stats.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        cb.build_from_host(host, hidx, out=out, stats=stats)
+        got = stats.cpu()
+        e1.record()
+        torch.cuda.synchronize()
+        es.append(e0.elapsed_time(e1))
+        match = match and bool(torch.equal(got, want))
+    ems = statistics.median(es[2:])
+    hbm, _, _ = peaks()
+    byt = B * T * algorithmic_bytes_per_frame(H, W, 4)
+    return {"source": wl["cfg"], "kernel_ms": ms, "clips_per_s": B / (ms * 1e-3), "frac": byt / ms / 1e6 / hbm, "bound": "hbm",
+            "e2e_clips_per_s": B / (ems * 1e-3), "e2e_ms": ems, "e2e_checksum_matches_device": match,
+            "h2d_bytes": cb.last_h2d_bytes}
+
+
+def committed_ncu():
+    """Figures read from ncu captures committed under profiles/ (never measured in this run): per-launch DRAM traffic of
+    the headline kernel, tensor-pipe utilisation of the GEMMs -- each with the capture file and the git sha it was taken at."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_committed.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+def compact_secondary(detail, ncu):
+    """One short object per config for the JSON line; the verbose record goes to the side file."""
+    out = {}
+    for name, e in detail.items():
+        if "pipeline_ms" not in e:
+            continue
+        r = e["gemm_roofline"]
+        c = {"pipeline_ms": round(e["pipeline_ms"], 4), "clip_ms": round(e["clip_kernel_ms"], 4), "gemm_ms": round(e["gemm_ms"], 4),
+             "frac": round(r["frac"], 3), "bound": r["bound"], "clips_per_s": round(e["clips_per_s"], 1)}
+        if "fused_ms" in e:
+            c["fused_ms"] = round(e["fused_ms"], 4)
+        tp = ncu.get("tensor_pipe", {}).get(name)
+        if tp:
+            c["ncu_tensor_pipe_pct"] = tp.get("pct_of_elapsed")
+        if "cpu_reference" in e:
+            c["cpu_clips_per_s"] = round(e["cpu_reference"]["clips_per_s"], 2)
+        out[name] = c
+    if "hf_raw_1080p" in detail:
+        h = detail["hf_raw_1080p"]
+        out["hf_raw_1080p"] = {"kernel_ms": round(h["kernel_ms"], 4), "clips_per_s": round(h["clips_per_s"], 1),
+                               "e2e_clips_per_s": round(h.get("e2e", {}).get("clips_per_s", 0.0), 1)}
+        if "cpu_reference" in h:
+            out["hf_raw_1080p"]["cpu_clips_per_s"] = round(h["cpu_reference"]["clips_per_s"], 3)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -445,10 +579,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="sweep1080p", choices=sorted(WORKLOADS))
+    ap.add_argument("--host-mem", default="pinned", choices=["pinned", "wc"],
+                    help="e2e leg: ordinary page-locked host frames, or write-combined (device reads are not snooped)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host->device leg (profiling runs only)")
-    ap.add_argument("--no-secondary", action="store_true", help="skip the configs[1..3] clip+embed pipelines")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the configs[0..3] legs")
     ap.add_argument("--secondary-only", action="store_true", help="run only the configs[1..3] pipelines (profiling)")
+    ap.add_argument("--detail-file", default=None, help="where the verbose per-config record goes (default: "
+                    "gpurun_out/bench_detail.json when gpurun_out/ exists, else ./bench_detail.json)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
@@ -480,30 +618,31 @@ def main():
     frames = wl["videos"] * wl["T"]
     launch_s = statistics.mean(r["launch_ms"]) * 1e-3
     achieved = frames * bpf / launch_s / 1e9
-    traffic = None
-    try:  # per-launch DRAM bytes of the same kernel from the committed `ncu --set full` capture
-        with open(os.path.join(ROOT, "profiles", "clip_kernel_dram.json")) as f:
-            traffic = json.load(f).get(args.workload)
-    except Exception:
-        pass
+    ncu = committed_ncu()
+    tr = ncu.get("dram_traffic", {}).get(args.workload) or {}
     line = {"metric": "clips_per_sec_224", "value": r["value"], "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": args.workload, "source": wl["cfg"], "videos_per_gpu": wl["videos"],
-                       "frame": [wl["h"], wl["w"]], "frames_per_video": wl["frames"], "T": wl["T"],
-                       "sampling": wl["sampling"], "preset": wl["preset"], "out": wl["layout"] + " fp32",
-                       "parallelism": f"videos sharded over {world} GPU(s), no collective on the path",
-                       "l2": "inputs (19 GB) and outputs (1.2 GB) per step exceed L2; no flush needed"},
-            "clocks": r["clocks"],
-            "e2e": {"value": r["e2e"], "unit": "clips/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "steps": r["e2e_steps"], "path": "pinned host frames read by the fused kernel over PCIe (zero-copy, tapped rows only) -> clips in HBM -> D2H checksums"},
-            "gpu_launches": r["launches"],
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                         "traffic": traffic, "peak_source": src, "kernel": "lvc_clip_kernel<MODE_CV2>",
-                         "algorithmic_bytes_per_launch": frames * bpf, "kernel_ms": launch_s * 1e3},
-            "per_rank": [[float(v) for v in g.tolist()] for g in gathered]}
+            "gpu_launches": r["launches"], "config": config_of(args, wl, world), "clocks": r["clocks"]}
+    if r["e2e"] is not None:
+        line["e2e"] = {"value": r["e2e"], "unit": "clips/s", "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                       "steps": r["e2e_steps"], "checksum_matches_device": r["e2e_match"], "host_mem": r["host_mem"],
+                       "h2d_counted_by": "device counter of the kernel's bulk-copy producers (lvc_device_bytes_fetched)",
+                       "path": "ClipBuilder.build_from_host: pinned host frames read in place by the fused kernel over PCIe "
+                               "(tapped rows only) -> clips stay in HBM for the model -> D2H of the per-clip checksums only"}
+    line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                        "traffic": tr.get("bytes_per_launch"), "traffic_source": {k: tr.get(k) for k in ("capture", "git", "when")} if tr else None,
+                        "peak_source": src, "kernel": "lvc_clip_kernel<MODE_CV2>",
+                        "algorithmic_bytes_per_launch": frames * bpf, "kernel_ms": launch_s * 1e3,
+                        "fetched_bytes_per_launch": r["fetched_per_launch"]}
+    line["numa"] = r["numa"]
+    line["per_rank"] = [[round(float(v), 4) for v in g.tolist()] for g in gathered]
+    detail = {}
     if world == 1 and not args.no_secondary:
-        line["secondary"] = run_secondary(torch.device("cuda", local))
+        torch.set_grad_enabled(False)
+        cfg1 = run_cfg1(torch.device("cuda", local))
+        detail = run_secondary(torch.device("cuda", local))
+        detail["cfg1_720p"] = cfg1
         if not args.no_cpu_baseline:
             # the reference's CPU recipe of each secondary config on the host cores, same run:
             # clip construction on a pool of single-thread workers, fp32 patch embedding on all threads
@@ -516,28 +655,45 @@ def main():
                 clip_rate = cbm.run(c["h"], c["w"], 48, c["T"], cores, 1, repeats=2, recipe=rec)
                 emb_ms = cbm.embed_cpu_ms(kind, c["videos"], c["T"], cores)
                 both = 1.0 / (1.0 / clip_rate + emb_ms * 1e-3 / c["videos"])
-                line["secondary"][name]["cpu_reference"] = {
+                detail[name]["cpu_reference"] = {
                     "clips_per_s": both, "clip_recipe_clips_per_s": clip_rate, "embed_ms_per_batch": emb_ms, "cores": cores,
                     "sample": f"{cores} single-thread workers x 1 clip, median of 2; fp32 torch embed on {cores} threads, median of 2"}
-        if not args.no_cpu_baseline and "hf_raw_1080p" in line["secondary"]:
-            line["secondary"]["hf_raw_1080p"]["cpu_reference"] = _hf_raw_cpu()
+            c1 = WORKLOADS["cfg1_720p"]
+            cfg1["cpu_clips_per_s"] = cbm.run(c1["h"], c1["w"], 64, c1["T"], cores, 2, repeats=2)
+            cfg1["cpu_cores"] = cores
+            if "hf_raw_1080p" in detail:
+                detail["hf_raw_1080p"]["cpu_reference"] = _hf_raw_cpu()
+        line["secondary"] = compact_secondary(detail, ncu)
+        line["secondary"]["cfg1_720p"] = {k: (round(v, 4) if isinstance(v, float) else v) for k, v in cfg1.items() if k != "source"}
     if not args.no_cpu_baseline:
         from oracle import cpu_baseline as cbm
 
         cores = cbm.host_cores()
-        per = max(1, int(round(160 / cores)))  # ~10-20 s of CPU work in total
+        per = ref_clips_per_worker(wl["videos"], cores)
         v = cbm.run(wl["h"], wl["w"], wl["frames"], wl["T"], cores, per, repeats=3)
         # the same recipe three ways -- one process, the reference's DataLoader-style 4 workers
         # (vivit_transformer/main.py:49), all host cores (the headline `value`)
         v1 = cbm.run(wl["h"], wl["w"], wl["frames"], wl["T"], 1, 6, repeats=3)
         v4 = cbm.run(wl["h"], wl["w"], wl["frames"], wl["T"], min(4, cores), 6, repeats=3)
         line["cpu_baseline"] = {"value": v, "unit": "clips/s", "cores": cores, "kind": "port",
-                                "sample": f"{cores} single-thread workers x {per} clip(s), median of 3 (cv2.resize + /255 + mean/std + permute)",
-                                "ways": {"1_process_1_thread": v1, "4_workers": v4, "all_cores": v,
+                                "sample": f"{cores} single-thread workers, {cores * per} clips from a shared queue, median of 3 "
+                                          "(cv2.resize + /255 + mean/std + permute)",
+                                "ways": {"1_process_1_thread": round(v1, 2), "4_workers": round(v4, 2), "all_cores": round(v, 2),
                                          "os_cpu_count": os.cpu_count()}}
+    if detail:
+        path = args.detail_file or os.path.join(ROOT, "gpurun_out" if os.path.isdir(os.path.join(ROOT, "gpurun_out")) else ".",
+                                                "bench_detail.json")
+        try:
+            with open(path, "w") as f:
+                json.dump({"secondary": detail, "headline": line}, f, indent=1)
+            line["detail_file"] = os.path.relpath(path, ROOT)
+        except OSError:
+            pass
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if r["e2e"] is not None and not r["e2e_match"]:
+        sys.exit("bench.py: the end-to-end result differs from the device-resident result on the same videos")
 
 
 if __name__ == "__main__":

@@ -204,8 +204,8 @@ int lvc_clip_forward_aug(const lvc_clip_desc* desc, const lvc_video* videos, con
  *                  resized to 224 independently (aspect not kept), the crop is the identity
  *   max_height     largest frame height among the B videos (with desc->max_width it sizes the shared-memory
  *                  buffers; a larger video is a contract violation: lvc_clip_validate reports it on the host,
- *                  the kernel leaves its frames unwritten and raises LVC_DEVERR_FRAME_TOO_LARGE).  Down-scales
- *                  up to 11.5x.
+ *                  the kernel treats it as max-sized -- every access stays inside its buffer, its output frames
+ *                  are meaningless -- and raises LVC_DEVERR_FRAME_TOO_LARGE).  Down-scales up to 11.5x.
  * desc->resample is ignored (LVC_RESAMPLE_PIL_SHORT implied), desc->src_float must be 0; no ROI boxes, no stats.
  * Output size is (int(E*W/H)|E) x (E|int(E*H/W)) as get_resize_output_image_size computes it, cropped at
  * ((nh-224)//2, (nw-224)//2).  Bit-exact against the processor (tests/test_hfraw_gpu.py). */
@@ -238,6 +238,18 @@ enum {
 };
 int lvc_device_status(void* stream, uint32_t* flags, int32_t clear);
 
+/* Bytes the clip kernels' bulk-copy producers requested from the source buffers (HBM, or pinned host memory read over
+ * PCIe) since the counter was last cleared, on the current device: a device-side counter, one atomic per producer
+ * warp per launch.  Synchronises `stream`. */
+int lvc_device_bytes_fetched(void* stream, uint64_t* bytes, int32_t clear);
+
+/* Page-locked host memory for decoded frames the kernels read in place (zero-copy ingest): portable + mapped, and with
+ * LVC_HOST_WRITE_COMBINED not snooped by the CPU caches on device reads (fast to fill sequentially from a decoder,
+ * slow to READ from the CPU).  The reference holds decoded frames in numpy arrays (vivit .../dataset.py:336-341). */
+enum { LVC_HOST_WRITE_COMBINED = 1 };
+int lvc_host_alloc(int64_t nbytes, int32_t flags, void** out);
+int lvc_host_free(void* p);
+
 /* Launch geometry lvc_clip_forward derives from a descriptor (pure host arithmetic; for tests and tuning reports).
  * sm_count / max_smem: the device's SM count and opt-in shared memory per CTA; <= 0 = query the current device
  * (B200: 148, 232448). */
@@ -253,7 +265,8 @@ typedef struct {
   int32_t grid, threads, smem_bytes;
   int32_t reserved[5];
 } lvc_clip_plan;
-int lvc_clip_plan_query(const lvc_clip_desc* desc, int32_t has_boxes, int32_t sm_count, int32_t max_smem,
+enum { LVC_PLAN_BOXES = 1 /* an ROI table will be passed */, LVC_PLAN_STATS = 2 /* a stats buffer will be passed */ };
+int lvc_clip_plan_query(const lvc_clip_desc* desc, int32_t flags, int32_t sm_count, int32_t max_smem,
                         lvc_clip_plan* out);
 
 /* ------------------------------------------------------------ patch / tubelet embedding ---- */

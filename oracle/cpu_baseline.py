@@ -146,10 +146,12 @@ class Pool:
         self.pool = mp.get_context("fork").Pool(workers, initializer=_init)
 
     def step(self, clips_per_worker=1):
-        """All workers build `clips_per_worker` clips; returns (clips built, seconds)."""
+        """The pool builds `workers * clips_per_worker` clips, handed out one clip at a time from a shared queue (a
+        worker that finishes early takes the next clip: no straggler wait beyond one clip); returns (clips, seconds)."""
+        total = self.workers * clips_per_worker
         t0 = time.perf_counter()
-        self.pool.map(_work, [(self.T, clips_per_worker)] * self.workers, chunksize=1)
-        return self.workers * clips_per_worker, time.perf_counter() - t0
+        self.pool.map(_work, [(self.T, 1)] * total, chunksize=1)
+        return total, time.perf_counter() - t0
 
     def close(self):
         self.pool.terminate()

@@ -4,6 +4,8 @@ import os
 import sys
 
 import numpy as np
+
+os.environ["LVC_PROFILING_KNOBS"] = "1"  # opt in to the launch knobs (read once per process, before the library loads)
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -43,8 +45,8 @@ def timeit(cb, batch, tok, n=15):
     return float(np.median(ts[3:]))
 
 
-KNOBS = [{}, {"LVC_CLIP_RPS": "4"}, {"LVC_CLIP_RPS": "2"}, {"LVC_CLIP_SMEM_KB": "100"}, {"LVC_CLIP_BAND": "56"}, {"LVC_CLIP_BAND": "16"},
-         {"LVC_CLIP_BAND": "224"}]
+KNOBS = [{}, {"LVC_CLIP_RPS": "16"}, {"LVC_CLIP_RPS": "4"}, {"LVC_CLIP_RPS": "2"}, {"LVC_CLIP_SMEM_KB": "100"}, {"LVC_CLIP_BAND": "56"},
+         {"LVC_CLIP_BAND": "16"}, {"LVC_CLIP_BAND": "224"}]
 if os.environ.get("CLIP_KNOBS_MATRIX"):   # producers x rows-per-stage
     KNOBS = [{"LVC_CLIP_NP": str(n), **({"LVC_CLIP_RPS": r} if r else {})} for n in (1, 2, 4) for r in ("", "4")]
 for name in (sys.argv[1:] or ["swin_cfg4", "timesformer_cfg3", "vivit_cfg2"]):
