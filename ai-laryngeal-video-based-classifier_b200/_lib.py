@@ -87,9 +87,6 @@ _SIGS = {
     "lvc_clip_validate": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_void_p]),
     "lvc_device_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.c_int32]),
     "lvc_clip_plan_query": (C.c_int, [C.POINTER(ClipDesc), C.c_int32, C.c_int32, C.c_int32, C.POINTER(ClipPlan)]),
-    "lvc_device_bytes_fetched": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32]),
-    "lvc_host_alloc": (C.c_int, [C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
-    "lvc_host_free": (C.c_int, [C.c_void_p]),
     "lvc_torch_randint": (C.c_int, [C.POINTER(Rng), C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "lvc_torch_rand": (C.c_float, [C.POINTER(Rng)]),
     "lvc_train_aug_draw": (C.c_int, [C.POINTER(Rng), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double,
@@ -97,6 +94,9 @@ _SIGS = {
 }
 # entry points added by later translation units; bound when the library exports them
 _OPTIONAL_SIGS = {
+    "lvc_device_bytes_fetched": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.c_int32]),
+    "lvc_host_alloc": (C.c_int, [C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
+    "lvc_host_free": (C.c_int, [C.c_void_p]),
     "lvc_patch_embed_workspace": (C.c_int64, [C.POINTER(EmbedDesc)]),
     "lvc_patch_embed_pack_weights": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_patch_embed": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

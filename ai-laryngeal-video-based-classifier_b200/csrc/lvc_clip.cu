@@ -84,6 +84,7 @@ struct ClipParams {
   int rps, stages, pitch;    // rows per stage, barrier slots in use (= kMaxStages), bytes per row slot of the WIDEST video
   int ring_bytes;            // size of the byte-granular source-row ring
   int lut4_off;              // lean cv2 consumer: byte offset of the 3 x 1024 table indexed by the unrounded vertical sum
+  int tok_stage_off;         // lean cv2 consumer, 4x4-patch token layout: byte offset of the per-group store staging tiles
   unsigned* err;             // device error word (LVC_DEVERR_*), never NULL
   unsigned long long* fetched;  // device counter: bytes the producers requested from the source buffers (bulk copies)
   unsigned long long* trace;    // profiling (LVC_CLIP_TRACE=1 under the knob gate): CTA 0 logs 4 timestamps per stage, else NULL
@@ -132,6 +133,7 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       : "memory");
 }
 constexpr int kTraceStages = 4096;
+constexpr int kTraceWords = kTraceStages * 4 + 2 * 1024;   // per-stage stamps of CTA 0, then (start, end) of every CTA
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -302,7 +304,8 @@ __device__ __forceinline__ uint32_t shf_r_wrap(uint32_t lo, uint32_t hi, uint32_
 
 template <int ODT, bool STATS>
 __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* smem, uint64_t* full, uint64_t* empty,
-                                                  const StageHdr* hdrs, const int ct, const int lane) {
+                                                  const StageHdr* hdrs, const int ct, const int lane, const bool use_fma,
+                                                  const float (&fa)[3], const float (&fb)[3]) {
   constexpr int kGroups = groups_of(MODE_CV2);
   constexpr int kEsz = ODT == LVC_DT_F32 ? 4 : (ODT == LVC_DT_BF16 ? 2 : 1);
   constexpr bool kT4 = !STATS && ODT != LVC_DT_U8;   // table indexed by the unrounded vertical sum
@@ -331,6 +334,8 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
   uint32_t phase = 0;
   const int stages_per_item = p.rows_per_band / p.rps;
   const bool pair_rows = (p.rps & (2 * kGroups - 1)) == 0;
+  const bool tok44 = ODT == LVC_DT_BF16 && p.layout == LVC_LAYOUT_TOKENS && p.kh == 4 && p.kw == 4 && p.tok_stage_off != 0 &&
+                     (p.rps % (4 * kGroups)) == 0;
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
@@ -387,12 +392,19 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
         t[1] = __umulhi((unsigned)rd.b0, s01 >> 4) + __umulhi((unsigned)rd.b1, s11 >> 4);
         t[2] = __umulhi((unsigned)rd.b0, s02 >> 4) + __umulhi((unsigned)rd.b1, s12 >> 4);
       };
-      auto emit = [&](const unsigned eo, unsigned (&t)[3]) {
+      auto emit = [&](auto FMA, const unsigned eo, unsigned (&t)[3]) {
+        constexpr bool kFma = decltype(FMA)::value;
         char* q = obase + (size_t)eo * kEsz;
-        if (!kT4) {
+        if (!kT4 || kFma) {
 #pragma unroll
           for (int c = 0; c < 3; ++c) t[c] = (t[c] + 2u) >> 2;
           if (STATS) acc32 += t[0] + t[1] + t[2];
+        }
+        if (kFma) {   // bf16 only: verified equal to the table for every 8-bit value (kernel prologue)
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            *reinterpret_cast<__nv_bfloat16*>(q + (size_t)c * cs) = __float2bfloat16_rn(__fmaf_rn((float)t[c], fa[c], fb[c]));
+          return;
         }
         if (ODT == LVC_DT_F32) {
 #pragma unroll
@@ -405,7 +417,59 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
           for (int c = 0; c < 3; ++c) *reinterpret_cast<uint8_t*>(q + (size_t)c * cs) = (uint8_t)t[c];
         }
       };
-      if (!(flags & 4)) {
+      // 4x4-patch token layout (Video Swin): a thread's three samples of a row land 64 B apart as 2-byte stores, eight
+      // sectors per warp-wide store (ncu: a quarter of the LSU data-pipe wavefronts, 3.3x write amplification towards
+      // L2).  Here a group owns whole patch rows of the stage: its 4 x 224 x 3 samples go to a shared-memory tile
+      // [c][dy][x] first, then every thread writes 16-byte pieces = (2 rows x 4 columns) of one (token, channel):
+      // two pieces fill a 32-byte sector of A[m][k].
+      auto rows_tok44 = [&](auto FMA) {
+        constexpr bool kFma = decltype(FMA)::value;
+        unsigned short* stg = reinterpret_cast<unsigned short*>(smem + p.tok_stage_off) + g * (3 * 4 * S);
+        const unsigned K = 3u * (unsigned)p.kt * 16u, csel = (unsigned)p.kt * 16u;
+        auto val = [&](int c, unsigned t) -> unsigned short {
+          if (kFma) return __bfloat16_as_ushort(__float2bfloat16_rn(__fmaf_rn((float)t, fa[c], fb[c])));
+          return __bfloat16_as_ushort(luth[c * kLutStride + t]);
+        };
+        for (int pr = g; pr < (p.rps >> 2); pr += kGroups) {
+          const int r0 = pr * 4;
+#pragma unroll
+          for (int d = 0; d < 4; d += 2) {
+            const RowDesc ra = h->rows[r0 + d], rb = h->rows[r0 + d + 1];
+            const uint32_t oa0 = (uint32_t)ra.off0 + xo_s, oa1 = (uint32_t)ra.off1 + xo_s;
+            const uint32_t ob0 = (uint32_t)rb.off0 + xo_s, ob1 = (uint32_t)rb.off1 + xo_s;
+            uint32_t w[12];
+            lds3(oa0 & ~3u, w[0], w[1], w[2]);
+            lds3(oa1 & ~3u, w[3], w[4], w[5]);
+            lds3(ob0 & ~3u, w[6], w[7], w[8]);
+            lds3(ob1 & ~3u, w[9], w[10], w[11]);
+            unsigned ta[3], tb[3];
+            vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, ta);
+            vert(rb, w[6], w[7], w[8], ob0, w[9], w[10], w[11], ob1, tb);
+            if (!kT4 || kFma) {
+#pragma unroll
+              for (int c = 0; c < 3; ++c) { ta[c] = (ta[c] + 2u) >> 2; tb[c] = (tb[c] + 2u) >> 2; }
+              if (STATS) acc32 += ta[0] + ta[1] + ta[2] + tb[0] + tb[1] + tb[2];
+            }
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              stg[(c * 4 + d) * S + x] = val(c, ta[c]);
+              stg[(c * 4 + d + 1) * S + x] = val(c, tb[c]);
+            }
+          }
+          group_bar(g);
+          const unsigned e0 = h->roff[r0];   // patch row's first output row: ho * (Wo * K)
+          for (int q = x; q < (S / 4) * 6; q += S) {
+            const int tok = q / 6, rem = q - tok * 6, c = rem >> 1, half = rem & 1;
+            const uint2 lo = *reinterpret_cast<const uint2*>(stg + (c * 4 + 2 * half) * S + tok * 4);
+            const uint2 hi = *reinterpret_cast<const uint2*>(stg + (c * 4 + 2 * half + 1) * S + tok * 4);
+            char* dst = obase + (size_t)(e0 + (unsigned)tok * K + (unsigned)c * csel + (unsigned)half * 8u) * 2;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+          }
+          group_bar(g);   // the tile is reused by the group's next patch row / next stage
+        }
+      };
+      auto rows = [&](auto FMA) {
+        if (tok44) { rows_tok44(FMA); return; }
         if (pair_rows) {
           for (int r = g; r < p.rps; r += 2 * kGroups) {
             const RowDesc ra = h->rows[r], rb = h->rows[r + kGroups];
@@ -420,8 +484,8 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
             unsigned ta[3], tb[3];
             vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, ta);
             vert(rb, w[6], w[7], w[8], ob0, w[9], w[10], w[11], ob1, tb);
-            emit(ea, ta);
-            emit(eb, tb);
+            emit(FMA, ea, ta);
+            emit(FMA, eb, tb);
           }
         } else {
           for (int r = g; r < p.rps; r += kGroups) {
@@ -433,9 +497,13 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
             lds3(oa1 & ~3u, w[3], w[4], w[5]);
             unsigned ta[3];
             vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, ta);
-            emit(ea, ta);
+            emit(FMA, ea, ta);
           }
         }
+      };
+      if (!(flags & 4)) {
+        if (ODT == LVC_DT_BF16 && use_fma) rows(std::true_type{});
+        else rows(std::false_type{});
       }
       if (STATS) acc += acc32;
       __syncwarp();
@@ -448,6 +516,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
   }
+  if (p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();   // consumer warp 0 done
 }
 
 // ODT: compile-time output type of the lean cv2 consumer (LVC_DT_*), or -1 = the general consumer (type from the descriptor)
@@ -466,6 +535,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   // scheduled as SMs free up; it waits for this grid to complete before it touches global data
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int tid = threadIdx.x;
+  if (p.trace && tid == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2] = globaltimer_ns();   // CTA start
   const int warp = tid >> 5, lane = tid & 31;
   const int stages_per_item = MODE == MODE_VIVIT ? p.v_stages : p.rows_per_band / p.rps;
 
@@ -493,6 +563,28 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
     }
   }
   __syncthreads();
+  // bf16 outputs: the look-up costs three bank-conflicted shared loads per sample (random 8-bit indices: ~3.5 wavefronts
+  // each -- ncu: 41 % of this kernel's shared-memory wavefronts on the small-source configs, whose consumers are bound by
+  // the LSU data pipe).  The reference's normalisation is affine in the pixel value, so y = fma(v, a, b) rounded to bf16
+  // usually equals the rounded table entry for all 3 x 256 values; every CTA VERIFIES that here and only then replaces
+  // the look-up by two FMA-pipe instructions (bit-identical by construction; any table that fails keeps the look-up).
+  float fa[3] = {0.f, 0.f, 0.f}, fb[3] = {0.f, 0.f, 0.f};
+  bool use_fma = false;
+  if (MODE != MODE_PTV && p.out_dtype == LVC_DT_BF16 && p.lut) {
+    bool ok = true;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      fb[c] = lut[c * 256];
+      fa[c] = __fdiv_rn(__fsub_rn(lut[c * 256 + 255], lut[c * 256]), 255.0f);
+    }
+    for (int i = tid; i < 3 * 256; i += kThreads) {
+      const int c = i >> 8;
+      const float a = c == 0 ? fa[0] : (c == 1 ? fa[1] : fa[2]), b = c == 0 ? fb[0] : (c == 1 ? fb[1] : fb[2]);
+      const __nv_bfloat16 y = __float2bfloat16_rn(__fmaf_rn((float)(i & 255), a, b));
+      ok = ok && (__bfloat16_as_ushort(y) == __bfloat16_as_ushort(lut16[i]));
+    }
+    use_fma = __syncthreads_and(ok) != 0;
+  }
 
   if (warp < kProducers) {
     // ================= producer warps: lane j fetches source row (j&1 ? y1 : y0) of output row j>>1
@@ -685,7 +777,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   // ================= consumer warps: thread -> output column x, group -> rows g, g+G, ...
   const int ct = tid - 32 * kProducers;
   if constexpr (MODE == MODE_CV2 && ODT >= 0) {
-    lean_cv2_consumer<ODT, STATS>(p, smem, full, empty, hdrs, ct, lane);
+    lean_cv2_consumer<ODT, STATS>(p, smem, full, empty, hdrs, ct, lane, use_fma, fa, fb);
     return;
   }
   const int g = ct / S;
@@ -717,8 +809,13 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
       for (int c = 0; c < 3; ++c) __stcs(o + c * cstride, lut[c * 256 + v[c]]);
     } else if (odt == LVC_DT_BF16) {
       __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
+      if (use_fma) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) o[c * cstride] = lut16[c * 256 + v[c]];
+        for (int c = 0; c < 3; ++c) o[c * cstride] = __float2bfloat16_rn(__fmaf_rn((float)v[c], fa[c], fb[c]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) o[c * cstride] = lut16[c * 256 + v[c]];
+      }
     } else {
       uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
 #pragma unroll
@@ -1022,6 +1119,12 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
     p.lut4_off = fixed;
     fixed += 3 * 1024 * (d->out_dtype == LVC_DT_F32 ? 4 : 2);
   }
+  p.tok_stage_off = 0;
+  if (mode == MODE_CV2 && !d->src_float && d->layout == LVC_LAYOUT_TOKENS && d->tok_kh == 4 && d->tok_kw == 4) {
+    p.tok_stage_off = fixed;                       // store staging of the 4x4-patch token layout: [group][c][dy][x] bf16
+    fixed += groups_of(MODE_CV2) * 3 * 4 * S * 2;
+    fixed = (fixed + 127) / 128 * 128;
+  }
   p.ring_off = fixed;
   const int budget = budget_all - fixed;
   p.rps = env_int("LVC_CLIP_RPS", 0);
@@ -1030,7 +1133,9 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
     // 3 stages leave a third of the ring idle, 6 a sixth; cfg 3: 60 -> 53 us with 4 producers); ROI rows are much
     // shorter than a frame row (the ring is byte-granular: their stages take what they need) and the ViViT preset is
     // consumer-bound: those prefer fewer, larger stages
-    const int want_stages = (boxes || mode == MODE_VIVIT) ? 3 : 6;
+    // (with boxes the slots of max_width rows are only the worst case: two such stages must fit, the usual ROI stage is
+    // a fraction of that and the byte-granular ring keeps several in flight)
+    const int want_stages = boxes ? 2 : (mode == MODE_VIVIT ? 3 : 6);
     p.rps = (budget / (16 * p.pitch) >= want_stages) ? 8 : 4;
   }
   if (p.rps < 2 || p.rps > kMaxRPS || (S % p.rps)) return lvc_fail(LVC_E_INVAL, "LVC_CLIP_RPS=%d invalid", p.rps);
@@ -1078,7 +1183,8 @@ namespace { unsigned long long* g_trace_buf = nullptr; }
 // CTA 0 -- producer issued, consumer warp 0 began waiting, stage landed, consumer warp 0 done.
 extern "C" int lvc_clip_trace_read(unsigned long long* out, int stages) {
   if (!g_trace_buf || !out) return lvc_fail(LVC_E_INVAL, "lvc_clip_trace_read: no trace (LVC_PROFILING_KNOBS=1 LVC_CLIP_TRACE=1)");
-  LVC_CUDA_TRY(cudaMemcpy(out, g_trace_buf, (size_t)std::min(stages, kTraceStages) * 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  (void)stages;   // the whole buffer: kTraceStages x 4 stage stamps, then 1024 x (CTA start, CTA end)
+  LVC_CUDA_TRY(cudaMemcpy(out, g_trace_buf, (size_t)kTraceWords * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return LVC_OK;
 }
 
@@ -1222,8 +1328,8 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   if (int rc = make_plan(d, boxes != nullptr, stats != nullptr, di.sms, di.max_smem, p, smem, grid)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (env_int("LVC_CLIP_TRACE", 0)) {   // profiling only: per-stage timeline of CTA 0 (lvc_clip_trace_read)
-    if (!g_trace_buf) LVC_CUDA_TRY(cudaMalloc(&g_trace_buf, kTraceStages * 4 * sizeof(unsigned long long)));
-    LVC_CUDA_TRY(cudaMemsetAsync(g_trace_buf, 0, kTraceStages * 4 * sizeof(unsigned long long), st));
+    if (!g_trace_buf) LVC_CUDA_TRY(cudaMalloc(&g_trace_buf, kTraceWords * sizeof(unsigned long long)));
+    LVC_CUDA_TRY(cudaMemsetAsync(g_trace_buf, 0, kTraceWords * sizeof(unsigned long long), st));
     p.trace = g_trace_buf;
   }
   if (mode == MODE_CV2) {

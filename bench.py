@@ -53,6 +53,16 @@ def algorithmic_bytes_per_frame(h, w, out_elem=4):
     return uniq(h) * uniq(w) * 3 + 150528 * out_elem + 4
 
 
+def l2_flush(buf):
+    """Flush L2 between timed iterations of the small configs: WRITE a buffer larger than L2 (256 MB vs 126 MB), then READ it
+    back.  The write alone leaves L2 full of dirty lines whose write-back (126 MB, ~19 us of HBM time) lands inside the next
+    timed kernel -- on a 50 us kernel that is a quarter of the measurement and hides every kernel-side change (measured: the
+    TimeSformer clip stage read 54 us by events whatever the kernel did, 41-43 us by in-kernel CTA timestamps).  The read pass
+    forces the write-back before the timed region and leaves L2 full of clean lines of the flush buffer."""
+    buf.zero_()
+    buf.view(-1)[: buf.numel() // 8 * 8].view(dtype=__import__("torch").int64).sum()
+
+
 class ClockSampler:
     """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md): NVML polled from
     a thread every ~2 ms (the timed region of the headline workload lasts ~20 ms, too short for
@@ -356,7 +366,7 @@ def run_secondary(dev, iters=10):
             ts = []
             for _ in range(3 + iters):
                 if flush_l2:
-                    flush.zero_()
+                    l2_flush(flush)
                 # keep the device busy ~0.2 ms so the host-side call (Python + ctypes) is fully enqueued
                 # before e0 fires: the interval then holds device time only, no launch gap
                 torch.cuda._sleep(400000)
@@ -439,7 +449,7 @@ def run_secondary(dev, iters=10):
     clip = torch.empty(batch.shape, dtype=torch.float32, device=dev)
     ts = []
     for _ in range(3 + iters):
-        flush.zero_()
+        l2_flush(flush)
         torch.cuda._sleep(400000)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -497,7 +507,7 @@ def run_cfg1(dev, iters=10):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     ts = []
     for _ in range(3 + iters):
-        flush.zero_()
+        l2_flush(flush)
         torch.cuda._sleep(400000)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()

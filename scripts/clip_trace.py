@@ -25,12 +25,21 @@ for _ in range(3):
     cb.run(batch, tok)
 torch.cuda.synchronize()
 n = 4096
-buf = (C.c_ulonglong * (4 * n))()
+buf = (C.c_ulonglong * (4 * n + 2048))()
 fn = _lib.lib().lvc_clip_trace_read
 fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_int]
 assert fn(buf, n) == 0
-t = np.frombuffer(buf, dtype=np.uint64).reshape(n, 4).astype(np.int64)
+raw = np.frombuffer(buf, dtype=np.uint64).astype(np.int64)
+cta = raw[4 * n:].reshape(1024, 2)
+cta = cta[(cta > 0).all(axis=1)]
+t = raw[:4 * n].reshape(n, 4)
 t = t[(t > 0).all(axis=1)]
+if len(cta):
+    s0 = cta[:, 0].min()
+    dur = cta[:, 1] - cta[:, 0]
+    print(f"{name}: {len(cta)} CTAs; start spread {(cta[:, 0].max() - s0) / 1e3:.1f} us; CTA duration min {dur.min() / 1e3:.1f} median "
+          f"{np.median(dur) / 1e3:.1f} max {dur.max() / 1e3:.1f} us; first start -> last end {(cta[:, 1].max() - s0) / 1e3:.1f} us; "
+          f"CTA 0: {dur[0] / 1e3:.1f} us" if len(dur) else "")
 t0 = t[:, 0].min()
 t = t - t0
 issue, wait0, have, done = t[:, 0], t[:, 1], t[:, 2], t[:, 3]
@@ -47,6 +56,7 @@ print(f"  producer issue spacing: median {np.median(gaps):.0f} ns, p90 {np.perce
 w = have - wait0
 big = np.argsort(-w)[:12]
 print("  longest waits (stage, wait ns, issued-before-wait-start ns):", [(int(i), int(w[i]), int(wait0[i] - issue[i])) for i in sorted(big)])
-print("  first 24 stages [issue, wait0, have, done] (ns):")
-for i in range(min(24, len(t))):
-    print("   ", i, t[i].tolist())
+if os.environ.get("CLIP_TRACE_STAGES"):
+    print("  first 24 stages [issue, wait0, have, done] (ns):")
+    for i in range(min(24, len(t))):
+        print("   ", i, t[i].tolist())

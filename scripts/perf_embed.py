@@ -31,7 +31,7 @@ def run(name, iters=20):
     torch.cuda.synchronize()
     ts = []
     for _ in range(iters):
-        flush.zero_()  # > L2
+        flush.zero_(); flush.view(torch.int64).sum()  # > L2
         torch.cuda._sleep(400000)  # host call fully enqueued before e0 fires
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
