@@ -29,6 +29,9 @@ enum { MODE_CV2 = 0, MODE_VIVIT = 1, MODE_PTV = 2 };
 // Consumer groups work on different rows of a stage (224 threads each, thread = output column).  Two groups for the
 // cv2 / torch chains; the ViViT preset runs two Pillow passes on top of the resize and is bound by consumer issue,
 // so it gets four (measured with 2+ producer warps: 155 -> 135 us on config 2; the other modes lose with four).
+#ifndef LVC_CLIP_MINBLOCKS
+#define LVC_CLIP_MINBLOCKS 1   // 2: cap the cv2 / torch kernels at 56 registers so that two CTAs share an SM (experiment)
+#endif
 #ifndef LVC_CLIP_GROUPS_CV2
 #define LVC_CLIP_GROUPS_CV2 2
 #endif
@@ -84,7 +87,7 @@ struct ClipParams {
   int rps, stages, pitch;    // rows per stage, barrier slots in use (= kMaxStages), bytes per row slot of the WIDEST video
   int ring_bytes;            // size of the byte-granular source-row ring
   int lut4_off;              // lean cv2 consumer: byte offset of the 3 x 1024 table indexed by the unrounded vertical sum
-  int tok_stage_off;         // lean cv2 consumer, 4x4-patch token layout: byte offset of the per-group store staging tiles
+  int no_fma;                // profiling knob LVC_CLIP_NO_FMA: keep the bf16 look-up even when the affine form verifies
   unsigned* err;             // device error word (LVC_DEVERR_*), never NULL
   unsigned long long* fetched;  // device counter: bytes the producers requested from the source buffers (bulk copies)
   unsigned long long* trace;    // profiling (LVC_CLIP_TRACE=1 under the knob gate): CTA 0 logs 4 timestamps per stage, else NULL
@@ -334,8 +337,6 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
   uint32_t phase = 0;
   const int stages_per_item = p.rows_per_band / p.rps;
   const bool pair_rows = (p.rps & (2 * kGroups - 1)) == 0;
-  const bool tok44 = ODT == LVC_DT_BF16 && p.layout == LVC_LAYOUT_TOKENS && p.kh == 4 && p.kw == 4 && p.tok_stage_off != 0 &&
-                     (p.rps % (4 * kGroups)) == 0;
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
@@ -417,59 +418,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
           for (int c = 0; c < 3; ++c) *reinterpret_cast<uint8_t*>(q + (size_t)c * cs) = (uint8_t)t[c];
         }
       };
-      // 4x4-patch token layout (Video Swin): a thread's three samples of a row land 64 B apart as 2-byte stores, eight
-      // sectors per warp-wide store (ncu: a quarter of the LSU data-pipe wavefronts, 3.3x write amplification towards
-      // L2).  Here a group owns whole patch rows of the stage: its 4 x 224 x 3 samples go to a shared-memory tile
-      // [c][dy][x] first, then every thread writes 16-byte pieces = (2 rows x 4 columns) of one (token, channel):
-      // two pieces fill a 32-byte sector of A[m][k].
-      auto rows_tok44 = [&](auto FMA) {
-        constexpr bool kFma = decltype(FMA)::value;
-        unsigned short* stg = reinterpret_cast<unsigned short*>(smem + p.tok_stage_off) + g * (3 * 4 * S);
-        const unsigned K = 3u * (unsigned)p.kt * 16u, csel = (unsigned)p.kt * 16u;
-        auto val = [&](int c, unsigned t) -> unsigned short {
-          if (kFma) return __bfloat16_as_ushort(__float2bfloat16_rn(__fmaf_rn((float)t, fa[c], fb[c])));
-          return __bfloat16_as_ushort(luth[c * kLutStride + t]);
-        };
-        for (int pr = g; pr < (p.rps >> 2); pr += kGroups) {
-          const int r0 = pr * 4;
-#pragma unroll
-          for (int d = 0; d < 4; d += 2) {
-            const RowDesc ra = h->rows[r0 + d], rb = h->rows[r0 + d + 1];
-            const uint32_t oa0 = (uint32_t)ra.off0 + xo_s, oa1 = (uint32_t)ra.off1 + xo_s;
-            const uint32_t ob0 = (uint32_t)rb.off0 + xo_s, ob1 = (uint32_t)rb.off1 + xo_s;
-            uint32_t w[12];
-            lds3(oa0 & ~3u, w[0], w[1], w[2]);
-            lds3(oa1 & ~3u, w[3], w[4], w[5]);
-            lds3(ob0 & ~3u, w[6], w[7], w[8]);
-            lds3(ob1 & ~3u, w[9], w[10], w[11]);
-            unsigned ta[3], tb[3];
-            vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, ta);
-            vert(rb, w[6], w[7], w[8], ob0, w[9], w[10], w[11], ob1, tb);
-            if (!kT4 || kFma) {
-#pragma unroll
-              for (int c = 0; c < 3; ++c) { ta[c] = (ta[c] + 2u) >> 2; tb[c] = (tb[c] + 2u) >> 2; }
-              if (STATS) acc32 += ta[0] + ta[1] + ta[2] + tb[0] + tb[1] + tb[2];
-            }
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              stg[(c * 4 + d) * S + x] = val(c, ta[c]);
-              stg[(c * 4 + d + 1) * S + x] = val(c, tb[c]);
-            }
-          }
-          group_bar(g);
-          const unsigned e0 = h->roff[r0];   // patch row's first output row: ho * (Wo * K)
-          for (int q = x; q < (S / 4) * 6; q += S) {
-            const int tok = q / 6, rem = q - tok * 6, c = rem >> 1, half = rem & 1;
-            const uint2 lo = *reinterpret_cast<const uint2*>(stg + (c * 4 + 2 * half) * S + tok * 4);
-            const uint2 hi = *reinterpret_cast<const uint2*>(stg + (c * 4 + 2 * half + 1) * S + tok * 4);
-            char* dst = obase + (size_t)(e0 + (unsigned)tok * K + (unsigned)c * csel + (unsigned)half * 8u) * 2;
-            *reinterpret_cast<uint4*>(dst) = make_uint4(lo.x, lo.y, hi.x, hi.y);
-          }
-          group_bar(g);   // the tile is reused by the group's next patch row / next stage
-        }
-      };
       auto rows = [&](auto FMA) {
-        if (tok44) { rows_tok44(FMA); return; }
         if (pair_rows) {
           for (int r = g; r < p.rps; r += 2 * kGroups) {
             const RowDesc ra = h->rows[r], rb = h->rows[r + kGroups];
@@ -521,7 +470,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
 
 // ODT: compile-time output type of the lean cv2 consumer (LVC_DT_*), or -1 = the general consumer (type from the descriptor)
 template <int MODE, int ODT, bool STATS>
-__global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
+__global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LVC_CLIP_MINBLOCKS)) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
   constexpr int kGroups = groups_of(MODE), kConsumers = kGroups * S, kThreads = threads_of(MODE);
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
@@ -570,7 +519,7 @@ __global__ void __launch_bounds__(threads_of(MODE), 1) lvc_clip_kernel(const __g
   // the look-up by two FMA-pipe instructions (bit-identical by construction; any table that fails keeps the look-up).
   float fa[3] = {0.f, 0.f, 0.f}, fb[3] = {0.f, 0.f, 0.f};
   bool use_fma = false;
-  if (MODE != MODE_PTV && p.out_dtype == LVC_DT_BF16 && p.lut) {
+  if (MODE != MODE_PTV && p.out_dtype == LVC_DT_BF16 && p.lut && !p.no_fma) {
     bool ok = true;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -1119,12 +1068,6 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
     p.lut4_off = fixed;
     fixed += 3 * 1024 * (d->out_dtype == LVC_DT_F32 ? 4 : 2);
   }
-  p.tok_stage_off = 0;
-  if (mode == MODE_CV2 && !d->src_float && d->layout == LVC_LAYOUT_TOKENS && d->tok_kh == 4 && d->tok_kw == 4) {
-    p.tok_stage_off = fixed;                       // store staging of the 4x4-patch token layout: [group][c][dy][x] bf16
-    fixed += groups_of(MODE_CV2) * 3 * 4 * S * 2;
-    fixed = (fixed + 127) / 128 * 128;
-  }
   p.ring_off = fixed;
   const int budget = budget_all - fixed;
   p.rps = env_int("LVC_CLIP_RPS", 0);
@@ -1150,6 +1093,7 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
   p.ring_bytes = (int)std::min<long long>((long long)budget, (long long)kMaxStages * stage_bytes) & ~127;
   smem = (size_t)fixed + (size_t)p.ring_bytes;
   p.merge_rows = env_int("LVC_CLIP_MERGE", 1);
+  p.no_fma = env_int("LVC_CLIP_NO_FMA", 0);
   p.producers = std::max(1, std::min(kProducers, env_int("LVC_CLIP_NP", kProducers)));
 
   const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)max_smem / (smem + 1024)));

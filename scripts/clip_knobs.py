@@ -47,12 +47,14 @@ def timeit(cb, batch, tok, n=15):
 
 KNOBS = [{}, {"LVC_CLIP_RPS": "16"}, {"LVC_CLIP_RPS": "4"}, {"LVC_CLIP_RPS": "2"}, {"LVC_CLIP_SMEM_KB": "100"}, {"LVC_CLIP_BAND": "56"},
          {"LVC_CLIP_BAND": "16"}, {"LVC_CLIP_BAND": "224"}]
+if os.environ.get("CLIP_KNOBS_AB"):   # the consumer variants of round 2
+    KNOBS = [{}, {"LVC_CLIP_NO_FMA": "1"}]
 if os.environ.get("CLIP_KNOBS_MATRIX"):   # producers x rows-per-stage
     KNOBS = [{"LVC_CLIP_NP": str(n), **({"LVC_CLIP_RPS": r} if r else {})} for n in (1, 2, 4) for r in ("", "4")]
 for name in (sys.argv[1:] or ["swin_cfg4", "timesformer_cfg3", "vivit_cfg2"]):
     cb, batch, tok, vids = setup(name)
     for k in KNOBS:
-        for kk in ("LVC_CLIP_RPS", "LVC_CLIP_SMEM_KB", "LVC_CLIP_BAND", "LVC_CLIP_NP"):
+        for kk in ("LVC_CLIP_RPS", "LVC_CLIP_SMEM_KB", "LVC_CLIP_BAND", "LVC_CLIP_NP", "LVC_CLIP_NO_FMA", "LVC_CLIP_NO_TOK44"):
             os.environ.pop(kk, None)
         os.environ.update(k)
         try:
