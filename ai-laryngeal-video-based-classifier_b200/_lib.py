@@ -16,7 +16,7 @@ VARIANT_DATASET, VARIANT_CLAMPED, VARIANT_NUMPY_INFER = 0, 1, 2
 LUT_DIV, LUT_MUL64 = 0, 1
 HF_SRC_HOST = 1
 HOST_WRITE_COMBINED = 1
-DEVERR_FRAME_TOO_WIDE, DEVERR_FRAME_TOO_LARGE = 1, 2
+DEVERR_FRAME_TOO_WIDE, DEVERR_FRAME_TOO_LARGE, DEVERR_INTERNAL = 1, 2, 4
 B200_SMS, B200_MAX_SMEM = 148, 232448
 RESAMPLE_CV2, RESAMPLE_CV2_PIL256, RESAMPLE_PTV_EVAL, RESAMPLE_PIL_SHORT = 0, 1, 2, 3
 LAYOUT_BTCHW, LAYOUT_BCTHW, LAYOUT_BTHWC, LAYOUT_TOKENS = 0, 1, 2, 3

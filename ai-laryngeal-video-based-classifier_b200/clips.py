@@ -60,7 +60,8 @@ def device_status(clear=True, device=None):
         flags = C.c_uint32(0)
         _lib.check(_lib.lib().lvc_device_status(torch.cuda.current_stream(dev).cuda_stream, C.byref(flags), int(clear)),
                    "lvc_device_status")
-    names = {_lib.DEVERR_FRAME_TOO_WIDE: "frame_too_wide", _lib.DEVERR_FRAME_TOO_LARGE: "frame_too_large"}
+    names = {_lib.DEVERR_FRAME_TOO_WIDE: "frame_too_wide", _lib.DEVERR_FRAME_TOO_LARGE: "frame_too_large",
+             _lib.DEVERR_INTERNAL: "internal_check_failed"}
     return {n for bit, n in names.items() if flags.value & bit}
 
 

@@ -468,6 +468,181 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
   if (p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();   // consumer warp 0 done
 }
 
+// ---- lean consumer of the ViViT preset ---------------------------------------------------------------------------------
+// cv2 resize row (lean arithmetic as above) -> Pillow horizontal 224 -> 256 pass (cropped columns) into the band's
+// intermediate buffer; after the band's last stage the Pillow vertical pass, normalisation and store.  This preset runs
+// 28 consumer warps and IS issue-bound (ncu: issue slots 76 % busy), so the instruction count is the time: against the
+// general consumer the per-stage bookkeeping shrinks to what this mode reads, the resize uses the lean row body, the output
+// type is resolved once per band instead of once per sample, and bf16 outputs take the verified affine form instead of
+// three bank-conflicted table look-ups per sample.
+// Pillow's BILINEAR 224 -> 256 pass on one packed pixel pair (R | G << 8 | B << 16).  Pillow computes, per channel,
+// (2^21 + p0*k0 + p1*k1 [+ p2*k2]) >> 22 with 22-bit weights; for THIS geometry (scale 7/8, sample centres on multiples of
+// 1/16) every sample has exactly two taps and the weights are k = m * 2^18 with m0 + m1 = 16 (pil_tap; the kernel prologue
+// checks the table), so the expression is 2^18 * (8 + m0*p0 + m1*p1) >> 22 = (m0*p0 + m1*p1 + 8) >> 4 -- exactly.  With
+// 4-bit weights the sums stay below 2^12: R and B go through one 32-bit multiply-add chain in 16-bit fields, G through a
+// second (13 instructions per pixel instead of 9 PRMT + 9 IMAD + packing).
+__device__ __forceinline__ uint32_t pil16(const uint32_t w0, const uint32_t w1, const uint32_t m0, const uint32_t m1) {
+  const uint32_t rb = (w0 & 0x00ff00ffu) * m0 + ((w1 & 0x00ff00ffu) * m1 + 0x00080008u);
+  const uint32_t gg = (w0 & 0x0000ff00u) * m0 + ((w1 & 0x0000ff00u) * m1 + 0x00000800u);
+  return ((rb >> 4) & 0x00ff00ffu) | ((gg >> 4) & 0x0000ff00u);
+}
+
+__device__ __forceinline__ void cv2_row_lean(const RowDesc& rd, const uint32_t xo_s, const uint32_t a01, const uint32_t selA,
+                                             const uint32_t selB, unsigned (&v)[3]) {
+  const uint32_t o0 = (uint32_t)rd.off0 + xo_s, o1 = (uint32_t)rd.off1 + xo_s;
+  uint32_t a, b, c, d, e, f;
+  lds3(o0 & ~3u, a, b, c);
+  lds3(o1 & ~3u, d, e, f);
+  const uint32_t sh0 = o0 << 3, sh1 = o1 << 3;   // shf wraps at 32: (o & 3) * 8
+  const uint32_t lo0 = shf_r_wrap(a, b, sh0), hi0 = shf_r_wrap(b, c, sh0);
+  const uint32_t lo1 = shf_r_wrap(d, e, sh1), hi1 = shf_r_wrap(e, f, sh1);
+  const uint32_t wa0 = __byte_perm(lo0, hi0, selA), wb0 = __byte_perm(lo0, hi0, selB);
+  const uint32_t wa1 = __byte_perm(lo1, hi1, selA), wb1 = __byte_perm(lo1, hi1, selB);
+  const unsigned s00 = __dp2a_lo(a01, wa0, 0u), s01 = __dp2a_hi(a01, wa0, 0u), s02 = __dp2a_lo(a01, wb0, 0u);
+  const unsigned s10 = __dp2a_lo(a01, wa1, 0u), s11 = __dp2a_hi(a01, wa1, 0u), s12 = __dp2a_lo(a01, wb1, 0u);
+  v[0] = (__umulhi((unsigned)rd.b0, s00 >> 4) + __umulhi((unsigned)rd.b1, s10 >> 4) + 2u) >> 2;
+  v[1] = (__umulhi((unsigned)rd.b0, s01 >> 4) + __umulhi((unsigned)rd.b1, s11 >> 4) + 2u) >> 2;
+  v[2] = (__umulhi((unsigned)rd.b0, s02 >> 4) + __umulhi((unsigned)rd.b1, s12 >> 4) + 2u) >> 2;
+}
+
+template <bool STATS>
+__device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t* smem, uint64_t* full, uint64_t* empty,
+                                                    const StageHdr* hdrs, const int ct, const int lane, const bool use_fma,
+                                                    const float (&fa)[3], const float (&fb)[3]) {
+  constexpr int kGroups = groups_of(MODE_VIVIT), kConsumers = kGroups * S;
+  const int g = ct / S, x = ct - g * S;
+  const uint32_t ring_s = smem_u32(smem) + (uint32_t)p.ring_off;
+  const float* lut = reinterpret_cast<const float*>(smem + kLutOff);
+  const __nv_bfloat16* lut16 = reinterpret_cast<const __nv_bfloat16*>(smem + kLut16Off);
+  const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
+  const int4 hx = vt[x];   // Pillow taps of this thread's (cropped) column: first source column, 22-bit weights
+  const uint32_t hm0 = (uint32_t)hx.y >> 18, hm1 = (uint32_t)hx.z >> 18;   // ... which are m * 2^18 here: see pil16
+  uint32_t* rbuf = reinterpret_cast<uint32_t*>(smem + kVivitRowBufOff) + g * 2 * S;   // [parity][S] per group
+  uint32_t* inter = reinterpret_cast<uint32_t*>(smem + kVivitInterOff);
+  const uint32_t selA = p.bgr ? 0x4152u : 0x4130u, selB = p.bgr ? 0x4430u : 0x4452u;
+  const unsigned xoff = col_offset(p, x);
+  // output addressing of the layout: channel stride (elements) and the multiplier of row_part()
+  unsigned cs, rowmul;
+  switch (p.layout) {
+    case LVC_LAYOUT_BTCHW: cs = S * S; rowmul = S; break;
+    case LVC_LAYOUT_BCTHW: cs = (unsigned)p.T * S * S; rowmul = S; break;
+    case LVC_LAYOUT_BTHWC: cs = 1; rowmul = S * 3; break;
+    default: cs = (unsigned)(p.kt * p.kh * p.kw); rowmul = (unsigned)(S / p.kw) * (unsigned)(3 * p.kt * p.kh * p.kw);
+  }
+  int cached_sw = -1, cached_flags = -1;
+  uint32_t xo_s = 0, a01 = 0;
+  unsigned long long acc = 0;
+  int acc_b = -1, parity = 0;
+  int slot = 0, cn = 0;
+  uint32_t phase = 0;
+
+  for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+    bool item_bad = false;
+    unsigned long long obase = 0;
+    for (int st = 0; st < p.v_stages; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
+      const bool tr = p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
+      if (tr) p.trace[cn * 4 + 1] = globaltimer_ns();
+      mbar_wait(&full[slot], phase);
+      if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();
+      const StageHdr* h = &hdrs[slot];
+      const int sw = h->sw, flags = h->flags;
+      if (sw != cached_sw || flags != cached_flags) {
+        cached_sw = sw; cached_flags = flags;
+        int xo, a0, a1;
+        if (flags & 1) { xo = 6 * x; a0 = 32; a1 = 32; }   // exact 2x2: INTER_AREA as the same fixed-point blend
+        else {
+          int sx; float fr;
+          cv_tap(x, cv_scale(sw), sx, fr);
+          if (sx < 0) { sx = 0; fr = 0.f; }
+          if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }
+          a0 = coef(__fsub_rn(1.0f, fr));
+          a1 = coef(fr);
+          xo = 3 * sx;
+        }
+        xo_s = ring_s + (uint32_t)xo;
+        a01 = (uint32_t)a0 | ((uint32_t)a1 << 16);
+      }
+      if (STATS) {
+        const int b = h->clip;
+        if (b != acc_b) {
+          if (acc_b >= 0 && p.stats) {
+#pragma unroll
+            for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
+          }
+          acc = 0; acc_b = b;
+        }
+      }
+      if (st == 0) obase = h->obase;
+      if (flags & 4) item_bad = true;   // nothing was fetched for this item (contract violation, flagged by the producer)
+      else {
+        const int oy0 = h->oy0, rlo = h->rlo, own_hi = h->nw;
+        unsigned acc32 = 0;
+        for (int r = g; r < p.rps; r += kGroups) {
+          const RowDesc rd = h->rows[r];
+          const int oyr = oy0 + r;
+          unsigned v[3];
+          cv2_row_lean(rd, xo_s, a01, selA, selB, v);
+          // checksum of the resized rows this band OWNS (halo rows belong to the neighbour band)
+          if (STATS && oyr < S && oyr < own_hi) acc32 += v[0] + v[1] + v[2];
+          // Pillow horizontal pass of the row (224 -> cropped 224 of 256), rounded to uint8; one word per pixel
+          uint32_t* rb = rbuf + parity * S;
+          parity ^= 1;
+          rb[x] = v[0] | (v[1] << 8) | (v[2] << 16);
+          group_bar(g);
+          inter[(oyr - rlo) * S + x] = pil16(rb[hx.x], rb[hx.x + 1], hm0, hm1);
+        }
+        if (STATS) acc += acc32;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (tr) p.trace[cn * 4 + 3] = globaltimer_ns();
+    }
+    // the band's resized rows went through the horizontal pass: Pillow vertical pass + normalisation + store
+    consumers_bar(kConsumers);
+    if (!item_bad) {
+      const int band = item % p.bands, ylo = band * p.rows_per_band, rlo = vt[ylo].x;
+      auto vpass = [&](auto ODTV) {
+        constexpr int kOdt = decltype(ODTV)::value;   // 0 f32, 1 bf16 table, 2 u8, 3 bf16 affine
+#pragma unroll 2
+        for (int y = ylo + g; y < ylo + p.rows_per_band; y += kGroups) {
+          const size_t eoff = (size_t)obase + (size_t)(row_part(p, rowmul, y) + xoff);
+          const int4 ty = vt[y];
+          const uint32_t* tp = inter + (ty.x - rlo) * S + x;
+          const uint32_t pk = pil16(tp[0], tp[S], (uint32_t)ty.y >> 18, (uint32_t)ty.z >> 18);
+          const int v[3] = {(int)(pk & 0xffu), (int)((pk >> 8) & 0xffu), (int)(pk >> 16)};
+          if (kOdt == 0) {
+            float* o = reinterpret_cast<float*>(p.out) + eoff;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) __stcs(o + (size_t)c * cs, lut[c * 256 + v[c]]);
+          } else if (kOdt == 2) {
+            uint8_t* o = reinterpret_cast<uint8_t*>(p.out) + eoff;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o[(size_t)c * cs] = (uint8_t)v[c];
+          } else {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + eoff;
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+              o[(size_t)c * cs] = kOdt == 3 ? __float2bfloat16_rn(__fmaf_rn((float)v[c], fa[c], fb[c])) : lut16[c * 256 + v[c]];
+          }
+        }
+      };
+      using std::integral_constant;
+      if (p.out_dtype == LVC_DT_F32) vpass(integral_constant<int, 0>{});
+      else if (p.out_dtype == LVC_DT_U8) vpass(integral_constant<int, 2>{});
+      else if (use_fma) vpass(integral_constant<int, 3>{});
+      else vpass(integral_constant<int, 1>{});
+    }
+    consumers_bar(kConsumers);   // the next band's horizontal pass overwrites the intermediate buffer
+  }
+  if (STATS && p.stats && acc_b >= 0) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
+  }
+  if (p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();
+}
+
 // ODT: compile-time output type of the lean cv2 consumer (LVC_DT_*), or -1 = the general consumer (type from the descriptor)
 template <int MODE, int ODT, bool STATS>
 __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LVC_CLIP_MINBLOCKS)) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
@@ -502,7 +677,12 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
       lut16[i] = __float2bfloat16_rn(w);
     }
   if (MODE == MODE_VIVIT)
-    for (int i = tid; i < S; i += kThreads) reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = pil_tap(i);
+    for (int i = tid; i < S; i += kThreads) {
+      const int4 t = pil_tap(i);
+      reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = t;
+      // the lean consumer's 4-bit form of the Pillow pass (pil16) needs two taps, multiples of 2^18, summing to 2^22
+      if (((t.y | t.z) & 0x3ffff) || t.w || t.y + t.z != (1 << 22)) atomicOr(p.err, (unsigned)LVC_DEVERR_INTERNAL);
+    }
   if (MODE == MODE_CV2 && ODT >= 0 && ODT != LVC_DT_U8 && !STATS && p.lut) {
     // table of the lean consumer: entry t = LUT[(t + 2) >> 2], t = unrounded sum of the two vertical terms (<= 1020)
     for (int i = tid; i < 3 * 1024; i += kThreads) {
@@ -728,6 +908,12 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
   if constexpr (MODE == MODE_CV2 && ODT >= 0) {
     lean_cv2_consumer<ODT, STATS>(p, smem, full, empty, hdrs, ct, lane, use_fma, fa, fb);
     return;
+  }
+  if constexpr (MODE == MODE_VIVIT) {
+    if (!p.f32src) {   // float frames keep the general consumer below
+      lean_vivit_consumer<STATS>(p, smem, full, empty, hdrs, ct, lane, use_fma, fa, fb);
+      return;
+    }
   }
   const int g = ct / S;
   const int x = ct - g * S;
@@ -1035,7 +1221,9 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
   const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
   // row slot of the widest video: window bytes + alignment slack, rounded to 16 (+16 to stagger banks)
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
-  const int budget_all = std::min(max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", 200) * 1024, 96 * 1024));
+  // the whole opt-in shared memory of the SM (227 KB on B200): the kernel keeps next to nothing in L1, and the ViViT preset --
+  // whose Pillow intermediate takes 50-60 KB -- gains a fifth ring stage (cfg 2: 133 -> 121 us); LVC_CLIP_SMEM_KB narrows it
+  const int budget_all = std::min(max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", max_smem / 1024 + 1) * 1024, 96 * 1024));
   // MODE_VIVIT: the Pillow stage needs its vertical window on chip.  A band of R output rows spans at most
   // floor((R-1)*7/8) + 4 resized rows (halo included); pick the band count that minimises rounds x rows per
   // item (whole frames when the batch is large enough that quantisation does not matter) AMONG the candidates whose
@@ -1285,6 +1473,7 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
       default: return st8 ? launch<MODE_CV2, LVC_DT_U8, true>(p, grid, smem, st) : launch<MODE_CV2, LVC_DT_U8, false>(p, grid, smem, st);
     }
   }
-  if (mode == MODE_VIVIT) return launch<MODE_VIVIT>(p, grid, smem, st);
+  if (mode == MODE_VIVIT)
+    return stats ? launch<MODE_VIVIT, -1, true>(p, grid, smem, st) : launch<MODE_VIVIT, -1, false>(p, grid, smem, st);
   return launch<MODE_PTV, -1, false>(p, grid, smem, st);
 }

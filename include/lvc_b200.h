@@ -234,7 +234,8 @@ int lvc_clip_validate(const lvc_clip_desc* desc, int32_t max_height, const lvc_v
  * bit mask per device, OR-ed by the kernels.  Synchronises `stream`, returns the mask and (clear != 0) resets it. */
 enum {
   LVC_DEVERR_FRAME_TOO_WIDE = 1,  /* lvc_clip_forward: a source window does not fit the ring sized by max_width */
-  LVC_DEVERR_FRAME_TOO_LARGE = 2  /* lvc_hf_clip_forward: a video exceeds max_width x max_height */
+  LVC_DEVERR_FRAME_TOO_LARGE = 2, /* lvc_hf_clip_forward: a video exceeds max_width x max_height */
+  LVC_DEVERR_INTERNAL = 4         /* a kernel's own consistency check failed (never expected; report it) */
 };
 int lvc_device_status(void* stream, uint32_t* flags, int32_t clear);
 

@@ -45,7 +45,7 @@ def timeit(cb, batch, tok, n=15):
     return float(np.median(ts[3:]))
 
 
-KNOBS = [{}, {"LVC_CLIP_RPS": "16"}, {"LVC_CLIP_RPS": "4"}, {"LVC_CLIP_RPS": "2"}, {"LVC_CLIP_SMEM_KB": "100"}, {"LVC_CLIP_BAND": "56"},
+KNOBS = [{}, {"LVC_CLIP_SMEM_KB": "227"}, {"LVC_CLIP_RPS": "16"}, {"LVC_CLIP_RPS": "4"}, {"LVC_CLIP_RPS": "2"}, {"LVC_CLIP_SMEM_KB": "100"}, {"LVC_CLIP_BAND": "56"},
          {"LVC_CLIP_BAND": "16"}, {"LVC_CLIP_BAND": "224"}]
 if os.environ.get("CLIP_KNOBS_AB"):   # the consumer variants of round 2
     KNOBS = [{}, {"LVC_CLIP_NO_FMA": "1"}]
