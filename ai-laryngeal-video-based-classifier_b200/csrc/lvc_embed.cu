@@ -17,6 +17,7 @@
 #include <utility>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdint>
 #include <cstdlib>
 
@@ -1296,3 +1297,50 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
   return LVC_OK;
 }
 }  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+// lvc_patch_embed_static: lvc_patch_embed for callers that cannot allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  The patch matrix A[M][K] lives in a file-scope device array instead of a
+// caller workspace; every GPU that loads the library holds LVC_STATIC_SCRATCH_BYTES of it until the process exits.
+// The array's name is a host-side stand-in in host code, so the device address is taken once per device with
+// cudaGetSymbolAddress (that device current) and cached.  No cudaMalloc / cudaFree / allocating routine is called.
+__device__ __align__(256) static unsigned char g_static_scratch[LVC_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+std::atomic<void*> g_static_scratch_ptr[kMaxStaticDevices];
+
+int static_scratch_address(void** out) {
+  int dev = -1;
+  LVC_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxStaticDevices) return lvc_fail(LVC_E_NOTSUP, "patch_embed_static: device ordinal %d out of range", dev);
+  void* p = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    LVC_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));   // address on the CURRENT device (= dev)
+    if (!p || (reinterpret_cast<uintptr_t>(p) & 255))
+      return lvc_fail(LVC_E_CUDA, "patch_embed_static: cudaGetSymbolAddress returned an unusable address %p", p);
+    g_static_scratch_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return LVC_OK;
+}
+}  // namespace
+
+extern "C" int64_t lvc_patch_embed_static_capacity(void) { return (int64_t)LVC_STATIC_SCRATCH_BYTES; }
+
+extern "C" int lvc_patch_embed_static(const lvc_embed_desc* d, const void* x, const void* w_packed, const float* bias,
+                                      const float* ln_w, const float* ln_b, void* out, void* stream) {
+  if (!d) return lvc_fail(LVC_E_INVAL, "patch_embed_static: NULL descriptor");
+  const int64_t need = lvc_patch_embed_workspace(d);
+  if (need < 0) return LVC_E_INVAL;   // message already recorded by the geometry check
+  if (d->x_layout != LVC_LAYOUT_TOKENS && need > (int64_t)LVC_STATIC_SCRATCH_BYTES)
+    return lvc_fail(LVC_E_SHAPE, "patch_embed_static: the patch matrix needs %lld bytes of scratch, the built-in array holds "
+                    "%lld (LVC_STATIC_SCRATCH_BYTES); use lvc_patch_embed with a caller workspace",
+                    (long long)need, (long long)LVC_STATIC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  int rc = static_scratch_address(&scratch);
+  if (rc != LVC_OK) return rc;
+  // Nothing has to start at zero: the im2col pass overwrites all M*K elements of A before the GEMM reads them, and the
+  // tensor map is built on exactly M rows (rows past M are zero-filled by TMA, never read from the array).
+  return patch_embed_impl(d, x, w_packed, bias, ln_w, ln_b, EmbTables{nullptr, nullptr, nullptr, 0}, out, scratch, stream);
+}

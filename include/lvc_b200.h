@@ -305,6 +305,22 @@ int lvc_patch_embed(const lvc_embed_desc* d, const void* x, const void* w_packed
                     void* workspace, void* stream);
 int lvc_patch_embed_launch_count(const lvc_embed_desc* d);
 
+/* lvc_patch_embed without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The bf16 patch matrix A[M][K] is written to a file-scope
+ * `static __device__` array of LVC_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it
+ * until the process exits); the entry point calls no cudaMalloc / cudaFree / allocating library routine.
+ * Shapes whose lvc_patch_embed_workspace() exceeds LVC_STATIC_SCRATCH_BYTES return LVC_E_SHAPE (16 MiB holds one
+ * clip of every configured model: ViViT 32x224x224 = 9.6 MB, TimeSformer 8x224x224 = 2.4 MB, Swin-B 32x224x224 =
+ * 9.6 MB).  All calls on a device share the one array: it keeps the previous call's contents (nothing needs clearing,
+ * the im2col pass overwrites every element the GEMM reads), and two calls that overlap on the GPU (different streams,
+ * or graphs replayed concurrently) RACE -- serialise them on one stream.  Other arguments and results are exactly
+ * lvc_patch_embed's (same kernels). */
+#define LVC_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
+int64_t lvc_patch_embed_static_capacity(void);
+int lvc_patch_embed_static(const lvc_embed_desc* d, const void* x, const void* w_packed_bf16,
+                           const float* bias, const float* ln_w, const float* ln_b, void* out, void* stream);
+
 /* The step after the patch embedding, fused into the GEMM epilogue:
  *   VIVIT        VivitEmbeddings.forward (transformers modeling_vivit.py:141-155): cat(cls_token, patches) +
  *                position_embeddings -> out (B, 1 + T/2*14*14, E)
