@@ -66,7 +66,7 @@ struct StageHdr {
   unsigned long long cstride;  // channel stride in elements
   unsigned rowmul;             // planar layouts: elements per output row; tokens: Wo*K (per patch row)
   int clip;                    // b = frame / T (stats slot)
-  int pad_[2];
+  double xscale;               // cv::resize column scale of the item's window (two double divisions, done once by the producer)
   unsigned roff[kMaxRPS];      // element offset of each output row of the stage inside the frame
   RowDesc rows[kMaxRPS];
 };
@@ -354,7 +354,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
         if (flags & 1) { xo = 6 * x; a0 = 32; a1 = 32; }
         else {
           int sx; float fr;
-          cv_tap(x, cv_scale(sw), sx, fr);
+          cv_tap(x, h->xscale, sx, fr);
           if (sx < 0) { sx = 0; fr = 0.f; }
           if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }   // clamped edge: a1 == 0, the bytes read at +3 do not matter
           a0 = coef(__fsub_rn(1.0f, fr));
@@ -552,7 +552,7 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
         if (flags & 1) { xo = 6 * x; a0 = 32; a1 = 32; }   // exact 2x2: INTER_AREA as the same fixed-point blend
         else {
           int sx; float fr;
-          cv_tap(x, cv_scale(sw), sx, fr);
+          cv_tap(x, h->xscale, sx, fr);
           if (sx < 0) { sx = 0; fr = 0.f; }
           if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }
           a0 = coef(__fsub_rn(1.0f, fr));
@@ -785,6 +785,7 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
       }
       const bool area = MODE != MODE_PTV && (sw == 2 * S) && (sh == 2 * S);
       const double scale_y = cv_scale(sh);
+      const double scale_x = MODE == MODE_PTV ? 0.0 : cv_scale(sw);   // consumers' column taps (header)
       const uint64_t row_bytes = (uint64_t)v.width * 3u;
       const bool full_width = MODE != MODE_PTV && ox == 0 && sw == v.width && env_merge;
       const uint64_t frame_base = v.base + (uint64_t)idx * (uint64_t)v.height * row_bytes;
@@ -882,7 +883,7 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
           h->frame = f; h->sw = (MODE == MODE_PTV) ? v.width : sw; h->oy0 = oy_first;
           h->flags = (area ? 1 : 0) | (flip << 1) | (bad ? 4 : 0);
           h->ox = ox; h->nw = (MODE == MODE_VIVIT) ? own_hi : nw; h->left = left; h->rlo = rlo;
-          h->obase = fo.base; h->cstride = fo.cstride; h->rowmul = fo.rowmul; h->clip = b;
+          h->obase = fo.base; h->cstride = fo.cstride; h->rowmul = fo.rowmul; h->clip = b; h->xscale = scale_x;
         }
         if (leader && bulk_bytes < my_bytes) {
           // last bytes of the buffer: not a whole 16-byte granule, copy them by hand
@@ -986,7 +987,7 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
         if (flags & 1) { xo = 6 * x; d1 = 3; a0 = 32; a1 = 32; }
         else {
           int sx; float fr;
-          if (p.f32src) cv_tap64(x, cv_scale(sw), sx, fr); else cv_tap(x, cv_scale(sw), sx, fr);
+          if (p.f32src) cv_tap64(x, h->xscale, sx, fr); else cv_tap(x, h->xscale, sx, fr);
           if (sx < 0) { sx = 0; fr = 0.f; }
           if (sx >= sw - 1) { sx = sw - 1; fr = 0.f; }
           a0 = coef(__fsub_rn(1.0f, fr));

@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 
@@ -17,7 +18,10 @@
 namespace {
 
 constexpr int kLbThreads = 256;
-constexpr int kLbRows = 16;       // output rows per block
+#ifndef LVC_LB_ROWS
+#define LVC_LB_ROWS 8
+#endif
+constexpr int kLbRows = LVC_LB_ROWS;        // output rows per work item (the grid is persistent: blocks walk the items round-robin)
 constexpr int kLbMaxW = 4096;     // widest resize target the tap table holds
 constexpr int kLbUnroll = 3;      // pixels per thread and pass (768 columns per pass)
 
@@ -39,9 +43,11 @@ struct LbParams {
   const uint8_t* frames;
   void* out;
   int n, out_bf16;
+  int row_blocks, items;   // items = n * row_blocks, item = frame * row_blocks + row block
+  int rows, pitch;         // staged kernel: output rows per item, bytes per source-row slot
 };
 
-__global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_constant__ LbParams p) {
+__global__ void __launch_bounds__(kLbThreads) lvc_letterbox_direct_kernel(const __grid_constant__ LbParams p) {
   __shared__ XTap xt[kLbMaxW];
   const lvc_letterbox_geom& g = p.g;
   const bool area = g.src_w == 2 * g.new_w && g.src_h == 2 * g.new_h;   // cv::resize switches to INTER_AREA
@@ -61,10 +67,17 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
   }
   // x / 255 for every uint8 value (IEEE division = what torch's CPU `im /= 255` computes), once per block
   __shared__ float s_div[256];
-  __shared__ int4 s_row[kLbRows];   // y0, y1, b0, b1 of the block's rows (y0 < 0: border row)
+  __shared__ int4 s_row[2][kLbRows];   // y0, y1, b0, b1 of the item's rows (y0 < 0: border row), double-buffered over items
   for (int i = threadIdx.x; i < 256; i += kLbThreads) s_div[i] = __fdiv_rn((float)i, 255.0f);
+  const uint8_t* frames_end = p.frames + (size_t)p.n * g.src_h * g.src_w * 3;
+  const size_t plane = (size_t)g.out_h * g.out_w;
+  // Persistent grid: the tables above are built once per block (they depend on the geometry only), the blocks then walk
+  // the (frame, row block) items round-robin -- one wave of resident blocks instead of 1.5 waves of 16-row blocks.
+  int buf = 0;
+  for (int item = blockIdx.x; item < p.items; item += gridDim.x, buf ^= 1) {
+  const int frame = item / p.row_blocks, rblk = item - frame * p.row_blocks;
   if (threadIdx.x < kLbRows) {
-    const int iy = blockIdx.x * kLbRows + threadIdx.x - g.top;
+    const int iy = rblk * kLbRows + threadIdx.x - g.top;
     int4 rt = make_int4(-1, 0, 0, 0);
     if (iy >= 0 && iy < g.new_h) {
       if (area) rt = make_int4(2 * iy, 2 * iy + 1, 0, 0);
@@ -75,18 +88,15 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
         rt = make_int4(min(max(sy, 0), g.src_h - 1), min(max(sy + 1, 0), g.src_h - 1), coef(__fsub_rn(1.0f, fr)), coef(fr));
       }
     }
-    s_row[threadIdx.x] = rt;
+    s_row[buf][threadIdx.x] = rt;
   }
-  __syncthreads();
-  const int frame = blockIdx.y;
+  __syncthreads();   // also publishes xt / s_div on the first trip; the other buffer is free (everyone passed the previous sync)
   const uint8_t* src = p.frames + (size_t)frame * g.src_h * g.src_w * 3;
-  const uint8_t* frames_end = p.frames + (size_t)p.n * g.src_h * g.src_w * 3;
-  const size_t plane = (size_t)g.out_h * g.out_w;
   const float pad = s_div[114];
   for (int r = 0; r < kLbRows; ++r) {
-    const int oy = blockIdx.x * kLbRows + r;
+    const int oy = rblk * kLbRows + r;
     if (oy >= g.out_h) break;
-    const int4 rt = s_row[r];
+    const int4 rt = s_row[buf][r];
     const bool row_in = rt.x >= 0;
     const int y0 = max(rt.x, 0), y1 = rt.y, b0 = rt.z, b1 = rt.w;
     const uint8_t* r0 = src + (size_t)y0 * g.src_w * 3;
@@ -146,6 +156,182 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
         }
       }
     }
+  }
+  }   // items
+}
+
+// ---- staged variant: the item's tapped source rows travel HBM -> shared memory as whole-row bulk copies (cp.async.bulk,
+// the TMA engine; SASS UBLKCP) on an mbarrier, double-buffered over items, and the taps are shared-memory word loads.
+// The direct kernel above issues 6 scattered 4-byte global loads per output pixel and is latency-bound at half the
+// copy rate; whole rows keep the memory system streaming (the clip kernel's ingest, csrc/lvc_clip.cu).
+__device__ __forceinline__ uint32_t lb_s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void lb_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(lb_s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void lb_mbar_expect(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(lb_s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void lb_mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(lb_s32(bar)), "r"(parity), "r"(0x989680u) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void lb_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(lb_s32(dst)), "l"(src), "r"(bytes), "r"(lb_s32(bar)) : "memory");
+}
+constexpr int kLbMaxRows = 8;   // output rows per item of the staged kernel (2 * rows source-row slots <= 16 lanes)
+
+// shared memory: [0,16) two mbarriers | s_div[256] | s_row[2][kLbMaxRows] (off0, off1, b0, b1; off0 < 0: border row) |
+// xt[new_w] | row slots [2][2 * rows][pitch] (16-byte aligned)
+__global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_constant__ LbParams p) {
+  extern __shared__ __align__(128) uint8_t lb_smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(lb_smem);
+  float* s_div = reinterpret_cast<float*>(lb_smem + 16);
+  int4* s_row = reinterpret_cast<int4*>(lb_smem + 16 + 1024);
+  XTap* xt = reinterpret_cast<XTap*>(lb_smem + 16 + 1024 + 2 * kLbMaxRows * 16);
+  const lvc_letterbox_geom& g = p.g;
+  uint8_t* slots = lb_smem + ((16 + 1024 + 2 * kLbMaxRows * 16 + (size_t)g.new_w * 8 + 127) & ~(size_t)127);
+  const int R = p.rows, nslot = 2 * R;
+  const bool area = g.src_w == 2 * g.new_w && g.src_h == 2 * g.new_h;   // cv::resize switches to INTER_AREA
+  const double sx_scale = cv_scale(g.src_w, g.new_w), sy_scale = cv_scale(g.src_h, g.new_h);
+  for (int x = threadIdx.x; x < g.new_w; x += kLbThreads) {
+    XTap t;
+    if (area) { t.off = 6 * x; t.a01 = 1 | (1 << 16); }
+    else {
+      int sx; float fr;
+      cv_tap(x, sx_scale, sx, fr);
+      if (sx < 0) { sx = 0; fr = 0.f; }
+      if (sx >= g.src_w - 1) { sx = g.src_w - 1; fr = 0.f; }   // clamped edge: a1 == 0, the slack bytes read at +3 weigh nothing
+      t.off = 3 * sx;
+      t.a01 = coef(__fsub_rn(1.0f, fr)) | (coef(fr) << 16);
+    }
+    xt[x] = t;
+  }
+  for (int i = threadIdx.x; i < 256; i += kLbThreads) s_div[i] = __fdiv_rn((float)i, 255.0f);
+  if (threadIdx.x == 0) {
+    lb_mbar_init(&full[0], 1);
+    lb_mbar_init(&full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const uint64_t row_bytes = (uint64_t)g.src_w * 3u;
+  const uint64_t buf_end = reinterpret_cast<uint64_t>(p.frames) + (uint64_t)p.n * g.src_h * row_bytes;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  // warp 0: lane j < 2R owns tap (j & 1) of output row j >> 1 of the item; duplicates inside the item are fetched once
+  auto issue = [&](int item, int b) {
+    const int frame = item / p.row_blocks, rblk = item - frame * p.row_blocks;
+    const unsigned lanes = nslot >= 32 ? 0xffffffffu : ((1u << nslot) - 1u);
+    uint32_t bulk_bytes = 0;
+    if (lane < nslot) {
+      const int r = lane >> 1, iy = rblk * R + r - g.top;
+      const bool row_in = iy >= 0 && iy < g.new_h && rblk * R + r < g.out_h;
+      int ysrc = -1 - lane, cb = 0;   // border rows: a distinct key per lane, nothing fetched
+      if (row_in) {
+        if (area) { ysrc = 2 * iy + (lane & 1); cb = 0; }
+        else {
+          int sy; float fr;
+          cv_tap(iy, sy_scale, sy, fr);
+          // cv::resize does not reset the fraction of clamped ROWS
+          ysrc = min(max(sy + (lane & 1), 0), g.src_h - 1);
+          cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
+        }
+      }
+      const unsigned same = __match_any_sync(lanes, ysrc);
+      const int lead = __ffs(same) - 1;
+      const uint64_t addr = reinterpret_cast<uint64_t>(p.frames) + ((uint64_t)frame * g.src_h + (uint64_t)max(ysrc, 0)) * row_bytes;
+      const uint64_t a = addr & ~(uint64_t)15;
+      const uint32_t shift = (uint32_t)(addr - a);
+      const uint32_t my_bytes = (shift + (uint32_t)row_bytes + 15u) & ~15u;   // <= pitch - 16 by construction
+      const int my_off = row_in ? (b * nslot + lead) * p.pitch + (int)shift : -1;
+      uint8_t* dst = slots + (size_t)(b * nslot + lane) * p.pitch;
+      if (row_in && lead == lane) {
+        bulk_bytes = my_bytes;
+        if (a + my_bytes > buf_end) {   // last bytes of the buffer: not a whole 16-byte granule, copied by hand
+          bulk_bytes = (uint32_t)((buf_end - a) & ~(uint64_t)15);
+          for (uint64_t q = a + bulk_bytes; q < buf_end; ++q) dst[q - a] = *reinterpret_cast<const uint8_t*>(q);
+        }
+      }
+      const int off_next = __shfl_down_sync(lanes, my_off, 1);
+      const int cb_next = __shfl_down_sync(lanes, cb, 1);
+      if (!(lane & 1)) s_row[b * kLbMaxRows + r] = make_int4(my_off, off_next, cb, cb_next);
+      uint32_t total = bulk_bytes;
+      // xor-reduction over the 2R active lanes (R is 1, 2, 4 or 8: 2R is a power of two, partners stay inside `lanes`)
+      for (int o = nslot >> 1; o; o >>= 1) total += __shfl_xor_sync(lanes, total, o);
+      __syncwarp(lanes);   // the row table and any hand-copied tail bytes are written before the barrier is armed
+      if (lane == 0) lb_mbar_expect(&full[b], total);
+      __syncwarp(lanes);
+      if (bulk_bytes) lb_bulk_g2s(dst, reinterpret_cast<const void*>(a), bulk_bytes, &full[b]);
+    }
+  };
+
+  const size_t plane = (size_t)g.out_h * g.out_w;
+  const float pad = s_div[114];
+  if (warp == 0 && (int)blockIdx.x < p.items) issue(blockIdx.x, 0);
+  uint32_t it = 0;
+  for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+    const int b = it & 1;
+    // the other buffer was read by the previous trip, which every thread has left (the barrier at the end of the trip)
+    if (warp == 0 && item + (int)gridDim.x < p.items) issue(item + gridDim.x, b ^ 1);
+    lb_mbar_wait(&full[b], (it >> 1) & 1u);
+    const int frame = item / p.row_blocks, rblk = item - frame * p.row_blocks;
+    for (int r = 0; r < R; ++r) {
+      const int oy = rblk * R + r;
+      if (oy >= g.out_h) break;
+      const int4 rt = s_row[b * kLbMaxRows + r];
+      const bool row_in = rt.x >= 0;
+      const uint32_t base0 = lb_s32(slots) + (uint32_t)max(rt.x, 0), base1 = lb_s32(slots) + (uint32_t)max(rt.y, 0);
+      const int b0 = rt.z, b1 = rt.w;
+      for (int ox0 = threadIdx.x; ox0 < g.out_w; ox0 += kLbThreads * kLbUnroll) {
+        uint32_t lo0[kLbUnroll], hi0[kLbUnroll], lo1[kLbUnroll], hi1[kLbUnroll], a01[kLbUnroll];
+        bool in[kLbUnroll];
+#pragma unroll
+        for (int u = 0; u < kLbUnroll; ++u) {
+          const int ox = ox0 + u * kLbThreads, ix = ox - g.left;
+          in[u] = row_in && ox < g.out_w && ix >= 0 && ix < g.new_w;
+          lo0[u] = hi0[u] = lo1[u] = hi1[u] = a01[u] = 0u;
+          if (!in[u]) continue;
+          const XTap t = xt[ix];
+          a01[u] = (uint32_t)t.a01;
+          const uint32_t q0 = base0 + (uint32_t)t.off, q1 = base1 + (uint32_t)t.off;
+          uint32_t a, bq, cq, d, e, fq;
+          asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+                       : "=r"(a), "=r"(bq), "=r"(cq) : "r"(q0 & ~3u));
+          asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+                       : "=r"(d), "=r"(e), "=r"(fq) : "r"(q1 & ~3u));
+          const uint32_t sh0 = (q0 & 3u) * 8u, sh1 = (q1 & 3u) * 8u;
+          lo0[u] = __funnelshift_r(a, bq, sh0); hi0[u] = __funnelshift_r(bq, cq, sh0);
+          lo1[u] = __funnelshift_r(d, e, sh1); hi1[u] = __funnelshift_r(e, fq, sh1);
+        }
+#pragma unroll
+        for (int u = 0; u < kLbUnroll; ++u) {
+          const int ox = ox0 + u * kLbThreads;
+          if (ox >= g.out_w) continue;
+          float v[3] = {pad, pad, pad};
+          if (in[u]) {
+            const uint32_t sel[3] = {0x4430u, 0x4441u, 0x4452u};   // (c of pixel 0, c of pixel 1) of the 8 bytes
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const int s0 = (int)__dp2a_lo(a01[u], __byte_perm(lo0[u], hi0[u], sel[c]), 0u);
+              const int s1 = (int)__dp2a_lo(a01[u], __byte_perm(lo1[u], hi1[u], sel[c]), 0u);
+              const int uu = area ? ((s0 + s1 + 2) >> 2) : ((((b0 * (s0 >> 4)) >> 16) + ((b1 * (s1 >> 4)) >> 16) + 2) >> 2);
+              v[c] = s_div[uu];
+            }
+          }
+          // transpose(2,0,1)[::-1]: output channel k is input channel 2 - k
+          const size_t e = (size_t)frame * 3 * plane + (size_t)oy * g.out_w + ox;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            if (p.out_bf16) reinterpret_cast<__nv_bfloat16*>(p.out)[e + k * plane] = __float2bfloat16_rn(v[2 - k]);
+            else __stcs(reinterpret_cast<float*>(p.out) + e + k * plane, v[2 - k]);
+          }
+        }
+      }
+    }
+    __syncthreads();   // buffer b (rows and s_row) may be refilled by the next trip's issue
   }
 }
 
@@ -240,8 +426,40 @@ extern "C" int lvc_letterbox_forward(const lvc_letterbox_geom* g, const uint8_t*
   if (g->new_w > kLbMaxW) return lvc_fail(LVC_E_SHAPE, "letterbox_forward: resize target wider than %d", kLbMaxW);
   LbParams p;
   p.g = *g; p.frames = frames; p.out = out; p.n = n; p.out_bf16 = out_dtype == LVC_DT_BF16;
-  dim3 grid((g->out_h + kLbRows - 1) / kLbRows, n);
-  lvc_letterbox_kernel<<<grid, kLbThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  int dev = 0, sms = 0, per_sm = 0, max_smem = 0;
+  LVC_CUDA_TRY(cudaGetDevice(&dev));
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  // staged kernel: the most rows per item (4, 2, 1) whose double-buffered row slots leave room for four blocks per SM
+  // (measured on B200, 64 frames: 1080p 2 rows 0.094 ms vs 4 rows 0.112, 8 rows 0.167; 480p 4 rows 0.108 vs 2 rows 0.116),
+  // else for two, else for one; frames too wide even for that take the direct-global kernel
+  p.pitch = ((g->src_w * 3 + 15 + 15) & ~15) + 16;
+  const size_t fixed = ((size_t)16 + 1024 + 2 * kLbMaxRows * 16 + (size_t)g->new_w * 8 + 127) & ~(size_t)127;
+  p.rows = 0;
+  const int forced_rows = lvc_knob_int("LVC_LB_STAGE_ROWS", -1);   // profiling knob (gated): 0 = direct kernel
+  for (int pass = 0; pass < 3 && !p.rows && forced_rows != 0; ++pass)
+    for (int r = forced_rows > 0 ? kLbMaxRows : 4; r >= 1; r >>= 1) {
+      if (forced_rows > 0 && r != forced_rows) continue;
+      const size_t need = fixed + (size_t)2 * 2 * r * p.pitch;
+      const size_t budget = pass == 0 ? (size_t)(max_smem / 4 - 1024) : (pass == 1 ? (size_t)(max_smem / 2 - 1024) : (size_t)max_smem);
+      if (need <= budget && (pass == 2 || r >= 2 || forced_rows > 0)) { p.rows = r; break; }
+    }
+  if (p.rows) {
+    const size_t smem = fixed + (size_t)2 * 2 * p.rows * p.pitch;
+    p.row_blocks = (g->out_h + p.rows - 1) / p.rows;
+    p.items = n * p.row_blocks;
+    LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_letterbox_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LVC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lvc_letterbox_kernel, kLbThreads, smem));
+    const int grid = std::min(p.items, sms * std::max(per_sm, 1));
+    lvc_letterbox_kernel<<<grid, kLbThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+    LVC_CUDA_TRY(cudaGetLastError());
+    return LVC_OK;
+  }
+  p.row_blocks = (g->out_h + kLbRows - 1) / kLbRows;
+  p.items = n * p.row_blocks;
+  LVC_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lvc_letterbox_direct_kernel, kLbThreads, 0));
+  const int grid = std::min(p.items, sms * std::max(per_sm, 1));
+  lvc_letterbox_direct_kernel<<<grid, kLbThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;
 }

@@ -51,6 +51,9 @@ if os.environ.get("CLIP_KNOBS_AB"):   # the consumer variants of round 2
     KNOBS = [{}, {"LVC_CLIP_NO_FMA": "1"}]
 if os.environ.get("CLIP_KNOBS_MATRIX"):   # producers x rows-per-stage
     KNOBS = [{"LVC_CLIP_NP": str(n), **({"LVC_CLIP_RPS": r} if r else {})} for n in (1, 2, 4) for r in ("", "4")]
+if os.environ.get("CLIP_KNOBS_JSON"):   # explicit list of knob dicts, e.g. '[{}, {"LVC_CLIP_SMEM_KB": "110"}]'
+    import json
+    KNOBS = json.loads(os.environ["CLIP_KNOBS_JSON"])
 for name in (sys.argv[1:] or ["swin_cfg4", "timesformer_cfg3", "vivit_cfg2"]):
     cb, batch, tok, vids = setup(name)
     for k in KNOBS:
