@@ -24,6 +24,21 @@ def test_letterbox_batch_matches_reference_preprocessing(hw):
     assert torch.equal(bf.cpu(), want.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize("hw", [(64, 20000), (2160, 3840), (1080, 1921), (31, 9001)])
+def test_letterbox_wide_and_odd_frames(hw):
+    """Rows too wide for the staged kernel's shared-memory slots take the direct-global kernel (20000 px = 60 KB per row,
+    eight slots do not fit); 4K rows get one block per SM; a width that is not a multiple of 16 bytes exercises the
+    aligned-superset bulk copies and the hand-copied tail of the last frame's last row."""
+    from lvc_b200 import yolo
+
+    h, w = hw
+    frames = np.random.default_rng(h * 7 + w).integers(0, 256, (2, h, w, 3), dtype=np.uint8)
+    im, g = yolo.letterbox_batch(torch.from_numpy(frames).cuda())
+    want = torch.cat([oy.preprocess(f) for f in frames])
+    assert tuple(im.shape) == tuple(want.shape)
+    assert torch.equal(im.cpu(), want)
+
+
 def test_scale_boxes_and_best_boxes_feed_the_clip_kernel():
     from lvc_b200 import ClipBuilder, yolo
     from oracle import processors as op
