@@ -483,6 +483,32 @@ def run_secondary(dev, iters=10):
                                   "path": "pinned host frames read by the kernel over PCIe (bulk copy per source row, crop region only)"}
     del hv, clip
     torch.cuda.empty_cache()
+    # detector pre-processing (row f4, src/yolo_detector.py:52-61): letterbox 640 + BGR->RGB + /255 + CHW of 64 1080p
+    # frames in one launch; HBM-bound on the sector-granular traffic (tapped source rows + fp32 output)
+    from lvc_b200 import yolo
+
+    n = 64
+    fr = torch.randint(0, 256, (n, h, w, 3), dtype=torch.uint8, device=dev, generator=g)
+    im, geo = yolo.letterbox_batch(fr)
+    ts = []
+    for _ in range(3 + iters):
+        l2_flush(flush)
+        torch.cuda._sleep(400000)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        yolo.letterbox_batch(fr, out=im)
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ms = statistics.median(ts[3:])
+    phys = n * (min(2 * geo.new_h, h) * w * 3 + im[0].numel() * 4)
+    out["letterbox_1080p"] = {"source": "yolov5 letterbox + BGR->RGB + /255 + CHW, 64 frames 1080p -> 384x640 fp32 (src/yolo_detector.py:52-61)",
+                              "kernel": "lvc_letterbox_kernel", "kernel_ms": ms, "frames_per_s": n / (ms * 1e-3),
+                              "roofline": {"bound": "hbm", "achieved": phys / ms / 1e6, "peak": hbm, "unit": "GB/s",
+                                           "frac": phys / ms / 1e6 / hbm,
+                                           "bytes": "tapped source rows (all sectors of a tapped row are touched at this scale) + fp32 output"}}
+    del fr, im
+    torch.cuda.empty_cache()
     return out
 
 
@@ -579,6 +605,10 @@ def compact_secondary(detail, ncu):
                                "e2e_clips_per_s": round(h.get("e2e", {}).get("clips_per_s", 0.0), 1)}
         if "cpu_reference" in h:
             out["hf_raw_1080p"]["cpu_clips_per_s"] = round(h["cpu_reference"]["clips_per_s"], 3)
+    if "letterbox_1080p" in detail:
+        lb = detail["letterbox_1080p"]
+        out["letterbox_1080p"] = {"kernel_ms": round(lb["kernel_ms"], 4), "frames_per_s": round(lb["frames_per_s"]),
+                                  "frac": round(lb["roofline"]["frac"], 3), "bound": "hbm"}
     return out
 
 
