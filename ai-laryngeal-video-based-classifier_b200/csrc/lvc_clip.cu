@@ -182,7 +182,8 @@ constexpr int kLut16Off = kLutOff + 3 * 256 * 4;    // the same table rounded to
 constexpr int kAuxOff = (kLut16Off + 3 * 256 * 2 + 127) / 128 * 128;
 constexpr int kRowBytes = S * 4;                    // one resized row, a 32-bit word (R | G<<8 | B<<16) per pixel
 constexpr int kVivitTapOff = kAuxOff;               // int4[224]: ymin, k0, k1, k2
-constexpr int kVivitRowBufOff = kVivitTapOff + S * 16;   // [group][parity][224 words]
+constexpr int kVivitRowPartOff = kVivitTapOff + S * 16;  // unsigned[224]: row term of the output offset (row_part) of every output row
+constexpr int kVivitRowBufOff = kVivitRowPartOff + S * 4;    // [group][parity][224 words]
 constexpr int kVivitInterOff = kVivitRowBufOff + groups_of(MODE_VIVIT) * 2 * kRowBytes;
 
 // Pillow BILINEAR 224 -> 256 taps for cropped output coordinate d (source coordinate d + 16 of the
@@ -515,6 +516,7 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
   const float* lut = reinterpret_cast<const float*>(smem + kLutOff);
   const __nv_bfloat16* lut16 = reinterpret_cast<const __nv_bfloat16*>(smem + kLut16Off);
   const int4* vt = reinterpret_cast<const int4*>(smem + kVivitTapOff);
+  const unsigned* rpart = reinterpret_cast<const unsigned*>(smem + kVivitRowPartOff);
   const int4 hx = vt[x];   // Pillow taps of this thread's (cropped) column: first source column, 22-bit weights
   const uint32_t hm0 = (uint32_t)hx.y >> 18, hm1 = (uint32_t)hx.z >> 18;   // ... which are m * 2^18 here: see pil16
   uint32_t* rbuf = reinterpret_cast<uint32_t*>(smem + kVivitRowBufOff) + g * 2 * S;   // [parity][S] per group
@@ -522,12 +524,12 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
   const uint32_t selA = p.bgr ? 0x4152u : 0x4130u, selB = p.bgr ? 0x4430u : 0x4452u;
   const unsigned xoff = col_offset(p, x);
   // output addressing of the layout: channel stride (elements) and the multiplier of row_part()
-  unsigned cs, rowmul;
+  unsigned cs;   // (the row term comes from the kernel prologue's table, rpart[])
   switch (p.layout) {
-    case LVC_LAYOUT_BTCHW: cs = S * S; rowmul = S; break;
-    case LVC_LAYOUT_BCTHW: cs = (unsigned)p.T * S * S; rowmul = S; break;
-    case LVC_LAYOUT_BTHWC: cs = 1; rowmul = S * 3; break;
-    default: cs = (unsigned)(p.kt * p.kh * p.kw); rowmul = (unsigned)(S / p.kw) * (unsigned)(3 * p.kt * p.kh * p.kw);
+    case LVC_LAYOUT_BTCHW: cs = S * S; break;
+    case LVC_LAYOUT_BCTHW: cs = (unsigned)p.T * S * S; break;
+    case LVC_LAYOUT_BTHWC: cs = 1; break;
+    default: cs = (unsigned)(p.kt * p.kh * p.kw);
   }
   int cached_sw = -1, cached_flags = -1;
   uint32_t xo_s = 0, a01 = 0;
@@ -606,7 +608,7 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
         constexpr int kOdt = decltype(ODTV)::value;   // 0 f32, 1 bf16 table, 2 u8, 3 bf16 affine
 #pragma unroll 2
         for (int y = ylo + g; y < ylo + p.rows_per_band; y += kGroups) {
-          const size_t eoff = (size_t)obase + (size_t)(row_part(p, rowmul, y) + xoff);
+          const size_t eoff = (size_t)obase + (size_t)(rpart[y] + xoff);
           const int4 ty = vt[y];
           const uint32_t* tp = inter + (ty.x - rlo) * S + x;
           const uint32_t pk = pil16(tp[0], tp[S], (uint32_t)ty.y >> 18, (uint32_t)ty.z >> 18);
@@ -682,6 +684,10 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
       reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = t;
       // the lean consumer's 4-bit form of the Pillow pass (pil16) needs two taps, multiples of 2^18, summing to 2^22
       if (((t.y | t.z) & 0x3ffff) || t.w || t.y + t.z != (1 << 22)) atomicOr(p.err, (unsigned)LVC_DEVERR_INTERNAL);
+      // row term of the output offset, once per kernel instead of once per thread and output row (warp-uniform arithmetic)
+      const unsigned rowmul = p.layout == LVC_LAYOUT_TOKENS ? (unsigned)(S / p.kw) * (unsigned)(3 * p.kt * p.kh * p.kw)
+                                                             : (p.layout == LVC_LAYOUT_BTHWC ? S * 3 : S);
+      reinterpret_cast<unsigned*>(smem + kVivitRowPartOff)[i] = row_part(p, rowmul, i);
     }
   if (MODE == MODE_CV2 && ODT >= 0 && ODT != LVC_DT_U8 && !STATS && p.lut) {
     // table of the lean consumer: entry t = LUT[(t + 2) >> 2], t = unrounded sum of the two vertical terms (<= 1020)

@@ -61,6 +61,12 @@ class PinnedRing:
         self.high_water = max(self.high_water, sum(e - s for s, e, _ in self.live))
         return self.buf[start:start + nbytes]
 
+    def release_last(self):
+        """Give back the most recent allocation (nothing will ever be fenced behind it: the decode that asked for it failed)."""
+        if self.live and self.live[-1][2] is None:
+            start, _, _ = self.live.pop()
+            self.head = start
+
     def fence(self, event):
         self.live = collections.deque((s, e, ev if ev is not None else event) for s, e, ev in self.live)
         while self.live and self.live[0][2] is not None and self.live[0][2].query():
@@ -157,6 +163,49 @@ class OpenCVFrameSource(FrameSource):
                 self.placeholders += 1
         cap.release()
         return frames, remap.astype(np.int32)
+
+    # -- sequential decode: data_handling.py:12-38 / vivit_transformer/inference.py:81-103 (read_video_pyav) -----------
+    def read_frames_sequential(self, i, indices):
+        """The frame SELECTION of the reference's PyAV reader: rewind, decode from frame 0 in order, keep frame ``k`` when
+        ``indices[0] <= k <= indices[-1]`` and ``k in indices`` -- each frame once however often it is listed, so a list
+        with repeats yields fewer frames than entries (the reference's ``np.stack`` has that shape too) -- and stop after
+        ``indices[-1]``.  No seek (robust on streams whose seek lands on key frames only); frames between the samples
+        are ``grab()``-bed (demuxed + decoded by the codec, never converted or copied), the kept ones land in the pinned
+        ring as decoded.  Returns ``(frames, kept)``: pinned uint8 ``(K, H, W, 3)`` and the K frame numbers, ascending.
+        The reader's ``frame.reformat(width=224, height=224)`` (libswscale) is NOT applied here: resizing is the clip
+        kernel's job with the cv2 arithmetic of the Dataset path; raises ValueError("No frames were extracted!") like
+        the reference when nothing is kept."""
+        import cv2
+
+        total, _, w, h = self.properties(i)
+        idx = [int(v) for v in indices]
+        if not idx:
+            raise ValueError("No frames were extracted!")
+        start, end = idx[0], idx[-1]
+        wanted = sorted({k for k in idx if start <= k <= end and 0 <= k < max(total, end + 1)})
+        frames = self.ring.alloc(max(len(wanted), 1) * h * w * 3)
+        dst = frames.narrow(0, 0, len(wanted) * h * w * 3).view(len(wanted), h, w, 3).numpy() if wanted else None
+        cap = cv2.VideoCapture(self.video_paths[i])
+        if not cap.isOpened():
+            self.ring.release_last()
+            raise ValueError(f"Could not open video: {self.video_paths[i]}")
+        kept, want_set = [], set(wanted)
+        for k in range(end + 1):
+            if not cap.grab():           # the stream ended before indices[-1]: the reference's loop ends there too
+                break
+            self.grabbed_frames += 1
+            if k in want_set:
+                ok, fr = cap.retrieve()
+                if not ok or fr.shape != (h, w, 3):
+                    break
+                dst[len(kept)] = fr if self.channel_order == "BGR" else cv2.cvtColor(fr, cv2.COLOR_BGR2RGB)
+                kept.append(k)
+                self.decoded_frames += 1
+        cap.release()
+        if not kept:
+            self.ring.release_last()
+            raise ValueError("No frames were extracted!")
+        return frames.narrow(0, 0, len(kept) * h * w * 3).view(len(kept), h, w, 3), np.asarray(kept, dtype=np.int64)
 
     def fence(self, event):
         """Tell the ring which event the frames handed out so far are read behind."""

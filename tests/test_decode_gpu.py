@@ -170,3 +170,39 @@ def test_seek_failure_falls_back_to_grab_then_placeholder(tmp_path, monkeypatch)
     src = OpenCVFrameSource(paths[:1])
     fr, _ = src.read_frames(0, [3])
     assert src.placeholders == 1 and bool((fr == 127).all())
+
+
+def test_sequential_reader_keeps_the_frames_the_pyav_reader_keeps(tmp_path):
+    """read_frames_sequential mirrors the frame selection of read_video_pyav (data_handling.py:12-38): decode in order
+    from frame 0, keep k when indices[0] <= k <= indices[-1] and k in indices (once each), stop after indices[-1]."""
+    import cv2
+
+    from lvc_b200 import ClipBuilder
+    from lvc_b200.decode import OpenCVFrameSource
+
+    paths = _write_tree(tmp_path, n_frames=30)
+    src = OpenCVFrameSource(paths, [1, 1, 0])
+    indices = [4, 4, 9, 10, 17, 17, 21]                      # repeats: the reference's np.stack holds 5 frames, not 7
+    frames, kept = src.read_frames_sequential(0, indices)
+    assert kept.tolist() == [4, 9, 10, 17, 21] and tuple(frames.shape) == (5, 120, 160, 3) and frames.is_pinned()
+    assert src.decoded_frames == 5 and src.grabbed_frames == 22 and src.seeks == 0     # frames 0..21 demuxed, 5 converted
+    cap = cv2.VideoCapture(paths[0])                          # the reference's loop, with cv2 standing in for PyAV
+    want = []
+    for k in range(indices[-1] + 1):
+        ok, fr = cap.read()
+        assert ok
+        if k >= indices[0] and k in indices:
+            want.append(fr)
+    cap.release()
+    assert np.array_equal(frames.numpy(), np.stack(want))
+    # ... and they feed the clip kernel in place (BGR as decoded, swapped in the gather)
+    clip = ClipBuilder("dataset_u8", num_frames=5, src_order="BGR").build_from_host([frames], [list(range(5))])
+    torch.cuda.synchronize()
+    ref = np.stack([cv2.resize(cv2.cvtColor(f, cv2.COLOR_BGR2RGB), (224, 224)) for f in want])
+    assert np.array_equal(clip[0].cpu().numpy(), ref)
+    # a list that starts past the end of the stream keeps nothing: the reference raises
+    with pytest.raises(ValueError, match="No frames were extracted"):
+        src.read_frames_sequential(0, [40, 45])
+    # indices[-1] bounds the scan: out-of-order lists drop what lies outside [indices[0], indices[-1]]
+    _, kept = src.read_frames_sequential(1, [10, 3, 25, 12])
+    assert kept.tolist() == [10, 12]
