@@ -16,6 +16,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstddef>
 #include <cstdint>
 #include <cstdlib>
 #include <type_traits>
@@ -51,7 +52,7 @@ struct RowDesc {  // one output row of a stage
   int off0, off1; // byte offsets in the ring of source pixel (x_origin, y0) / (x_origin, y1)
   int b0, b1;     // 11-bit vertical coefficients
 };
-struct StageHdr {
+struct alignas(16) StageHdr {   // (the lean consumers read the leading words as int4: keep their order)
   int frame;      // output frame id b*T + t
   int sw;         // source window width (pixels); PTV: full frame width
   int oy0;        // first output row of this stage
@@ -70,6 +71,8 @@ struct StageHdr {
   unsigned roff[kMaxRPS];      // element offset of each output row of the stage inside the frame
   RowDesc rows[kMaxRPS];
 };
+static_assert(sizeof(StageHdr) % 16 == 0 && offsetof(StageHdr, flags) == 12 && offsetof(StageHdr, ox) == 16 && offsetof(StageHdr, rlo) == 28,
+              "lean consumers load the header's leading words as two int4");
 struct ClipParams {
   const lvc_video* videos;
   const int32_t* indices;
@@ -346,7 +349,8 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
       mbar_wait(&full[slot], phase);
       if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();
       const StageHdr* h = &hdrs[slot];
-      const int sw = h->sw, flags = h->flags;
+      const int4 h0 = reinterpret_cast<const int4*>(h)[0];   // (frame, sw, oy0, flags) in one 16-byte load
+      const int sw = h0.y, flags = h0.w;
       if (sw != cached_sw || flags != cached_flags) {
         cached_sw = sw; cached_flags = flags;
         // exact 2x2 (INTER_AREA): a0 = a1 = 32 and b0 = b1 = 2^31 turn the fixed-point blend into
@@ -547,7 +551,9 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
       mbar_wait(&full[slot], phase);
       if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();
       const StageHdr* h = &hdrs[slot];
-      const int sw = h->sw, flags = h->flags;
+      // the eight leading header words as two 16-byte loads: (frame, sw, oy0, flags), (ox, own_hi, left, rlo)
+      const int4 h0 = reinterpret_cast<const int4*>(h)[0], h1 = reinterpret_cast<const int4*>(h)[1];
+      const int sw = h0.y, flags = h0.w;
       if (sw != cached_sw || flags != cached_flags) {
         cached_sw = sw; cached_flags = flags;
         int xo, a0, a1;
@@ -578,7 +584,7 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
       if (st == 0) obase = h->obase;
       if (flags & 4) item_bad = true;   // nothing was fetched for this item (contract violation, flagged by the producer)
       else {
-        const int oy0 = h->oy0, rlo = h->rlo, own_hi = h->nw;
+        const int oy0 = h0.z, rlo = h1.w, own_hi = h1.y;
         unsigned acc32 = 0;
         for (int r = g; r < p.rps; r += kGroups) {
           const RowDesc rd = h->rows[r];
