@@ -105,6 +105,10 @@ _OPTIONAL_SIGS = {
     "lvc_patch_embed_static_capacity": (C.c_int64, []),
     "lvc_patch_embed_static": (C.c_int, [C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lvc_clip_swin_embed_workspace": (C.c_int, [C.POINTER(EmbedDesc), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "lvc_clip_swin_embed_forward": (C.c_int, [C.POINTER(ClipDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.POINTER(EmbedDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lvc_letterbox_geometry": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                          C.POINTER(LetterboxGeom)]),
     "lvc_letterbox_forward": (C.c_int, [C.POINTER(LetterboxGeom), C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),

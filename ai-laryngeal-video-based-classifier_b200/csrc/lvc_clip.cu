@@ -44,7 +44,10 @@ __host__ __device__ constexpr int groups_of(int mode) { return mode == MODE_VIVI
 #define LVC_CLIP_PRODUCERS 4
 #endif
 constexpr int kProducers = LVC_CLIP_PRODUCERS;
-__host__ __device__ constexpr int threads_of(int mode) { return 32 * kProducers + groups_of(mode) * S; }
+__host__ __device__ constexpr int threads_of(int mode, int producers = kProducers) { return 32 * producers + groups_of(mode) * S; }
+// The variant that shares its SM with the patch-embedding kernel (lvc_clip_swin_embed_forward) runs two producer warps:
+// on ROI batches two are as good as four (cfg 4: 91 vs 90 us) and 64 fewer threads are 5.6 K registers for the neighbour.
+constexpr int kProducersFused = 2;
 constexpr int kMaxRPS = 16;               // output rows per stage (2*RPS source-row slots <= 32 lanes)
 constexpr int kMaxStages = 16;
 
@@ -91,6 +94,9 @@ struct ClipParams {
   int ring_bytes;            // size of the byte-granular source-row ring
   int lut4_off;              // lean cv2 consumer: byte offset of the 3 x 1024 table indexed by the unrounded vertical sum
   int no_fma;                // profiling knob LVC_CLIP_NO_FMA: keep the bf16 look-up even when the affine form verifies
+  unsigned* tile_ready;      // fused patch embedding: counters of token-row slices written per tile of A, else NULL
+  int tile_shift;            // log2(tokens per tile)
+  unsigned long long* tile_stamps;   // fused patch embedding: CTA 0 stamps its start / end here (timeline of the pair)
   unsigned* err;             // device error word (LVC_DEVERR_*), never NULL
   unsigned long long* fetched;  // device counter: bytes the producers requested from the source buffers (bulk copies)
   unsigned long long* trace;    // profiling (LVC_CLIP_TRACE=1 under the knob gate): CTA 0 logs 4 timestamps per stage, else NULL
@@ -313,7 +319,7 @@ template <int ODT, bool STATS>
 __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* smem, uint64_t* full, uint64_t* empty,
                                                   const StageHdr* hdrs, const int ct, const int lane, const bool use_fma,
                                                   const float (&fa)[3], const float (&fb)[3]) {
-  constexpr int kGroups = groups_of(MODE_CV2);
+  constexpr int kGroups = groups_of(MODE_CV2), kConsumers = kGroups * S;
   constexpr int kEsz = ODT == LVC_DT_F32 ? 4 : (ODT == LVC_DT_BF16 ? 2 : 1);
   constexpr bool kT4 = !STATS && ODT != LVC_DT_U8;   // table indexed by the unrounded vertical sum
   const int g = ct / S, x = ct - g * S;
@@ -464,6 +470,27 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
       if (lane == 0) mbar_arrive(&empty[slot]);
       if (tr) p.trace[cn * 4 + 3] = globaltimer_ns();
     }
+    if (ODT == LVC_DT_BF16 && p.tile_ready) {
+      // Fused patch embedding: tell the GEMM kernel running beside this one which tokens gained their rows.  The item's
+      // band of R output rows of frame f (R % kh == 0) holds, for the (R / kh) * Wo consecutive tokens starting at
+      // (f / kt * Ho + y0 / kh) * Wo, the kh row slices of tubelet frame f % kt: every tile the range overlaps gets
+      // overlap * kh.  Once per item, not per stage: the release needs a gpu-scope fence behind ALL of the CTA's stores,
+      // which is worth a microsecond.  Order: stores -> consumer barrier (CTA scope) -> fence (gpu scope, cumulative) -> red.
+      consumers_bar(kConsumers);
+      if (ct == 0) {
+        const unsigned Wo = (unsigned)(S / p.kw), Ho = (unsigned)(S / p.kh), tile = 1u << p.tile_shift;
+        const unsigned f = (unsigned)item / (unsigned)p.bands, band = (unsigned)item - f * (unsigned)p.bands;
+        const unsigned y0 = band * (unsigned)p.rows_per_band;
+        unsigned tok = ((f / (unsigned)p.kt) * Ho + y0 / (unsigned)p.kh) * Wo;
+        unsigned left = ((unsigned)p.rows_per_band / (unsigned)p.kh) * Wo;
+        __threadfence();
+        while (left) {
+          const unsigned n = min(left, tile - (tok & (tile - 1u)));
+          asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p.tile_ready + (tok >> p.tile_shift)), "r"(n * (unsigned)p.kh) : "memory");
+          tok += n; left -= n;
+        }
+      }
+    }
   }
   if (STATS && p.stats && acc_b >= 0) {
 #pragma unroll
@@ -471,6 +498,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
     if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
   }
   if (p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();   // consumer warp 0 done
+  if (p.tile_stamps && ct == 0 && blockIdx.x == 0) p.tile_stamps[1] = globaltimer_ns();
 }
 
 // ---- lean consumer of the ViViT preset ---------------------------------------------------------------------------------
@@ -652,9 +680,12 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
 }
 
 // ODT: compile-time output type of the lean cv2 consumer (LVC_DT_*), or -1 = the general consumer (type from the descriptor)
-template <int MODE, int ODT, bool STATS>
-__global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LVC_CLIP_MINBLOCKS)) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
-  constexpr int kGroups = groups_of(MODE), kConsumers = kGroups * S, kThreads = threads_of(MODE);
+template <int MODE, int ODT, bool STATS, int NPW = kProducers>   // NPW: producer warps the CTA is built with
+// (The variant that shares its SM declares a bound of 736 threads -- it is launched with 512 -- to cap it at 88 registers:
+// registers are allocated per FOUR warps, so the neighbour's 6 warps cost 8 x 32 x 80 = 20 480 and 16 x 32 x 88 = 45 056
+// is what is left of the 65 536.)
+__global__ void __launch_bounds__(NPW == kProducers ? threads_of(MODE, NPW) : 736, (MODE == MODE_VIVIT ? 1 : LVC_CLIP_MINBLOCKS)) lvc_clip_kernel(const __grid_constant__ ClipParams p) {
+  constexpr int kGroups = groups_of(MODE), kConsumers = kGroups * S, kThreads = threads_of(MODE, NPW);
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty = full + kMaxStages;
@@ -668,6 +699,7 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int tid = threadIdx.x;
   if (p.trace && tid == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2] = globaltimer_ns();   // CTA start
+  if (p.tile_stamps && tid == 0 && blockIdx.x == 0) p.tile_stamps[0] = globaltimer_ns();
   const int warp = tid >> 5, lane = tid & 31;
   const int stages_per_item = MODE == MODE_VIVIT ? p.v_stages : p.rows_per_band / p.rps;
 
@@ -727,7 +759,7 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
     use_fma = __syncthreads_and(ok) != 0;
   }
 
-  if (warp < kProducers) {
+  if (warp < NPW) {
     // ================= producer warps: lane j fetches source row (j&1 ? y1 : y0) of output row j>>1
     // No more active producers than ring slots: a warp that finished stage n has seen stage n - np - stages consumed;
     // its parity wait on the slot of stage n is unambiguous only if stage n - 2*stages is consumed too (np <= stages).
@@ -917,7 +949,7 @@ __global__ void __launch_bounds__(threads_of(MODE), (MODE == MODE_VIVIT ? 1 : LV
   }
 
   // ================= consumer warps: thread -> output column x, group -> rows g, g+G, ...
-  const int ct = tid - 32 * kProducers;
+  const int ct = tid - 32 * NPW;
   if constexpr (MODE == MODE_CV2 && ODT >= 0) {
     lean_cv2_consumer<ODT, STATS>(p, smem, full, empty, hdrs, ct, lane, use_fma, fa, fb);
     return;
@@ -1190,10 +1222,12 @@ __device__ unsigned g_dev_error;
 // Bytes the clip kernels' producers fetched from the source buffers since the last read: lvc_device_bytes_fetched()
 __device__ unsigned long long g_bytes_fetched;
 
-template <int MODE, int ODT = -1, bool STATS = true>
+template <int MODE, int ODT = -1, bool STATS = true, int NPW = kProducers>
 int launch(const ClipParams& p, int grid, size_t smem, cudaStream_t st) {
-  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE, ODT, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lvc_clip_kernel<MODE, ODT, STATS><<<grid, threads_of(MODE), smem, st>>>(p);
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE, ODT, STATS, NPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (NPW != kProducers)   // the variant that shares its SM: the L1 / shared split must leave room for the neighbour's CTA
+    LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_clip_kernel<MODE, ODT, STATS, NPW>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+  lvc_clip_kernel<MODE, ODT, STATS, NPW><<<grid, threads_of(MODE, NPW), smem, st>>>(p);
   LVC_CUDA_TRY(cudaGetLastError());
   return LVC_OK;
 }
@@ -1229,14 +1263,16 @@ int check_desc(const lvc_clip_desc* d, bool boxes, bool aug, bool lut) {
 
 // Launch geometry for a descriptor on a device with `sms` SMs and `max_smem` bytes of opt-in shared memory per CTA.
 // Pure host arithmetic (lvc_clip_plan_query runs it without a device).
-int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_smem, ClipParams& p, size_t& smem, int& grid) {
+int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_smem, ClipParams& p, size_t& smem, int& grid,
+              int smem_cap = 0, int built_producers = kProducers) {
   const bool ptv = d->resample == LVC_RESAMPLE_PTV_EVAL;
   const int mode = d->resample == LVC_RESAMPLE_CV2 ? MODE_CV2 : (ptv ? MODE_PTV : MODE_VIVIT);
   // row slot of the widest video: window bytes + alignment slack, rounded to 16 (+16 to stagger banks)
   p.pitch = ((d->max_width * 3 + 15 + 15) & ~15) + 16;
   // the whole opt-in shared memory of the SM (227 KB on B200): the kernel keeps next to nothing in L1, and the ViViT preset --
   // whose Pillow intermediate takes 50-60 KB -- gains a fifth ring stage (cfg 2: 133 -> 121 us); LVC_CLIP_SMEM_KB narrows it
-  const int budget_all = std::min(max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", max_smem / 1024 + 1) * 1024, 96 * 1024));
+  int budget_all = std::min(max_smem, std::max(env_int("LVC_CLIP_SMEM_KB", max_smem / 1024 + 1) * 1024, 96 * 1024));
+  if (smem_cap > 0) budget_all = std::min(budget_all, smem_cap);   // the SM is shared with another kernel (fused patch embedding)
   // MODE_VIVIT: the Pillow stage needs its vertical window on chip.  A band of R output rows spans at most
   // floor((R-1)*7/8) + 4 resized rows (halo included); pick the band count that minimises rounds x rows per
   // item (whole frames when the batch is large enough that quantisation does not matter) AMONG the candidates whose
@@ -1295,9 +1331,9 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
   smem = (size_t)fixed + (size_t)p.ring_bytes;
   p.merge_rows = env_int("LVC_CLIP_MERGE", 1);
   p.no_fma = env_int("LVC_CLIP_NO_FMA", 0);
-  p.producers = std::max(1, std::min(kProducers, env_int("LVC_CLIP_NP", kProducers)));
+  p.producers = std::max(1, std::min(built_producers, env_int("LVC_CLIP_NP", built_producers)));
 
-  const int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)max_smem / (smem + 1024)));
+  const int ctas_per_sm = smem_cap > 0 ? 1 : (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)max_smem / (smem + 1024)));
   const int grid_max = sms * ctas_per_sm;
   const int frames = d->batch * d->num_frames;
   // band = output rows per work item.  A CTA walks its items round-robin, and every item boundary costs about
@@ -1309,6 +1345,7 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
   long long band_cost = -1;
   for (int rb : kBands) {
     if (rb % p.rps) continue;
+    if (smem_cap > 0 && d->tok_kh > 0 && rb % d->tok_kh) continue;   // fused embedding: an item signals whole patch rows
     if (forced) { if (rb == forced) p.rows_per_band = rb; continue; }
     const long long items = (long long)frames * (S / rb);
     const long long cost = ((items + grid_max - 1) / grid_max) * (rb + 4);
@@ -1489,4 +1526,41 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   if (mode == MODE_VIVIT)
     return stats ? launch<MODE_VIVIT, -1, true>(p, grid, smem, st) : launch<MODE_VIVIT, -1, false>(p, grid, smem, st);
   return launch<MODE_PTV, -1, false>(p, grid, smem, st);
+}
+
+// Clip kernel for lvc_clip_swin_embed_forward (csrc/lvc_embed.cu): bf16 token layout, no checksum, two producer warps,
+// shared memory capped at `smem_cap` so that the patch-embedding kernel's CTA fits on the same SM, and per-tile ready
+// counters for that kernel (`tile_ready[t]` += token-row slices written into tile t of A; tiles of 1 << tile_shift tokens).
+int lvc_clip_forward_fused(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices, const int32_t* boxes,
+                           const float* lut, void* out, unsigned* tile_ready, int tile_shift, int smem_cap, void* stream) {
+  if (!d || !videos || !indices || !out || !tile_ready || !lut) return lvc_fail(LVC_E_INVAL, "clip_swin_embed: NULL argument");
+  if (int rc = check_desc(d, boxes != nullptr, false, true)) return rc;
+  if (d->resample != LVC_RESAMPLE_CV2 || d->layout != LVC_LAYOUT_TOKENS || d->out_dtype != LVC_DT_BF16 || d->src_float)
+    return lvc_fail(LVC_E_NOTSUP, "clip_swin_embed: the fused path is the cv2 chain on uint8 frames with the bf16 token layout");
+  if (boxes && (reinterpret_cast<uintptr_t>(boxes) & 15)) return lvc_fail(LVC_E_ALIGN, "clip_swin_embed: boxes must be 16-byte aligned");
+  const DeviceInfo& di = device_info();
+  if (di.err != cudaSuccess) return lvc_fail(LVC_E_CUDA, "clip_swin_embed: no usable CUDA device: %s", cudaGetErrorString(di.err));
+  ClipParams p{};
+  p.videos = videos; p.indices = indices; p.boxes = boxes; p.lut = lut; p.out = out;
+  p.T = d->num_frames; p.layout = d->layout; p.out_dtype = d->out_dtype;
+  p.kt = d->tok_kt; p.kh = d->tok_kh; p.kw = d->tok_kw;
+  p.bgr = d->src_order == LVC_SRC_BGR;
+  p.kh_shift = -1;
+  for (int sft = 0; sft < 8; ++sft) if (p.kh == (1 << sft)) p.kh_shift = sft;
+  p.tile_ready = tile_ready; p.tile_shift = tile_shift;
+  {
+    const long long tiles = ((long long)d->batch * (d->num_frames / d->tok_kt) * (S / d->tok_kh) * (S / d->tok_kw) + (1 << tile_shift) - 1) >> tile_shift;
+    p.tile_stamps = reinterpret_cast<unsigned long long*>(tile_ready + (tiles + 63) / 64 * 64);
+  }
+  p.err = lvc_dev_error_word();
+  if (!p.err) return lvc_fail(LVC_E_CUDA, "clip_swin_embed: cannot resolve the device error word");
+  {
+    unsigned long long* fptr = nullptr;
+    LVC_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&fptr), g_bytes_fetched));
+    p.fetched = fptr;
+  }
+  size_t smem = 0;
+  int grid = 0;
+  if (int rc = make_plan(d, boxes != nullptr, false, di.sms, std::min(di.max_smem, smem_cap), p, smem, grid, smem_cap, kProducersFused)) return rc;
+  return launch<MODE_CV2, LVC_DT_BF16, false, kProducersFused>(p, grid, smem, static_cast<cudaStream_t>(stream));
 }

@@ -315,6 +315,10 @@ struct GemmParams {
   const float* pos;    // [(1 + P)][N] position_embeddings
   const float* temb;   // [T][N] time_embeddings (mode 2, may be NULL = space_only)
   int emb_mode, emb_P, emb_T;
+  // fused clip -> embed (lvc_clip_swin_embed_forward): ready[tile] counts the token-row slices the clip kernel has
+  // written into tile `tile` of A; the TMA producer loads a tile once ready[tile] >= tokens in the tile x ready_need.  NULL = A is complete.
+  const unsigned* ready;
+  unsigned ready_need;
   const void* diag_a;  // A base pointer for the linear-copy experiment
   int diag;            // LVC_GEMM_DIAG (profiling only): 1 = no output stores, 2 = no MMAs, 4 = no TMA loads
   void* out;
@@ -815,15 +819,30 @@ lvc_embed_gemm2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_c
 // without re-reading TMEM, and rows leave through 128-byte-swizzled staging tiles and TMA stores.
 namespace {
 
-constexpr int kSwinGroups = 4;                           // epilogue warpgroups = TMEM accumulators
+constexpr int kSwinGroups = 4;                           // epilogue warpgroups = TMEM accumulators (stand-alone kernel)
 constexpr int kSwinThreads = 64 + kSwinGroups * 128;     // producer warp, MMA warp, 16 epilogue warps
+__host__ __device__ inline int num_tiles_of(const GemmParams& p) { return p.m_tiles; }
+constexpr int kSwinGroupsFused = 1;                      // the variant that shares its SM with the clip kernel: 6 warps
+__host__ __device__ constexpr int swin_threads(int ng) { return 64 + ng * 128; }
 
-template <int NCH, bool OUT_F32>  // N = 32 * NCH columns, kSwinGroups * N <= 512 TMEM columns
-__global__ void __launch_bounds__(kSwinThreads, 1)
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// NG = epilogue warpgroups = TMEM accumulators.  NG = 4: the stand-alone kernel (576 threads, the SM to itself).
+// NG = 1: 192 threads, 96 registers, ~110 KB of shared memory -- small enough to be CO-RESIDENT with the clip kernel
+// (lvc_clip_swin_embed_forward): it is launched behind the clip kernel with programmatic stream serialization, starts
+// while the clip kernel runs, and its producer loads a tile of A when the clip kernel's ready counter says the tile
+// is complete (p.ready).  It must then NOT execute griddepcontrol.wait (that would wait for the whole clip grid).
+template <int NCH, bool OUT_F32, int NG = kSwinGroups>  // N = 32 * NCH columns, NG * N <= 512 TMEM columns
+__global__ void __launch_bounds__(swin_threads(NG), (NG == kSwinGroupsFused ? 4 : 1))   // fused variant: <= 80 registers
 lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                       const __grid_constant__ CUtensorMap map_o, const __grid_constant__ GemmParams p) {
   constexpr int N = 32 * NCH;
-  constexpr int NG = kSwinGroups;
+  constexpr int kSwinThreads = swin_threads(NG);
+  constexpr int NA = NG == 1 ? 2 : NG;   // TMEM accumulators: one per epilogue group; the single-group variant ping-pongs two
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (s32(smem_raw) & 1023u)) & 1023u);
   const int span = p.BK * 2;
@@ -840,8 +859,8 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_a + (size_t)p.stages * a_bytes);
   uint64_t* empty = full + p.stages;
   uint64_t* tmem_full = empty + p.stages;
-  uint64_t* tmem_empty = tmem_full + NG;
-  uint64_t* b_full = tmem_empty + NG;
+  uint64_t* tmem_empty = tmem_full + NA;
+  uint64_t* b_full = tmem_empty + NA;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
   // parameters after the barriers, 16-byte aligned for float4 reads (barrier block is < 512 bytes)
   float* s_bias = reinterpret_cast<float*>(smem_a + (size_t)p.stages * a_bytes + 512);
@@ -852,12 +871,17 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_o);
     for (int s = 0; s < p.stages; ++s) { mb_init(&full[s], 1); mb_init(&empty[s], 1); }
-    for (int a = 0; a < NG; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
+    for (int a = 0; a < NA; ++a) { mb_init(&tmem_full[a], 1); mb_init(&tmem_empty[a], 4); }
     mb_init(b_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
-  griddep_wait();   // barrier set-up and the TMEM allocation overlap the previous kernel's tail; parameters do not
+  // barrier set-up and the TMEM allocation overlap the previous kernel's tail; parameters do not.  Gated on ready
+  // counters the kernel runs BESIDE its producer kernel: the counters, not grid completion, order the reads of A
+  // (bias / LayerNorm parameters and the weights were written before the producer kernel was launched).
+  if (!p.ready) griddep_wait();
+  unsigned long long* stamps = p.ready ? reinterpret_cast<unsigned long long*>(const_cast<unsigned*>(p.ready) + ((num_tiles_of(p) + 63) / 64) * 64) : nullptr;
+  if (stamps && blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); stamps[2] = t; }
   for (int i = threadIdx.x; i < N; i += kSwinThreads) {
     s_lnw[i] = p.do_ln ? p.ln_w[i] : 1.f;
     s_lnb[i] = p.do_ln ? p.ln_b[i] : 0.f;
@@ -892,6 +916,11 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         const int s = it % p.stages;
         mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
         if (p.diag & 4) { mb_arrive(&full[s]); continue; }
+        if (p.ready) {   // the clip kernel is still writing A: wait for this tile's token rows, then order the TMA read
+          const unsigned need = (unsigned)min(BM, p.M - tile * BM) * p.ready_need;   // the last tile may be partial
+          while (ld_acquire_gpu(p.ready + tile) < need) __nanosleep(200);
+          asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes (other SMs) -> async-proxy read
+        }
         mb_expect_tx(&full[s], a_bytes);
         if (p.diag & 128) {  // timing experiment: the tile as ONE linear bulk copy (layout is wrong for the MMA)
           const uint8_t* src = reinterpret_cast<const uint8_t*>(p.diag_a) + (size_t)tile * a_bytes;
@@ -910,7 +939,7 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
       mb_wait(b_full, 0);
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const uint32_t acc = it % NG, acc_phase = (it / NG) & 1u;
+        const uint32_t acc = it % NA, acc_phase = (it / NA) & 1u;
         const int s = it % p.stages;
         mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
         mb_wait(&full[s], (it / p.stages) & 1u);
@@ -938,13 +967,14 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       if ((int)(it % NG) != grp) continue;
-      if (p.diag & 256) mb_wait(&tmem_full[grp], (it / NG) & 1u); else mb_wait_backoff(&tmem_full[grp], (it / NG) & 1u);
+      const int acc = (int)(it % NA);   // == grp when every group owns an accumulator
+      if (p.diag & 256) mb_wait(&tmem_full[acc], (it / NA) & 1u); else mb_wait_backoff(&tmem_full[acc], (it / NA) & 1u);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * N);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * N);
       if (p.diag & 16) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mb_arrive(&tmem_empty[grp]);
+        if (lane == 0) mb_arrive(&tmem_empty[acc]);
         continue;
       }
       float v[2][32];
@@ -982,7 +1012,7 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         } else {   // accumulator fully read: the MMA issuer may overwrite it
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mb_arrive(&tmem_empty[grp]);
+          if (lane == 0) mb_arrive(&tmem_empty[acc]);
         }
         const int cc = c % CPF;
 #pragma unroll
@@ -1021,6 +1051,7 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   }
   tc_fence_before();
   __syncthreads();
+  if (stamps && blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); stamps[3] = t; }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
@@ -1273,6 +1304,15 @@ int patch_embed_impl(const lvc_embed_desc* d, const void* x, const void* w_packe
       rc = make_out_map(&mo, out, (uint64_t)g.M, (uint64_t)g.N, p.out_f32 != 0);
       if (rc != LVC_OK) return rc;
       const int grid3 = std::min(sms, p.m_tiles);
+      if (lvc_knob_set("LVC_SWIN_NG1")) {   // profiling: the 192-thread variant of the fused path, stand-alone and ungated
+        const int fixed1 = 1024 + 4 * kSwinGroupsFused * 4096 + b_all + (BM + g.N) * 64 + 512 + 3 * g.N * 4 + 64;
+        p.stages = env_i("LVC_FUSED_EMBED_STAGES", 2);
+        p.tmem_cols = 256;
+        const size_t smem1 = (size_t)fixed1 + (size_t)p.stages * a_tile;
+        LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, false, kSwinGroupsFused>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+        LVC_CUDA_TRY(launch_pdl(lvc_embed_swin_kernel<4, false, kSwinGroupsFused>, grid3, swin_threads(kSwinGroupsFused), smem1, st, ma, mb, mo, p));
+        return LVC_OK;
+      }
       p.tmem_cols = 512;  // kSwinGroups accumulators of N columns
       if (p.out_f32) {
         LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
@@ -1343,4 +1383,105 @@ extern "C" int lvc_patch_embed_static(const lvc_embed_desc* d, const void* x, co
   // Nothing has to start at zero: the im2col pass overwrites all M*K elements of A before the GEMM reads them, and the
   // tensor map is built on exactly M rows (rows past M are zero-filled by TMA, never read from the array).
   return patch_embed_impl(d, x, w_packed, bias, ln_w, ln_b, EmbTables{nullptr, nullptr, nullptr, 0}, out, scratch, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// lvc_clip_swin_embed_forward: the Video Swin pipeline (clip kernel -> PatchEmbed3d GEMM + LayerNorm) with the two
+// kernels CO-RESIDENT on every SM.  The clip stage of ROI batches is bound by its consumers' latency (half the issue
+// slots idle, 2 of 6.5 TB/s of DRAM) and the embedding is bound by HBM, so run in sequence they waste each other's
+// resource; side by side the embedding hides behind the clip stage.  Mechanics: (1) the clip kernel runs in a variant
+// with two producer warps and its shared memory capped so that a 192-thread / 80-register / 110 KB embedding CTA fits
+// on the same SM (64.5 K of 64 K... registers: 512 x 96 + 192 x 80); (2) it counts, per 128-token tile of A, the
+// token-row slices it has stored (red.release.gpu); (3) the embedding kernel is launched behind it with programmatic
+// stream serialization -- the clip kernel executes griddepcontrol.launch_dependents on entry, so the embedding grid
+// starts as soon as every clip CTA is resident -- and its TMA producer loads a tile when the tile's counter is complete
+// (ld.acquire.gpu + fence.proxy.async).  The clip kernel never waits for the embedding kernel, so if the two do not
+// fit together (another kernel holds the SM) the embedding simply runs afterwards: correctness does not depend on
+// co-residency.  A stays in L2 (77 MB of 126 MB) between the kernels' SMs.  Results are bit-identical to
+// lvc_clip_forward + lvc_patch_embed (same arithmetic in both kernels).
+extern "C" int lvc_clip_swin_embed_workspace(const lvc_embed_desc* ed, int64_t* tokens_bytes, int64_t* ready_bytes) {
+  EmbedGeom g;
+  if (!ed || !tokens_bytes || !ready_bytes) return lvc_fail(LVC_E_INVAL, "clip_swin_embed_workspace: NULL argument");
+  int rc = make_geom(ed, &g);
+  if (rc != LVC_OK) return rc;
+  *tokens_bytes = ((int64_t)g.M * g.K * 2 + 255) / 256 * 256;
+  // per-tile counters, then 256 bytes of timestamps (CTA 0 of either kernel: start / end, globaltimer ns) for scripts/perf_swin_fused.py
+  *ready_bytes = (((int64_t)g.M + BM - 1) / BM * 4 + 255) / 256 * 256 + 256;
+  return LVC_OK;
+}
+
+extern "C" int lvc_clip_swin_embed_forward(const lvc_clip_desc* cd, const lvc_video* videos, const int32_t* indices,
+                                           const int32_t* boxes, const float* lut, const lvc_embed_desc* ed,
+                                           const void* w_packed, const float* bias, const float* ln_w, const float* ln_b,
+                                           void* tokens, void* ready, void* out, void* stream) {
+  if (!cd || !ed || !videos || !indices || !lut || !w_packed || !bias || !ln_w || !ln_b || !tokens || !ready || !out)
+    return lvc_fail(LVC_E_INVAL, "clip_swin_embed: NULL argument");
+  EmbedGeom g;
+  int rc = make_geom(ed, &g);
+  if (rc != LVC_OK) return rc;
+  if (ed->kind != LVC_EMBED_SWIN || g.N != 128 || g.K > 256 || g.K % 32)
+    return lvc_fail(LVC_E_NOTSUP, "clip_swin_embed: Video Swin PatchEmbed3d shapes only (embed_dim 128, K <= 256)");
+  if (cd->layout != LVC_LAYOUT_TOKENS || cd->tok_kt != g.kt || cd->tok_kh != g.kh || cd->tok_kw != g.kw ||
+      cd->batch != ed->batch || cd->num_frames != ed->frames || ed->height != 224 || ed->width != 224)
+    return lvc_fail(LVC_E_SHAPE, "clip_swin_embed: the clip descriptor's token layout must be the embedding's patch (%d,%d,%d) on (B,T,224,224)", g.kt, g.kh, g.kw);
+  if (g.T % g.kt) return lvc_fail(LVC_E_SHAPE, "clip_swin_embed: T must divide by the tubelet");
+  if (ed->out_dtype != LVC_DT_F32 && ed->out_dtype != LVC_DT_BF16) return lvc_fail(LVC_E_INVAL, "clip_swin_embed: out_dtype must be f32 or bf16");
+  if ((reinterpret_cast<uintptr_t>(tokens) & 127) || (reinterpret_cast<uintptr_t>(w_packed) & 127) || (reinterpret_cast<uintptr_t>(out) & 15) ||
+      (reinterpret_cast<uintptr_t>(ready) & 3))
+    return lvc_fail(LVC_E_ALIGN, "clip_swin_embed: tokens / packed weights need 128-byte, out 16-byte alignment");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int dev = 0, sms = 0, max_smem = 0;
+  LVC_CUDA_TRY(cudaGetDevice(&dev));
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  LVC_CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+
+  GemmParams p{};
+  p.M = g.M; p.N = g.N; p.K = g.K;
+  p.BN = g.N;
+  p.BK = (g.K % 64 == 0) ? 64 : 32;
+  p.num_k_blocks = g.K / p.BK;
+  p.m_tiles = (g.M + BM - 1) / BM;
+  p.n_tiles = 1;
+  p.tmem_cols = 256;   // two accumulators of N columns (the one epilogue group ping-pongs)
+  p.bias = bias; p.ln_w = ln_w; p.ln_b = ln_b; p.ln_eps = ed->ln_eps;
+  p.do_ln = 1;
+  p.out_f32 = ed->out_dtype == LVC_DT_F32;
+  p.out = out;
+  p.ready = static_cast<const unsigned*>(ready);
+  p.ready_need = (unsigned)(g.kt * g.kh);   // per token: all kt * kh row slices (3 channels x kw columns each) are stored
+  const int a_tile = BM * g.K * 2, b_all = g.N * g.K * 2;
+  const int fixed3 = 1024 + 4 * kSwinGroupsFused * 4096 + b_all + (BM + g.N) * 64 + 512 + 3 * g.N * 4 + 64;
+  p.stages = env_i("LVC_FUSED_EMBED_STAGES", 2);
+  const size_t smem3 = (size_t)fixed3 + (size_t)p.stages * a_tile;
+  // what is left of the SM for the clip kernel: the opt-in maximum minus the embedding CTA and the per-CTA reserve
+  const int clip_cap = max_smem - (int)smem3 - 2048;
+  if (clip_cap < 64 * 1024) return lvc_fail(LVC_E_SHAPE, "clip_swin_embed: K = %d leaves the clip kernel %d bytes of shared memory", g.K, clip_cap);
+
+  const int tiles = p.m_tiles;
+  int tile_shift = 0;
+  while ((1 << tile_shift) < BM) ++tile_shift;
+  LVC_CUDA_TRY(cudaMemsetAsync(ready, 0, (size_t)tiles * 4, st));
+  rc = lvc_clip_forward_fused(cd, videos, indices, boxes, lut, tokens, static_cast<unsigned*>(ready), tile_shift, clip_cap, stream);
+  if (rc != LVC_OK) return rc;
+
+  if (lvc_knob_set("LVC_FUSED_NO_EMBED")) return LVC_OK;   // profiling: the clip half alone
+  CUtensorMap ma, mb, mo;
+  rc = make_map(&ma, tokens, (uint64_t)g.M, (uint64_t)g.K, (uint32_t)p.BK, BM);
+  if (rc != LVC_OK) return rc;
+  rc = make_map(&mb, w_packed, (uint64_t)g.N, (uint64_t)g.K, (uint32_t)p.BK, (uint32_t)g.N);
+  if (rc != LVC_OK) return rc;
+  rc = make_out_map(&mo, out, (uint64_t)g.M, (uint64_t)g.N, p.out_f32 != 0);
+  if (rc != LVC_OK) return rc;
+  const int grid3 = std::min(sms, tiles);
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, true, kSwinGroupsFused>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+  LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, false, kSwinGroupsFused>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+  if (p.out_f32) {
+    LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, true, kSwinGroupsFused>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+    LVC_CUDA_TRY(launch_pdl(lvc_embed_swin_kernel<4, true, kSwinGroupsFused>, grid3, swin_threads(kSwinGroupsFused), smem3, st, ma, mb, mo, p));
+  } else {
+    LVC_CUDA_TRY(cudaFuncSetAttribute(lvc_embed_swin_kernel<4, false, kSwinGroupsFused>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+    LVC_CUDA_TRY(launch_pdl(lvc_embed_swin_kernel<4, false, kSwinGroupsFused>, grid3, swin_threads(kSwinGroupsFused), smem3, st, ma, mb, mo, p));
+  }
+  LVC_CUDA_TRY(cudaGetLastError());
+  return LVC_OK;
 }

@@ -18,6 +18,10 @@ bool lvc_knob_set(const char* name);            // knob present (any value) and 
 // read by lvc_device_status.  NULL when no device is usable.
 unsigned* lvc_dev_error_word();
 
+// The clip kernel as the producer half of lvc_clip_swin_embed_forward (defined in lvc_clip.cu, used by lvc_embed.cu).
+int lvc_clip_forward_fused(const lvc_clip_desc* d, const lvc_video* videos, const int32_t* indices, const int32_t* boxes,
+                           const float* lut, void* out, unsigned* tile_ready, int tile_shift, int smem_cap, void* stream);
+
 #ifdef __CUDACC__
 #define LVC_CUDA_TRY(expr)                                                                  \
   do {                                                                                      \

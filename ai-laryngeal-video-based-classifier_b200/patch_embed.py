@@ -240,6 +240,66 @@ class PatchEmbed3d(_EmbedBase):
         return self._run(x, B, T, H, W, shape)
 
 
+    def forward_clips(self, clip_builder, batch, out=None):
+        """The whole Video Swin front end -- gather, ROI crop, cv2 resize, normalise (``clip_builder``, preset of the
+        cv2 chain with ``layout="TOKENS", patch=(2, 4, 4)``) and this module's Conv3d + LayerNorm -- as TWO CO-RESIDENT
+        kernels: the embedding kernel is launched behind the clip kernel with programmatic stream serialization and
+        consumes each 128-token tile of the patch matrix as soon as the clip kernel has completed it
+        (``lvc_clip_swin_embed_forward``).  ``batch = clip_builder.prepare(videos, indices, boxes)``.
+        Returns (B, T/2, 56, 56, embed_dim); bit-identical to ``self.forward_tokens(clip_builder.run(batch), ...)``."""
+        self._check_no_grad()
+        cb = clip_builder
+        d_clip = batch.desc
+        B, T = int(d_clip.batch), int(d_clip.num_frames)
+        kt, kh, kw = self.tuple_patch_size
+        if cb.layout != "TOKENS" or tuple(cb.patch) != (kt, kh, kw):
+            raise ValueError(f"the clip builder must write layout='TOKENS' with patch={(kt, kh, kw)}")
+        w, bias = self.proj.weight, self.proj.bias
+        dev = cb.device
+        if w.device != dev:
+            raise RuntimeError("module parameters and clip builder are on different devices")
+        with torch.no_grad():
+            lib = _lib.lib()
+            d = _lib.EmbedDesc(self.kind, _lib.DT_BF16, _lib.LAYOUT_TOKENS, _DT[self.out_dtype], B, T, 224, 224,
+                               kt, kh, kw, self.proj.out_channels, float(self.norm.eps), 0)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            key = (w.data_ptr(), w._version, tuple(w.shape))
+            if self._packed is None or self._packed_key != key:
+                self._packed = torch.empty(w.numel(), dtype=torch.bfloat16, device=dev)
+                _lib.check(lib.lvc_patch_embed_pack_weights(C.byref(d), self._fp32("weight", w).data_ptr(),
+                                                            self._packed.data_ptr(), stream), "pack_weights")
+                self._packed_key = key
+                self.launches += 1
+            tb, rb = C.c_int64(), C.c_int64()
+            _lib.check(lib.lvc_clip_swin_embed_workspace(C.byref(d), C.byref(tb), C.byref(rb)), "clip_swin_embed_workspace")
+            need = tb.value + rb.value
+            ws = getattr(self, "_fused_ws", None)
+            if ws is None or ws.numel() < need or ws.device != dev:
+                ws = self._fused_ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            shape = (B, T // kt, 224 // kh, 224 // kw, self.proj.out_channels)
+            if out is None:
+                out = torch.empty(shape, dtype=self.out_dtype, device=dev)
+            elif tuple(out.shape) != shape or out.dtype != self.out_dtype or not out.is_contiguous():
+                raise ValueError("out has the wrong shape, dtype or strides")
+            if bias is None:
+                if getattr(self, "_zero_bias", None) is None or self._zero_bias.device != dev:
+                    self._zero_bias = torch.zeros(self.proj.out_channels, device=dev)
+                bias = self._zero_bias
+            bias_f, lw_f, lb_f = self._fp32("bias", bias), self._fp32("ln_w", self.norm.weight), self._fp32("ln_b", self.norm.bias)
+            st = lib.lvc_clip_swin_embed_forward(C.byref(d_clip), batch.p_vid, batch.p_idx, batch.p_box, cb.lut.data_ptr(),
+                                                 C.byref(d), self._packed.data_ptr(), bias_f.data_ptr(), lw_f.data_ptr(),
+                                                 lb_f.data_ptr(), ws.data_ptr(), ws.data_ptr() + tb.value, out.data_ptr(), stream)
+            _lib.check(st, "lvc_clip_swin_embed_forward")
+            self.launches += 2
+        return out
+
+    def tokens_view(self, batch_size, frames):
+        """The bf16 patch matrix the last forward_clips call left in the module's workspace (tests, debugging)."""
+        kt, kh, kw = self.tuple_patch_size
+        M, K = batch_size * (frames // kt) * (224 // kh) * (224 // kw), 3 * kt * kh * kw
+        return self._fused_ws[:M * K * 2].view(torch.bfloat16).view(M, K)
+
+
 class VivitEmbeddings(nn.Module):
     """``transformers`` ``VivitEmbeddings`` (modeling_vivit.py:141-155): tubelet embedding, cls token and position
     embeddings, produced by ONE GEMM launch whose epilogue adds the tables and writes the (B, 1 + tokens, hidden)

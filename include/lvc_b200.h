@@ -334,6 +334,26 @@ int lvc_embeddings_forward(const lvc_embed_desc* d, const void* x, const void* w
                            const float* cls_token, const float* position_embeddings,
                            const float* time_embeddings, void* out, void* workspace, void* stream);
 
+/* The Video Swin front end in one call: lvc_clip_forward (cv2 chain, bf16 token layout of the (2,4,4) patch) and
+ * lvc_patch_embed (PatchEmbed3d + LayerNorm) as two CO-RESIDENT kernels -- replaces, in one pass,
+ * videoswintransformer/swin_video_classifier/data_config/dataset.py:151-173 (+ src/yolo_detector.py:76-85 boxes) and
+ * models/swin3d.py:22-44 (torchvision swin_transformer.py:353-363).  The embedding kernel is launched behind the clip
+ * kernel with programmatic stream serialization and loads each 128-token tile of the patch matrix as soon as the clip
+ * kernel's per-tile counter says it is complete, so the HBM-bound embedding hides behind the latency-bound clip stage.
+ * `tokens` (bf16 A[M][K]) and `ready` (uint32 per tile) are device workspaces of the sizes
+ * lvc_clip_swin_embed_workspace reports (ready is cleared by the call).  clip_desc: LVC_RESAMPLE_CV2, LVC_LAYOUT_TOKENS,
+ * LVC_DT_BF16, tok_* = the embedding's patch; embed_desc: LVC_EMBED_SWIN, x_layout LVC_LAYOUT_TOKENS, 224 x 224.
+ * Results are bit-identical to the two separate calls.  Other arguments as lvc_clip_forward / lvc_patch_embed.
+ * EXPERIMENTAL, NOT THE DEFAULT PATH: on BASELINE config 4 the pair measures 140 us against 120 us for the two launches
+ * (sharing the SM slows the clip stage from 88 to 113 us and the embedding ends 14 us after it);
+ * pipeline.ClipEmbedPipeline and bench.py keep the two launches.  Correctness never depends on co-residency: the clip
+ * kernel does not wait for the embedding kernel, which simply runs afterwards when the two do not fit on an SM together. */
+int lvc_clip_swin_embed_workspace(const lvc_embed_desc* embed_desc, int64_t* tokens_bytes, int64_t* ready_bytes);
+int lvc_clip_swin_embed_forward(const lvc_clip_desc* clip_desc, const lvc_video* videos, const int32_t* indices,
+                                const int32_t* boxes, const float* lut, const lvc_embed_desc* embed_desc,
+                                const void* w_packed_bf16, const float* bias, const float* ln_w, const float* ln_b,
+                                void* tokens, void* ready, void* out, void* stream);
+
 /* --------------------------------------------- detector pre / post-processing ---- */
 
 /* Geometry of yolov5 `letterbox(im, new_shape, stride=stride)` with its defaults auto=True, scaleFill=False,
