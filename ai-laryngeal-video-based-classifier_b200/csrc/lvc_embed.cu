@@ -837,7 +837,7 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
 // while the clip kernel runs, and its producer loads a tile of A when the clip kernel's ready counter says the tile
 // is complete (p.ready).  It must then NOT execute griddepcontrol.wait (that would wait for the whole clip grid).
 template <int NCH, bool OUT_F32, int NG = kSwinGroups>  // N = 32 * NCH columns, NG * N <= 512 TMEM columns
-__global__ void __launch_bounds__(swin_threads(NG), (NG == kSwinGroupsFused ? 4 : 1))   // fused variant: <= 80 registers
+__global__ void __launch_bounds__(swin_threads(NG), (NG == kSwinGroupsFused ? 3 : 1))   // fused variant: <= 112 registers (it takes 96: 8 x 32 x 96 + the clip variant's 16 x 32 x 80 = 65 536)
 lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                       const __grid_constant__ CUtensorMap map_o, const __grid_constant__ GemmParams p) {
   constexpr int N = 32 * NCH;
@@ -1390,8 +1390,8 @@ extern "C" int lvc_patch_embed_static(const lvc_embed_desc* d, const void* x, co
 // kernels CO-RESIDENT on every SM.  The clip stage of ROI batches is bound by its consumers' latency (half the issue
 // slots idle, 2 of 6.5 TB/s of DRAM) and the embedding is bound by HBM, so run in sequence they waste each other's
 // resource; side by side the embedding hides behind the clip stage.  Mechanics: (1) the clip kernel runs in a variant
-// with two producer warps and its shared memory capped so that a 192-thread / 80-register / 110 KB embedding CTA fits
-// on the same SM (64.5 K of 64 K... registers: 512 x 96 + 192 x 80); (2) it counts, per 128-token tile of A, the
+// with two producer warps, 80 registers and its shared memory capped so that a 192-thread / 96-register / 110 KB embedding
+// CTA fits on the same SM (registers are allocated per four warps: 16 x 32 x 80 + 8 x 32 x 96 = 65 536); (2) it counts, per 128-token tile of A, the
 // token-row slices it has stored (red.release.gpu); (3) the embedding kernel is launched behind it with programmatic
 // stream serialization -- the clip kernel executes griddepcontrol.launch_dependents on entry, so the embedding grid
 // starts as soon as every clip CTA is resident -- and its TMA producer loads a tile when the tile's counter is complete
