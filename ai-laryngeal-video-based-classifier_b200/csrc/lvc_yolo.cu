@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <type_traits>
 
 #include "lvc_internal.h"
 
@@ -184,22 +185,51 @@ __device__ __forceinline__ void lb_bulk_g2s(void* dst, const void* src, uint32_t
 }
 constexpr int kLbMaxRows = 8;   // output rows per item of the staged kernel (2 * rows source-row slots <= 16 lanes)
 
-// shared memory: [0,16) two mbarriers | s_div[256] | s_row[2][kLbMaxRows] (off0, off1, b0, b1; off0 < 0: border row) |
-// xt[new_w] | row slots [2][2 * rows][pitch] (16-byte aligned)
-__global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_constant__ LbParams p) {
+constexpr int kLbFixed = 16 + 4 * 1024 + 2 * kLbMaxRows * 16;   // barriers, value table, row tables (bytes before xt[])
+__host__ __device__ inline size_t lb_slots_offset(int new_w) { return ((size_t)kLbFixed + (size_t)new_w * 8 + 127) & ~(size_t)127; }
+
+// One output pixel of the staged kernel from its two tapped rows in shared memory: three aligned words per row + funnel
+// shift, PRMT into (c0 p0, c0 p1, c1 p0, c1 p1) / (c2 p0, c2 p1), cv2's exact 11-bit horizontal pass as DP2A, its vertical
+// pass ((b * (S >> 4)) >> 16) as one multiply-high per term (the row coefficients arrive as b << 16).  The exact-2x
+// INTER_AREA case is the same code with a0 = a1 = 32, b = 2^31: (p00 + p01 + p10 + p11 + 2) >> 2.  Returns the UNROUNDED
+// vertical sums t[c] (<= 1020): the value table is indexed by them and folds cv2's (+ 2) >> 2.
+__device__ __forceinline__ void lb_pixel(uint32_t q0, uint32_t q1, uint32_t a01, uint32_t b0s, uint32_t b1s, unsigned (&t)[3]) {
+  uint32_t a, bq, cq, d, e, fq;
+  asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+               : "=r"(a), "=r"(bq), "=r"(cq) : "r"(q0 & ~3u));
+  asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+               : "=r"(d), "=r"(e), "=r"(fq) : "r"(q1 & ~3u));
+  const uint32_t sh0 = q0 << 3, sh1 = q1 << 3;   // funnel shifts wrap at 32: (q & 3) * 8
+  const uint32_t lo0 = __funnelshift_r(a, bq, sh0), hi0 = __funnelshift_r(bq, cq, sh0);
+  const uint32_t lo1 = __funnelshift_r(d, e, sh1), hi1 = __funnelshift_r(e, fq, sh1);
+  const uint32_t wa0 = __byte_perm(lo0, hi0, 0x4130u), wb0 = __byte_perm(lo0, hi0, 0x4452u);
+  const uint32_t wa1 = __byte_perm(lo1, hi1, 0x4130u), wb1 = __byte_perm(lo1, hi1, 0x4452u);
+  const unsigned s00 = __dp2a_lo(a01, wa0, 0u), s01 = __dp2a_hi(a01, wa0, 0u), s02 = __dp2a_lo(a01, wb0, 0u);
+  const unsigned s10 = __dp2a_lo(a01, wa1, 0u), s11 = __dp2a_hi(a01, wa1, 0u), s12 = __dp2a_lo(a01, wb1, 0u);
+  t[0] = __umulhi(b0s, s00 >> 4) + __umulhi(b1s, s10 >> 4);
+  t[1] = __umulhi(b0s, s01 >> 4) + __umulhi(b1s, s11 >> 4);
+  t[2] = __umulhi(b0s, s02 >> 4) + __umulhi(b1s, s12 >> 4);
+}
+
+// shared memory: [0,16) two mbarriers | s_val[1024] (x / 255 of (t + 2) >> 2 for the unrounded vertical sum t) |
+// s_row[2][kLbMaxRows] (off0, off1, b0 << 16, b1 << 16; off0 < 0: border row) | xt[new_w] | row slots [2][2 * rows][pitch]
+#ifndef LVC_LB_MINBLOCKS
+#define LVC_LB_MINBLOCKS 3   // 80 registers, three blocks per SM: 0.088 ms for 64 x 1080p; capped at 64 registers (four blocks) it spills: 0.100 ms
+#endif
+__global__ void __launch_bounds__(kLbThreads, LVC_LB_MINBLOCKS) lvc_letterbox_kernel(const __grid_constant__ LbParams p) {
   extern __shared__ __align__(128) uint8_t lb_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(lb_smem);
-  float* s_div = reinterpret_cast<float*>(lb_smem + 16);
-  int4* s_row = reinterpret_cast<int4*>(lb_smem + 16 + 1024);
-  XTap* xt = reinterpret_cast<XTap*>(lb_smem + 16 + 1024 + 2 * kLbMaxRows * 16);
+  float* s_val = reinterpret_cast<float*>(lb_smem + 16);
+  int4* s_row = reinterpret_cast<int4*>(lb_smem + 16 + 4 * 1024);
+  XTap* xt = reinterpret_cast<XTap*>(lb_smem + kLbFixed);
   const lvc_letterbox_geom& g = p.g;
-  uint8_t* slots = lb_smem + ((16 + 1024 + 2 * kLbMaxRows * 16 + (size_t)g.new_w * 8 + 127) & ~(size_t)127);
+  uint8_t* slots = lb_smem + lb_slots_offset(g.new_w);
   const int R = p.rows, nslot = 2 * R;
   const bool area = g.src_w == 2 * g.new_w && g.src_h == 2 * g.new_h;   // cv::resize switches to INTER_AREA
   const double sx_scale = cv_scale(g.src_w, g.new_w), sy_scale = cv_scale(g.src_h, g.new_h);
   for (int x = threadIdx.x; x < g.new_w; x += kLbThreads) {
     XTap t;
-    if (area) { t.off = 6 * x; t.a01 = 1 | (1 << 16); }
+    if (area) { t.off = 6 * x; t.a01 = 32 | (32 << 16); }
     else {
       int sx; float fr;
       cv_tap(x, sx_scale, sx, fr);
@@ -210,7 +240,8 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
     }
     xt[x] = t;
   }
-  for (int i = threadIdx.x; i < 256; i += kLbThreads) s_div[i] = __fdiv_rn((float)i, 255.0f);
+  // x / 255 (IEEE division = what torch's CPU `im /= 255` computes) of the rounded value, indexed by the unrounded sum
+  for (int i = threadIdx.x; i < 1024; i += kLbThreads) s_val[i] = __fdiv_rn((float)min((i + 2) >> 2, 255), 255.0f);
   if (threadIdx.x == 0) {
     lb_mbar_init(&full[0], 1);
     lb_mbar_init(&full[1], 1);
@@ -231,13 +262,13 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
       const bool row_in = iy >= 0 && iy < g.new_h && rblk * R + r < g.out_h;
       int ysrc = -1 - lane, cb = 0;   // border rows: a distinct key per lane, nothing fetched
       if (row_in) {
-        if (area) { ysrc = 2 * iy + (lane & 1); cb = 0; }
+        if (area) { ysrc = 2 * iy + (lane & 1); cb = (int)0x80000000u; }
         else {
           int sy; float fr;
           cv_tap(iy, sy_scale, sy, fr);
           // cv::resize does not reset the fraction of clamped ROWS
           ysrc = min(max(sy + (lane & 1), 0), g.src_h - 1);
-          cb = (lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr));
+          cb = ((lane & 1) ? coef(fr) : coef(__fsub_rn(1.0f, fr))) << 16;   // pre-shifted: the blend is a multiply-high
         }
       }
       const unsigned same = __match_any_sync(lanes, ysrc);
@@ -269,7 +300,76 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
   };
 
   const size_t plane = (size_t)g.out_h * g.out_w;
-  const float pad = s_div[114];
+  const float pad = s_val[114 * 4];
+  const uint32_t slots_s = lb_s32(slots);
+  // The usual network input is at most 768 columns wide: a thread then owns the SAME (up to three) columns in every row
+  // of every item, and their taps live in registers for the whole kernel (no table look-up, no bounds logic per pixel).
+  const bool narrow = g.out_w <= kLbThreads * kLbUnroll;
+  uint32_t c_off[kLbUnroll], c_a01[kLbUnroll];
+  bool c_in[kLbUnroll], c_val[kLbUnroll];
+#pragma unroll
+  for (int u = 0; u < kLbUnroll; ++u) {
+    const int ox = (int)threadIdx.x + u * kLbThreads, ix = ox - g.left;
+    c_val[u] = ox < g.out_w;
+    c_in[u] = c_val[u] && ix >= 0 && ix < g.new_w;
+    const XTap t = c_in[u] ? xt[ix] : XTap{0, 0};
+    c_off[u] = (uint32_t)t.off; c_a01[u] = (uint32_t)t.a01;
+  }
+  // store of one pixel: transpose(2,0,1)[::-1] -- output channel k is input channel 2 - k
+  auto store3 = [&](auto BF, size_t e, const float (&v)[3]) {
+    if (decltype(BF)::value) {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + e;
+      o[0] = __float2bfloat16_rn(v[2]); o[plane] = __float2bfloat16_rn(v[1]); o[2 * plane] = __float2bfloat16_rn(v[0]);
+    } else {
+      float* o = reinterpret_cast<float*>(p.out) + e;
+      __stcs(o, v[2]); __stcs(o + plane, v[1]); __stcs(o + 2 * plane, v[0]);
+    }
+  };
+  auto rows = [&](auto BF, int frame, int rblk, int b) {
+    for (int r = 0; r < R; ++r) {
+      const int oy = rblk * R + r;
+      if (oy >= g.out_h) break;
+      const int4 rt = s_row[b * kLbMaxRows + r];
+      const bool row_in = rt.x >= 0;
+      const uint32_t base0 = slots_s + (uint32_t)max(rt.x, 0), base1 = slots_s + (uint32_t)max(rt.y, 0);
+      const uint32_t b0s = (uint32_t)rt.z, b1s = (uint32_t)rt.w;
+      const size_t erow = (size_t)frame * 3 * plane + (size_t)oy * g.out_w;
+      if (narrow) {
+        unsigned t[kLbUnroll][3];
+#pragma unroll
+        for (int u = 0; u < kLbUnroll; ++u)   // all shared loads of the thread's pixels are requested before the first is used
+          if (row_in && c_in[u]) lb_pixel(base0 + c_off[u], base1 + c_off[u], c_a01[u], b0s, b1s, t[u]);
+#pragma unroll
+        for (int u = 0; u < kLbUnroll; ++u) {
+          if (!c_val[u]) continue;
+          float v[3] = {pad, pad, pad};
+          if (row_in && c_in[u]) { v[0] = s_val[t[u][0]]; v[1] = s_val[t[u][1]]; v[2] = s_val[t[u][2]]; }
+          store3(BF, erow + threadIdx.x + u * kLbThreads, v);
+        }
+        continue;
+      }
+      for (int ox0 = threadIdx.x; ox0 < g.out_w; ox0 += kLbThreads * kLbUnroll) {
+        unsigned t[kLbUnroll][3];
+        bool in[kLbUnroll];
+#pragma unroll
+        for (int u = 0; u < kLbUnroll; ++u) {
+          const int ox = ox0 + u * kLbThreads, ix = ox - g.left;
+          in[u] = row_in && ox < g.out_w && ix >= 0 && ix < g.new_w;
+          if (!in[u]) continue;
+          const XTap tp = xt[ix];
+          lb_pixel(base0 + (uint32_t)tp.off, base1 + (uint32_t)tp.off, (uint32_t)tp.a01, b0s, b1s, t[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < kLbUnroll; ++u) {
+          const int ox = ox0 + u * kLbThreads;
+          if (ox >= g.out_w) continue;
+          float v[3] = {pad, pad, pad};
+          if (in[u]) { v[0] = s_val[t[u][0]]; v[1] = s_val[t[u][1]]; v[2] = s_val[t[u][2]]; }
+          store3(BF, erow + ox, v);
+        }
+      }
+    }
+  };
   if (warp == 0 && (int)blockIdx.x < p.items) issue(blockIdx.x, 0);
   uint32_t it = 0;
   for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
@@ -278,59 +378,8 @@ __global__ void __launch_bounds__(kLbThreads) lvc_letterbox_kernel(const __grid_
     if (warp == 0 && item + (int)gridDim.x < p.items) issue(item + gridDim.x, b ^ 1);
     lb_mbar_wait(&full[b], (it >> 1) & 1u);
     const int frame = item / p.row_blocks, rblk = item - frame * p.row_blocks;
-    for (int r = 0; r < R; ++r) {
-      const int oy = rblk * R + r;
-      if (oy >= g.out_h) break;
-      const int4 rt = s_row[b * kLbMaxRows + r];
-      const bool row_in = rt.x >= 0;
-      const uint32_t base0 = lb_s32(slots) + (uint32_t)max(rt.x, 0), base1 = lb_s32(slots) + (uint32_t)max(rt.y, 0);
-      const int b0 = rt.z, b1 = rt.w;
-      for (int ox0 = threadIdx.x; ox0 < g.out_w; ox0 += kLbThreads * kLbUnroll) {
-        uint32_t lo0[kLbUnroll], hi0[kLbUnroll], lo1[kLbUnroll], hi1[kLbUnroll], a01[kLbUnroll];
-        bool in[kLbUnroll];
-#pragma unroll
-        for (int u = 0; u < kLbUnroll; ++u) {
-          const int ox = ox0 + u * kLbThreads, ix = ox - g.left;
-          in[u] = row_in && ox < g.out_w && ix >= 0 && ix < g.new_w;
-          lo0[u] = hi0[u] = lo1[u] = hi1[u] = a01[u] = 0u;
-          if (!in[u]) continue;
-          const XTap t = xt[ix];
-          a01[u] = (uint32_t)t.a01;
-          const uint32_t q0 = base0 + (uint32_t)t.off, q1 = base1 + (uint32_t)t.off;
-          uint32_t a, bq, cq, d, e, fq;
-          asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
-                       : "=r"(a), "=r"(bq), "=r"(cq) : "r"(q0 & ~3u));
-          asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
-                       : "=r"(d), "=r"(e), "=r"(fq) : "r"(q1 & ~3u));
-          const uint32_t sh0 = (q0 & 3u) * 8u, sh1 = (q1 & 3u) * 8u;
-          lo0[u] = __funnelshift_r(a, bq, sh0); hi0[u] = __funnelshift_r(bq, cq, sh0);
-          lo1[u] = __funnelshift_r(d, e, sh1); hi1[u] = __funnelshift_r(e, fq, sh1);
-        }
-#pragma unroll
-        for (int u = 0; u < kLbUnroll; ++u) {
-          const int ox = ox0 + u * kLbThreads;
-          if (ox >= g.out_w) continue;
-          float v[3] = {pad, pad, pad};
-          if (in[u]) {
-            const uint32_t sel[3] = {0x4430u, 0x4441u, 0x4452u};   // (c of pixel 0, c of pixel 1) of the 8 bytes
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              const int s0 = (int)__dp2a_lo(a01[u], __byte_perm(lo0[u], hi0[u], sel[c]), 0u);
-              const int s1 = (int)__dp2a_lo(a01[u], __byte_perm(lo1[u], hi1[u], sel[c]), 0u);
-              const int uu = area ? ((s0 + s1 + 2) >> 2) : ((((b0 * (s0 >> 4)) >> 16) + ((b1 * (s1 >> 4)) >> 16) + 2) >> 2);
-              v[c] = s_div[uu];
-            }
-          }
-          // transpose(2,0,1)[::-1]: output channel k is input channel 2 - k
-          const size_t e = (size_t)frame * 3 * plane + (size_t)oy * g.out_w + ox;
-#pragma unroll
-          for (int k = 0; k < 3; ++k) {
-            if (p.out_bf16) reinterpret_cast<__nv_bfloat16*>(p.out)[e + k * plane] = __float2bfloat16_rn(v[2 - k]);
-            else __stcs(reinterpret_cast<float*>(p.out) + e + k * plane, v[2 - k]);
-          }
-        }
-      }
-    }
+    if (p.out_bf16) rows(std::true_type{}, frame, rblk, b);
+    else rows(std::false_type{}, frame, rblk, b);
     __syncthreads();   // buffer b (rows and s_row) may be refilled by the next trip's issue
   }
 }
@@ -434,7 +483,7 @@ extern "C" int lvc_letterbox_forward(const lvc_letterbox_geom* g, const uint8_t*
   // (measured on B200, 64 frames: 1080p 2 rows 0.094 ms vs 4 rows 0.112, 8 rows 0.167; 480p 4 rows 0.108 vs 2 rows 0.116),
   // else for two, else for one; frames too wide even for that take the direct-global kernel
   p.pitch = ((g->src_w * 3 + 15 + 15) & ~15) + 16;
-  const size_t fixed = ((size_t)16 + 1024 + 2 * kLbMaxRows * 16 + (size_t)g->new_w * 8 + 127) & ~(size_t)127;
+  const size_t fixed = lb_slots_offset(g->new_w);
   p.rows = 0;
   const int forced_rows = lvc_knob_int("LVC_LB_STAGE_ROWS", -1);   // profiling knob (gated): 0 = direct kernel
   for (int pass = 0; pass < 3 && !p.rows && forced_rows != 0; ++pass)
