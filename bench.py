@@ -391,6 +391,15 @@ def run_secondary(dev, iters=10):
         else:
             ent["gemm_roofline"] = {"bound": "tensor", "achieved": flops / gemm_ms / 1e9, "peak": tf_peak, "unit": "TFLOP/s",
                                     "frac": flops / gemm_ms / 1e9 / tf_peak}
+        if c["embed"] == "swin":
+            # experimental co-resident pair (lvc_clip_swin_embed_forward): reported beside the two-launch
+            # pipeline it does NOT replace (it measures slower); output compared bit for bit
+            fused_out = torch.empty((c["videos"], c["T"] // 2, 56, 56, 128), dtype=torch.bfloat16, device=dev)
+            ent["fused_ms"] = timed(lambda: m.forward_clips(cb, batch, out=fused_out), True)
+            want = m.forward_tokens(cb.run(batch, tok), c["videos"], c["T"])
+            torch.cuda.synchronize()
+            ent["fused_bit_identical"] = bool(torch.equal(want.view(torch.int16).view(-1), fused_out.view(torch.int16).view(-1)))
+            del fused_out, want
         # host-inclusive throughput (wall clock, Python call path included): two eager launches per batch vs the
         # captured CUDA graph of [table upload -> clip kernel -> GEMM] (pipeline.ClipEmbedPipeline)
         from lvc_b200.pipeline import ClipEmbedPipeline
