@@ -710,13 +710,7 @@ __global__ void __launch_bounds__(NPW == kProducers ? threads_of(MODE, NPW) : 73
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (p.lut)
-    for (int i = tid; i < 3 * 256; i += kThreads) {
-      const float w = p.lut[i];
-      lut[i] = w;
-      lut16[i] = __float2bfloat16_rn(w);
-    }
-  if (MODE == MODE_VIVIT)
+  if (MODE == MODE_VIVIT)   // (the producers read this table too: item geometry of the bands)
     for (int i = tid; i < S; i += kThreads) {
       const int4 t = pil_tap(i);
       reinterpret_cast<int4*>(smem + kVivitTapOff)[i] = t;
@@ -727,36 +721,50 @@ __global__ void __launch_bounds__(NPW == kProducers ? threads_of(MODE, NPW) : 73
                                                              : (p.layout == LVC_LAYOUT_BTHWC ? S * 3 : S);
       reinterpret_cast<unsigned*>(smem + kVivitRowPartOff)[i] = row_part(p, rowmul, i);
     }
-  if (MODE == MODE_CV2 && ODT >= 0 && ODT != LVC_DT_U8 && !STATS && p.lut) {
-    // table of the lean consumer: entry t = LUT[(t + 2) >> 2], t = unrounded sum of the two vertical terms (<= 1020)
-    for (int i = tid; i < 3 * 1024; i += kThreads) {
-      const float w = p.lut[(i >> 10) * 256 + min(((i & 1023) + 2) >> 2, 255)];
-      if (ODT == LVC_DT_F32) reinterpret_cast<float*>(smem + p.lut4_off)[i] = w;
-      else reinterpret_cast<__nv_bfloat16*>(smem + p.lut4_off)[i] = __float2bfloat16_rn(w);
+  __syncthreads();   // barriers (and the ViViT tap table) are ready: the producer warps start fetching NOW
+  // The value tables are the consumers' business: they build them while the first stages are in flight (the set-up used to
+  // sit in front of the producers' first copy: ~1.5 us of every launch) and meet on the consumers' own barrier.
+  const bool is_consumer = warp >= NPW;
+  const int ct0 = tid - 32 * NPW;
+  if (is_consumer) {
+    if (p.lut)
+      for (int i = ct0; i < 3 * 256; i += kConsumers) {
+        const float w = p.lut[i];
+        lut[i] = w;
+        lut16[i] = __float2bfloat16_rn(w);
+      }
+    if (MODE == MODE_CV2 && ODT >= 0 && ODT != LVC_DT_U8 && !STATS && p.lut) {
+      // table of the lean consumer: entry t = LUT[(t + 2) >> 2], t = unrounded sum of the two vertical terms (<= 1020)
+      for (int i = ct0; i < 3 * 1024; i += kConsumers) {
+        const float w = p.lut[(i >> 10) * 256 + min(((i & 1023) + 2) >> 2, 255)];
+        if (ODT == LVC_DT_F32) reinterpret_cast<float*>(smem + p.lut4_off)[i] = w;
+        else reinterpret_cast<__nv_bfloat16*>(smem + p.lut4_off)[i] = __float2bfloat16_rn(w);
+      }
     }
+    consumers_bar(kConsumers);
   }
-  __syncthreads();
   // bf16 outputs: the look-up costs three bank-conflicted shared loads per sample (random 8-bit indices: ~3.5 wavefronts
   // each -- ncu: 41 % of this kernel's shared-memory wavefronts on the small-source configs, whose consumers are bound by
   // the LSU data pipe).  The reference's normalisation is affine in the pixel value, so y = fma(v, a, b) rounded to bf16
-  // usually equals the rounded table entry for all 3 x 256 values; every CTA VERIFIES that here and only then replaces
-  // the look-up by two FMA-pipe instructions (bit-identical by construction; any table that fails keeps the look-up).
+  // usually equals the rounded table entry for all 3 x 256 values; every consumer WARP verifies that here (all 768 values,
+  // 24 per lane: the same answer in every warp, no vote across warps needed) and only then replaces the look-up by two
+  // FMA-pipe instructions (bit-identical by construction; any table that fails keeps the look-up).
   float fa[3] = {0.f, 0.f, 0.f}, fb[3] = {0.f, 0.f, 0.f};
   bool use_fma = false;
-  if (MODE != MODE_PTV && p.out_dtype == LVC_DT_BF16 && p.lut && !p.no_fma) {
+  if (is_consumer && MODE != MODE_PTV && p.out_dtype == LVC_DT_BF16 && p.lut && !p.no_fma) {
     bool ok = true;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       fb[c] = lut[c * 256];
       fa[c] = __fdiv_rn(__fsub_rn(lut[c * 256 + 255], lut[c * 256]), 255.0f);
     }
-    for (int i = tid; i < 3 * 256; i += kThreads) {
+    for (int i = lane; i < 3 * 256; i += 32) {
       const int c = i >> 8;
       const float a = c == 0 ? fa[0] : (c == 1 ? fa[1] : fa[2]), b = c == 0 ? fb[0] : (c == 1 ? fb[1] : fb[2]);
       const __nv_bfloat16 y = __float2bfloat16_rn(__fmaf_rn((float)(i & 255), a, b));
       ok = ok && (__bfloat16_as_ushort(y) == __bfloat16_as_ushort(lut16[i]));
     }
-    use_fma = __syncthreads_and(ok) != 0;
+    use_fma = __all_sync(0xffffffffu, ok) != 0;
   }
 
   if (warp < NPW) {
