@@ -13,6 +13,43 @@ def shard_indices(n_videos, rank, world_size):
     return list(range(rank, n_videos, world_size))
 
 
+def weighted_counts(n_items, weights, floor=1):
+    """Split ``n_items`` over ranks in proportion to ``weights`` (largest-remainder rounding, every rank at least
+    ``floor``).  Used to shard by MEASURED ingest rate: on a box whose GPUs do not all reach the same host-to-device
+    rate (shared PCIe uplinks: 23 vs 35 GB/s per GPU were measured with eight GPUs active, profiles/r02_pcie_probe_n8.json)
+    equal shards make every step wait for the slowest link; proportional shards finish together."""
+    w = np.asarray(weights, dtype=np.float64)
+    if w.ndim != 1 or len(w) == 0 or not np.all(np.isfinite(w)) or np.any(w <= 0):
+        raise ValueError("weights must be positive finite numbers, one per rank")
+    n_items, floor = int(n_items), int(floor)
+    if n_items < floor * len(w):
+        raise ValueError("fewer items than ranks x floor")
+    ideal = w / w.sum() * (n_items - floor * len(w))
+    counts = np.floor(ideal).astype(np.int64)
+    rest = int(n_items - floor * len(w) - counts.sum())
+    order = np.argsort(-(ideal - counts), kind="stable")          # ties: lowest rank first
+    counts[order[:rest]] += 1
+    return (counts + floor).tolist()
+
+
+def weighted_shards(n_videos, weights):
+    """Contiguous blocks of videos per rank, sized by ``weighted_counts``: ``[range(a0, a1), range(a1, a2), ...]``."""
+    counts = weighted_counts(n_videos, weights, floor=0)
+    out, a = [], 0
+    for c in counts:
+        out.append(list(range(a, a + c)))
+        a += c
+    return out
+
+
+def ingest_weights(seconds_per_clip, clamp=2.0):
+    """Per-rank weights from measured seconds per clip (all ranks ingesting concurrently): rate = 1 / seconds, clamped
+    to within ``clamp`` x of the median so that one noisy measurement cannot starve a rank."""
+    r = 1.0 / np.asarray(seconds_per_clip, dtype=np.float64)
+    med = float(np.median(r))
+    return np.clip(r, med / clamp, med * clamp).tolist()
+
+
 def plan_epoch(total_frames, method, num_frames, seed=42, reseed_each_call=False):
     """Index table (n_videos, T) for a whole pass IN DATASET ORDER on one stream seeded like the
     reference's ``VideoDataset.__init__`` (vivit .../dataset.py:39-40): exactly what a sequential,

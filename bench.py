@@ -263,31 +263,64 @@ def run_b200(args, wl):
     cb._retire()   # drop the parked batch (it holds the device videos)
     del vids, batch
     torch.cuda.empty_cache()
+    # N > 1: the GPUs of a box do not all reach the same host-to-device rate (shared PCIe uplinks: 23 vs 35 GB/s per GPU
+    # with eight active, profiles/r02_pcie_probe_n8.json).  Equal shards make every step wait for the slowest link, so the
+    # job's world x B clips are sharded by MEASURED ingest rate (lvc_b200.sharding.weighted_counts): one concurrent,
+    # untimed probe step on every rank, all_gather of its duration, proportional clip counts.  N = 1: nothing to do.
+    Bs, shard_note = [B] * world, "equal"
+    stats.zero_()
+    cb.build_from_host(host, idx, out=out, stats=stats)          # untimed: first touch of the pinned pages, caches
+    torch.cuda.synchronize()
+    if world > 1 and not args.equal_shards:
+        from lvc_b200 import sharding
+
+        barrier()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        cb.build_from_host(host, idx, out=out, stats=stats)
+        p1.record()
+        torch.cuda.synchronize()
+        mine = torch.tensor([p0.elapsed_time(p1) / B], dtype=torch.float64, device=dev)
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_clip_ms = [float(t.item()) for t in allr]
+        Bs = sharding.weighted_counts(B * world, sharding.ingest_weights(per_clip_ms, clamp=2.0))
+        Bs = [min(b, 2 * B) for b in Bs]                          # (the clamp keeps every rank within 2 x B anyway)
+        shard_note = "by measured ingest rate"
+    Bm = Bs[rank]
+    host_m = [host[i % B] for i in range(Bm)]
+    idx_m = np.stack([idx[i % B] for i in range(Bm)])
+    out_m = out if Bm <= B else torch.empty((Bm,) + tuple(out.shape[1:]), dtype=out.dtype, device=dev)
+    out_m = out_m[:Bm]
+    stats_m = torch.zeros(Bm, dtype=torch.int64, device=dev)
+    ref_m = torch.stack([ref_stats[i % B] for i in range(Bm)])
     d2h, match = 0, True
     device_bytes_fetched(clear=True)
-    for k in range(1 + e2e_steps):
-        if k == 1:
-            device_bytes_fetched(clear=True)
-            barrier()
-            t0 = torch.cuda.Event(enable_timing=True)
-            t1 = torch.cuda.Event(enable_timing=True)
-            t0.record()
-        stats.zero_()
-        cb.build_from_host(host, idx, out=out, stats=stats)
-        chk = stats.cpu()  # device -> host read of the step's result (per-clip checksums)
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for k in range(e2e_steps):
+        stats_m.zero_()
+        cb.build_from_host(host_m, idx_m, out=out_m, stats=stats_m)
+        chk = stats_m.cpu()  # device -> host read of the step's result (per-clip checksums)
         d2h = chk.numel() * chk.element_size()
-        match = match and bool(torch.equal(chk, ref_stats))
+        match = match and bool(torch.equal(chk, ref_m))
     t1.record()
     barrier()
     h2d = device_bytes_fetched(clear=True) // e2e_steps      # counted by the kernel's producers, not estimated
     e = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
     ok = torch.tensor([1.0 if (match and not device_status()) else 0.0], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(h2d), float(d2h)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e, op=dist.ReduceOp.MAX)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    e2e = B * world / (float(e.item()) / e2e_steps * 1e-3)
-    res.update(e2e=e2e, e2e_steps=e2e_steps, h2d=int(h2d), h2d_estimate=cb.last_h2d_bytes, d2h=d2h,
-               e2e_match=bool(ok.item() == 1.0), checksum=int(chk.sum().item()), host_mem=args.host_mem)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    e2e = sum(Bs) / (float(e.item()) / e2e_steps * 1e-3)
+    # bytes per step: mean per GPU (what the contract's per-step figure has been so far), job totals beside it
+    res.update(e2e=e2e, e2e_steps=e2e_steps, h2d=int(tot[0].item() / world), h2d_estimate=cb.last_h2d_bytes, d2h=int(tot[1].item() / world),
+               e2e_match=bool(ok.item() == 1.0), checksum=int(chk.sum().item()), host_mem=args.host_mem,
+               e2e_clips_per_rank=Bs, e2e_sharding=shard_note)
     return res
 
 
@@ -630,6 +663,8 @@ def main():
     ap.add_argument("--workload", default="sweep1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--host-mem", default="pinned", choices=["pinned", "wc"],
                     help="e2e leg: ordinary page-locked host frames, or write-combined (device reads are not snooped)")
+    ap.add_argument("--equal-shards", action="store_true", help="e2e leg at N > 1: 64 clips on every rank instead of "
+                    "shards sized by each rank's measured host-to-device rate")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host->device leg (profiling runs only)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the configs[0..3] legs")
@@ -678,7 +713,9 @@ def main():
                        "steps": r["e2e_steps"], "checksum_matches_device": r["e2e_match"], "host_mem": r["host_mem"],
                        "h2d_counted_by": "device counter of the kernel's bulk-copy producers (lvc_device_bytes_fetched)",
                        "path": "ClipBuilder.build_from_host: pinned host frames read in place by the fused kernel over PCIe "
-                               "(tapped rows only) -> clips stay in HBM for the model -> D2H of the per-clip checksums only"}
+                               "(tapped rows only) -> clips stay in HBM for the model -> D2H of the per-clip checksums only",
+                       "sharding": r.get("e2e_sharding", "equal"), "clips_per_rank": r.get("e2e_clips_per_rank"),
+                       "bytes_are": "mean per GPU and step"}
     line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                         "traffic": tr.get("bytes_per_launch"), "traffic_source": {k: tr.get(k) for k in ("capture", "git", "when")} if tr else None,
                         "peak_source": src, "kernel": "lvc_clip_kernel<MODE_CV2>",

@@ -52,3 +52,25 @@ def test_single_process_gather_and_reseed_plan():
     assert sharding.gather_stats(3, 1.5, 7) == [(3.0, 1.5, 7.0)]
     t = sharding.plan_epoch([100, 100], "random", 8, reseed_each_call=True)
     assert t[0].tolist() == t[1].tolist() == osm.dataset_indices("random", 100, 8, random.Random(42))
+
+
+def test_weighted_counts_and_shards():
+    # the measured eight-GPU box: four links at 23 GB/s, four at 35 GB/s, 512 clips per step
+    w = sharding.ingest_weights([1 / 23.2] * 4 + [1 / 35.4] * 4)
+    c = sharding.weighted_counts(512, w)
+    assert sum(c) == 512
+    assert max(c[:4]) - min(c[:4]) <= 1 and max(c[4:]) - min(c[4:]) <= 1 and 76 <= c[4] <= 78 and 50 <= c[0] <= 52
+    # every step then ends together: time = clips / rate is equal to within one clip
+    t = [c[i] / (23.2 if i < 4 else 35.4) for i in range(8)]
+    assert max(t) / min(t) < 1.03
+    assert sharding.weighted_counts(10, [1, 1, 1]) == [4, 3, 3]                 # ties: lowest rank first
+    assert sharding.weighted_counts(3, [100, 1, 1]) == [1, 1, 1]                # floor: nobody starves
+    assert sharding.weighted_counts(64, [1.0]) == [64]
+    sh = sharding.weighted_shards(7, [2, 1])
+    assert sh == [[0, 1, 2, 3, 4], [5, 6]] and sorted(sum(sh, [])) == list(range(7))
+    assert sharding.ingest_weights([1.0, 1.0, 100.0]) == [1.0, 1.0, 0.5]        # a stalled measurement is clamped
+    import pytest
+    with pytest.raises(ValueError):
+        sharding.weighted_counts(2, [1, 1, 1])
+    with pytest.raises(ValueError):
+        sharding.weighted_counts(8, [1, 0])
