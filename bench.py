@@ -274,19 +274,26 @@ def run_b200(args, wl):
     if world > 1 and not args.equal_shards:
         from lvc_b200 import sharding
 
-        barrier()
-        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        p0.record()
-        cb.build_from_host(host, idx, out=out, stats=stats)
-        p1.record()
-        torch.cuda.synchronize()
-        mine = torch.tensor([p0.elapsed_time(p1) / B], dtype=torch.float64, device=dev)
-        allr = [torch.empty_like(mine) for _ in range(world)]
-        dist.all_gather(allr, mine)
-        per_clip_ms = [float(t.item()) for t in allr]
-        Bs = sharding.weighted_counts(B * world, sharding.ingest_weights(per_clip_ms, clamp=2.0))
-        Bs = [min(b, 2 * B) for b in Bs]                          # (the clamp keeps every rank within 2 x B anyway)
-        shard_note = "by measured ingest rate"
+        for probe in range(2):   # second pass: the rates are re-measured UNDER the first split (links interact)
+            nb = Bs[rank]
+            hp = [host[i % B] for i in range(nb)]
+            ip = np.stack([idx[i % B] for i in range(nb)])
+            op = torch.empty((nb,) + tuple(out.shape[1:]), dtype=out.dtype, device=dev) if nb > B else out[:nb]
+            sp = torch.zeros(nb, dtype=torch.int64, device=dev)
+            barrier()
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
+            cb.build_from_host(hp, ip, out=op, stats=sp)
+            p1.record()
+            torch.cuda.synchronize()
+            mine = torch.tensor([p0.elapsed_time(p1) / nb], dtype=torch.float64, device=dev)
+            allr = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            per_clip_ms = [float(t.item()) for t in allr]
+            Bs = sharding.weighted_counts(B * world, sharding.ingest_weights(per_clip_ms, clamp=2.0))
+            Bs = [min(b, 2 * B) for b in Bs]                      # (the clamp keeps every rank within 2 x B anyway)
+            del op, sp
+        shard_note = "by measured ingest rate (two probe steps)"
     Bm = Bs[rank]
     host_m = [host[i % B] for i in range(Bm)]
     idx_m = np.stack([idx[i % B] for i in range(Bm)])
