@@ -144,6 +144,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
 }
+// The per-stage timeline (scripts/clip_trace.py) is a profiling aid: its checks sit in the stage loops of every consumer and
+// producer, so it is compiled in only with -DLVC_CLIP_TRACE_BUILD=1 (`make trace` builds liblvc_b200_trace.so beside the
+// shipped library; the shipped kernels carry none of it).
+#ifndef LVC_CLIP_TRACE_BUILD
+#define LVC_CLIP_TRACE_BUILD 0
+#endif
+constexpr bool kTraceBuild = LVC_CLIP_TRACE_BUILD != 0;
 constexpr int kTraceStages = 4096;
 constexpr int kTraceWords = kTraceStages * 4 + 2 * 1024;   // per-stage stamps of CTA 0, then (start, end) of every CTA
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -350,7 +357,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
-      const bool tr = p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
+      const bool tr = kTraceBuild && p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
       if (tr) p.trace[cn * 4 + 1] = globaltimer_ns();
       mbar_wait(&full[slot], phase);
       if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();
@@ -497,7 +504,7 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
   }
-  if (p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();   // consumer warp 0 done
+  if (kTraceBuild && p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();   // consumer warp 0 done
   if (p.tile_stamps && ct == 0 && blockIdx.x == 0) p.tile_stamps[1] = globaltimer_ns();
 }
 
@@ -574,7 +581,7 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
     bool item_bad = false;
     unsigned long long obase = 0;
     for (int st = 0; st < p.v_stages; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
-      const bool tr = p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
+      const bool tr = kTraceBuild && p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
       if (tr) p.trace[cn * 4 + 1] = globaltimer_ns();
       mbar_wait(&full[slot], phase);
       if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();
@@ -676,7 +683,7 @@ __device__ __forceinline__ void lean_vivit_consumer(const ClipParams& p, uint8_t
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0 && acc) atomicAdd(&p.stats[acc_b], acc);
   }
-  if (p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();
+  if (kTraceBuild && p.trace && ct == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2 + 1] = globaltimer_ns();
 }
 
 // ODT: compile-time output type of the lean cv2 consumer (LVC_DT_*), or -1 = the general consumer (type from the descriptor)
@@ -698,7 +705,7 @@ __global__ void __launch_bounds__(NPW == kProducers ? threads_of(MODE, NPW) : 73
   // scheduled as SMs free up; it waits for this grid to complete before it touches global data
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int tid = threadIdx.x;
-  if (p.trace && tid == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2] = globaltimer_ns();   // CTA start
+  if (kTraceBuild && p.trace && tid == 0) p.trace[kTraceStages * 4 + blockIdx.x * 2] = globaltimer_ns();   // CTA start
   if (p.tile_stamps && tid == 0 && blockIdx.x == 0) p.tile_stamps[0] = globaltimer_ns();
   const int warp = tid >> 5, lane = tid & 31;
   const int stages_per_item = MODE == MODE_VIVIT ? p.v_stages : p.rows_per_band / p.rps;
@@ -945,7 +952,7 @@ __global__ void __launch_bounds__(NPW == kProducers ? threads_of(MODE, NPW) : 73
         }
         __syncwarp();
         if (lane == 0) { mbar_arrive_expect_tx(&full[slot], total); fetched += total; }
-        if (p.trace && blockIdx.x == 0 && lane == 0 && n < kTraceStages) p.trace[n * 4 + 0] = globaltimer_ns();
+        if (kTraceBuild && p.trace && blockIdx.x == 0 && lane == 0 && n < kTraceStages) p.trace[n * 4 + 0] = globaltimer_ns();
         __syncwarp();
         if (leader && bulk_bytes)
           bulk_g2s(stage_base + (size_t)lane * item_pitch, reinterpret_cast<const void*>(a), bulk_bytes,
@@ -1014,7 +1021,7 @@ __global__ void __launch_bounds__(NPW == kProducers ? threads_of(MODE, NPW) : 73
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     bool item_bad = false;
     for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
-      const bool tr = p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
+      const bool tr = kTraceBuild && p.trace && blockIdx.x == 0 && ct == 0 && cn < kTraceStages;
       if (tr) p.trace[cn * 4 + 1] = globaltimer_ns();   // consumer starts waiting
       mbar_wait(&full[slot], phase);
       if (tr) p.trace[cn * 4 + 2] = globaltimer_ns();   // stage landed (or had landed)
@@ -1518,6 +1525,7 @@ extern "C" int lvc_clip_forward_aug(const lvc_clip_desc* d, const lvc_video* vid
   if (int rc = make_plan(d, boxes != nullptr, stats != nullptr, di.sms, di.max_smem, p, smem, grid)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (env_int("LVC_CLIP_TRACE", 0)) {   // profiling only: per-stage timeline of CTA 0 (lvc_clip_trace_read)
+    if (!kTraceBuild) return lvc_fail(LVC_E_NOTSUP, "LVC_CLIP_TRACE needs the trace build of the library (make -C csrc trace; LVC_B200_LIB=.../liblvc_b200_trace.so)");
     if (!g_trace_buf) LVC_CUDA_TRY(cudaMalloc(&g_trace_buf, kTraceWords * sizeof(unsigned long long)));
     LVC_CUDA_TRY(cudaMemsetAsync(g_trace_buf, 0, kTraceWords * sizeof(unsigned long long), st));
     p.trace = g_trace_buf;

@@ -6,6 +6,8 @@ import ctypes as C
 import os
 import sys
 
+_here = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+os.environ.setdefault("LVC_B200_LIB", os.path.join(_here, "ai-laryngeal-video-based-classifier_b200", "liblvc_b200_trace.so"))  # `make -C csrc trace`
 os.environ["LVC_PROFILING_KNOBS"] = "1"
 os.environ["LVC_CLIP_TRACE"] = "1"
 for a in sys.argv[2:]:
