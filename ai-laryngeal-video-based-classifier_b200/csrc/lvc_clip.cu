@@ -94,6 +94,7 @@ struct ClipParams {
   int ring_bytes;            // size of the byte-granular source-row ring
   int lut4_off;              // lean cv2 consumer: byte offset of the 3 x 1024 table indexed by the unrounded vertical sum
   int no_fma;                // profiling knob LVC_CLIP_NO_FMA: keep the bf16 look-up even when the affine form verifies
+  int no_tok44;              // profiling knob LVC_CLIP_NO_TOK44: 4 x 4 token blocks as four 2-byte stores per channel
   unsigned* tile_ready;      // fused patch embedding: counters of token-row slices written per tile of A, else NULL
   int tile_shift;            // log2(tokens per tile)
   unsigned long long* tile_stamps;   // fused patch embedding: CTA 0 stamps its start / end here (timeline of the pair)
@@ -322,6 +323,25 @@ __device__ __forceinline__ uint32_t shf_r_wrap(uint32_t lo, uint32_t hi, uint32_
   return d;
 }
 
+// Token layout of a 4 x 4 patch (Video Swin): a token's 16 samples of one (channel, tubelet frame) are 32 contiguous bytes
+// = one sector, but a thread (= column) holds one sample of each of the patch's four rows.  Stored directly that is four
+// 2-byte stores per channel whose warp-wide footprint is 8-byte fragments of eight different sectors (9.5 M written
+// sectors for 77 MB; the stage took 86 us against 68 us for planar bf16).  Instead the four lanes of a token transpose
+// their 4 x 4 block with two shuffles: P0 = (row 0, row 1), P1 = (row 2, row 3) of this lane's column, packed bf16;
+// afterwards lane dx holds ROW dx of the token, columns 0..3 = 8 contiguous bytes, and four lanes write one whole sector.
+__device__ __forceinline__ void tok44_transpose(uint32_t P0, uint32_t P1, int dx, uint32_t& w0, uint32_t& w1) {
+  const bool hi2 = (dx & 2) != 0, odd = (dx & 1) != 0;
+  const uint32_t keep1 = hi2 ? P1 : P0;
+  const uint32_t recv1 = __shfl_xor_sync(0xffffffffu, hi2 ? P0 : P1, 2);   // rows (rb, rb + 1), rb = dx & 2, of column dx ^ 2
+  const uint32_t clo = hi2 ? recv1 : keep1, chi = hi2 ? keep1 : recv1;     // ... ordered by column: dx & 1, (dx & 1) + 2
+  const uint32_t rowA = __byte_perm(clo, chi, 0x5410), rowB = __byte_perm(clo, chi, 0x7632);   // row rb / rb + 1 of both
+  const uint32_t keep2 = odd ? rowB : rowA;
+  const uint32_t recv2 = __shfl_xor_sync(0xffffffffu, odd ? rowA : rowB, 1);   // the same row of the neighbour's two columns
+  const uint32_t ev = odd ? recv2 : keep2, od = odd ? keep2 : recv2;            // columns (0, 2) / (1, 3) of row dx
+  w0 = __byte_perm(ev, od, 0x5410);   // columns 0, 1
+  w1 = __byte_perm(ev, od, 0x7632);   // columns 2, 3
+}
+
 template <int ODT, bool STATS>
 __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* smem, uint64_t* full, uint64_t* empty,
                                                   const StageHdr* hdrs, const int ct, const int lane, const bool use_fma,
@@ -354,6 +374,9 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
   uint32_t phase = 0;
   const int stages_per_item = p.rows_per_band / p.rps;
   const bool pair_rows = (p.rps & (2 * kGroups - 1)) == 0;
+  // 4 x 4 patches with one patch row per group and stage: whole-sector token stores (tok44_transpose)
+  const bool tok44 = ODT == LVC_DT_BF16 && p.layout == LVC_LAYOUT_TOKENS && p.kh == 4 && p.kw == 4 && p.rps == 4 * kGroups && !p.no_tok44;
+  const unsigned xoff44 = (unsigned)(x >> 2) * (unsigned)(3 * p.kt * 16) + (unsigned)(x & 3) * 4u;   // token, then ROW x & 3 of its block
 
   for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
     for (int st = 0; st < stages_per_item; ++st, ring_next(slot, phase, kMaxStages), ++cn) {
@@ -437,6 +460,49 @@ __device__ __forceinline__ void lean_cv2_consumer(const ClipParams& p, uint8_t* 
         }
       };
       auto rows = [&](auto FMA) {
+        constexpr bool kFma = decltype(FMA)::value;
+        if (ODT == LVC_DT_BF16 && tok44) {
+          const int r0 = 4 * g;   // rows [4g, 4g + 4) of the stage = one patch row
+          unsigned t[4][3];
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const RowDesc ra = h->rows[r0 + 2 * hh], rb = h->rows[r0 + 2 * hh + 1];
+            const uint32_t oa0 = (uint32_t)ra.off0 + xo_s, oa1 = (uint32_t)ra.off1 + xo_s;
+            const uint32_t ob0 = (uint32_t)rb.off0 + xo_s, ob1 = (uint32_t)rb.off1 + xo_s;
+            uint32_t w[12];
+            lds3(oa0 & ~3u, w[0], w[1], w[2]);
+            lds3(oa1 & ~3u, w[3], w[4], w[5]);
+            lds3(ob0 & ~3u, w[6], w[7], w[8]);
+            lds3(ob1 & ~3u, w[9], w[10], w[11]);
+            vert(ra, w[0], w[1], w[2], oa0, w[3], w[4], w[5], oa1, t[2 * hh]);
+            vert(rb, w[6], w[7], w[8], ob0, w[9], w[10], w[11], ob1, t[2 * hh + 1]);
+          }
+          if (!kT4 || kFma) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+              for (int c = 0; c < 3; ++c) { t[i][c] = (t[i][c] + 2u) >> 2; if (STATS) acc32 += t[i][c]; }
+          }
+          char* const q = obase + (size_t)(h->roff[r0] + xoff44) * 2;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            uint32_t P0, P1;
+            if (kFma) {
+              const __nv_bfloat162 a2 = __floats2bfloat162_rn(__fmaf_rn((float)t[0][c], fa[c], fb[c]), __fmaf_rn((float)t[1][c], fa[c], fb[c]));
+              const __nv_bfloat162 b2 = __floats2bfloat162_rn(__fmaf_rn((float)t[2][c], fa[c], fb[c]), __fmaf_rn((float)t[3][c], fa[c], fb[c]));
+              P0 = *reinterpret_cast<const uint32_t*>(&a2);
+              P1 = *reinterpret_cast<const uint32_t*>(&b2);
+            } else {
+              const unsigned short* lb = reinterpret_cast<const unsigned short*>(luth) + c * kLutStride;
+              P0 = (uint32_t)lb[t[0][c]] | ((uint32_t)lb[t[1][c]] << 16);
+              P1 = (uint32_t)lb[t[2][c]] | ((uint32_t)lb[t[3][c]] << 16);
+            }
+            uint32_t w0, w1;
+            tok44_transpose(P0, P1, x & 3, w0, w1);
+            *reinterpret_cast<uint2*>(q + (size_t)c * cs) = make_uint2(w0, w1);
+          }
+          return;
+        }
         if (pair_rows) {
           for (int r = g; r < p.rps; r += 2 * kGroups) {
             const RowDesc ra = h->rows[r], rb = h->rows[r + kGroups];
@@ -1346,6 +1412,7 @@ int make_plan(const lvc_clip_desc* d, bool boxes, bool stats, int sms, int max_s
   smem = (size_t)fixed + (size_t)p.ring_bytes;
   p.merge_rows = env_int("LVC_CLIP_MERGE", 1);
   p.no_fma = env_int("LVC_CLIP_NO_FMA", 0);
+  p.no_tok44 = env_int("LVC_CLIP_NO_TOK44", 0);
   p.producers = std::max(1, std::min(built_producers, env_int("LVC_CLIP_NP", built_producers)));
 
   const int ctas_per_sm = smem_cap > 0 ? 1 : (int)std::max<size_t>(1, std::min<size_t>(2, (size_t)max_smem / (smem + 1024)));
