@@ -363,14 +363,24 @@ idx = [osm.dataset_indices("random", v.shape[0], 5, random.Random(11)) for v in 
 out = {{}}
 for preset in ("resnet_infer", "vivit"):
     out[preset] = hashlib.sha256(ClipBuilder(preset, num_frames=5)(dev, idx).cpu().numpy().tobytes()).hexdigest()
-print("SHA", out["resnet_infer"], out["vivit"])
+# the Video Swin token layout (4 x 4 patches: whole-sector stores through the lane transpose), with and without a checksum
+idx4 = [i[:4] for i in idx]
+cb = ClipBuilder("resnet_infer", num_frames=4, layout="TOKENS", patch=(2, 4, 4), src_order="BGR")
+dev4, idx4 = dev[1:], idx4[1:]   # without the 720p video: 8-row stages, which is where the whole-sector path runs
+st = torch.zeros(len(dev4), dtype=torch.int64, device="cuda")
+tok = cb(dev4, idx4).view(torch.int16).cpu().numpy().tobytes()
+tok_s = cb(dev4, idx4, stats=st).view(torch.int16).cpu().numpy().tobytes()
+assert tok == tok_s
+out["tok44"] = hashlib.sha256(tok + st.cpu().numpy().tobytes()).hexdigest()
+print("SHA", out["resnet_infer"], out["vivit"], out["tok44"])
 """
 
 
 @pytest.mark.parametrize("knobs", [{}, {"LVC_CLIP_NP": "1"}, {"LVC_CLIP_NP": "2"}, {"LVC_CLIP_NP": "4", "LVC_CLIP_RPS": "4"},
                                    {"LVC_CLIP_MERGE": "0"}, {"LVC_CLIP_MERGE": "0", "LVC_CLIP_NP": "1", "LVC_CLIP_RPS": "8"},
                                    {"LVC_CLIP_NP": "4", "LVC_CLIP_RPS": "2", "LVC_CLIP_BAND": "2"},
-                                   {"LVC_CLIP_SMEM_KB": "100", "LVC_CLIP_VBANDS": "14"}])
+                                   {"LVC_CLIP_SMEM_KB": "100", "LVC_CLIP_VBANDS": "14"},
+                                   {"LVC_CLIP_NO_TOK44": "1"}, {"LVC_CLIP_NO_FMA": "1"}, {"LVC_CLIP_NO_FMA": "1", "LVC_CLIP_NO_TOK44": "1"}])
 def test_producer_count_and_stage_knobs_do_not_change_bytes(knobs):
     """The launch geometry (producer warps, rows per stage, band size, ring size) is a performance choice: results are
     identical.  The knobs are honoured only under LVC_PROFILING_KNOBS=1, read once per process -> a subprocess."""
@@ -385,12 +395,22 @@ def test_producer_count_and_stage_knobs_do_not_change_bytes(knobs):
     host, dev = _videos(SHAPES[:6])
     idx = [osm.dataset_indices("random", v.shape[0], T, __import__("random").Random(11)) for v in host]
     base = {p: sha(ClipBuilder(p, num_frames=T)(dev, idx).cpu().numpy()) for p in ("resnet_infer", "vivit")}
+    # Video Swin tokens: the shipped path (lane transpose, affine bf16 form) must equal every fallback, and the planar clip
+    dev4, idx4 = dev[1:], [i[:4] for i in idx][1:]   # without the 720p video: 8-row stages (the whole-sector path)
+    cbt = ClipBuilder("resnet_infer", num_frames=4, layout="TOKENS", patch=(2, 4, 4), src_order="BGR")
+    st = torch.zeros(len(dev4), dtype=torch.int64, device="cuda")
+    tok = cbt(dev4, idx4, stats=st)
+    base["tok44"] = sha(np.frombuffer(tok.view(torch.int16).cpu().numpy().tobytes() + st.cpu().numpy().tobytes(), dtype=np.uint8))
+    planar = ClipBuilder("resnet_infer", num_frames=4, layout="BCTHW", dtype=torch.bfloat16, src_order="BGR")(dev4, idx4)
+    B = len(dev4)   # A[m][k]: m = (b, t/2, y/4, x/4), k = (c, t%2, y%4, x%4)
+    want_tok = planar.view(B, 3, 2, 2, 56, 4, 56, 4).permute(0, 2, 4, 6, 1, 3, 5, 7).reshape(B * 2 * 56 * 56, 96)
+    assert torch.equal(tok.view(torch.int16), want_tok.contiguous().view(torch.int16))
     env = {k: v for k, v in os.environ.items() if not k.startswith("LVC_")}
     env.update(knobs, LVC_PROFILING_KNOBS="1")
     r = subprocess.run([sys.executable, "-c", _KNOB_SCRIPT.format(root=root, specs=SHAPES[:6])], env=env, capture_output=True,
                        text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     got = [ln for ln in r.stdout.splitlines() if ln.startswith("SHA")][-1].split()[1:]
-    assert got == [base["resnet_infer"], base["vivit"]], knobs
+    assert got == [base["resnet_infer"], base["vivit"], base["tok44"]], knobs
     want = op.manual_normalize(op.resize_clip_cv2(host[0][idx[0]]))
     assert sha(want) == sha(ClipBuilder("resnet_infer", num_frames=T)(dev[:1], idx[:1]).cpu().numpy()[0])
