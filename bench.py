@@ -640,6 +640,9 @@ def compact_secondary(detail, ncu):
         r = e["gemm_roofline"]
         c = {"pipeline_ms": round(e["pipeline_ms"], 4), "clip_ms": round(e["clip_kernel_ms"], 4), "gemm_ms": round(e["gemm_ms"], 4),
              "frac": round(r["frac"], 3), "bound": r["bound"], "clips_per_s": round(e["clips_per_s"], 1)}
+        # what the embedding adds to the pipeline once it runs BEHIND the clip kernel (programmatic dependent launch hides its
+        # prologue, the operand A is still in L2): pipeline - clip stage; gemm_ms is the same kernel alone behind an L2 flush
+        c["gemm_in_pipeline_ms"] = round(e["pipeline_ms"] - e["clip_kernel_ms"], 4)
         if "fused_ms" in e:
             c["fused_ms"] = round(e["fused_ms"], 4)
         tp = ncu.get("tensor_pipe", {}).get(name)
