@@ -315,7 +315,8 @@ int lvc_patch_embed_launch_count(const lvc_embed_desc* d);
  * 9.6 MB).  All calls on a device share the one array: it keeps the previous call's contents (nothing needs clearing,
  * the im2col pass overwrites every element the GEMM reads), and two calls that overlap on the GPU (different streams,
  * or graphs replayed concurrently) RACE -- serialise them on one stream.  Other arguments and results are exactly
- * lvc_patch_embed's (same kernels). */
+ * lvc_patch_embed's (same kernels).  The first call on a device resolves the array's address (cudaGetSymbolAddress) and loads
+ * the kernels: make it once outside a stream capture; later calls only enqueue launches. */
 #define LVC_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
 int64_t lvc_patch_embed_static_capacity(void);
 int lvc_patch_embed_static(const lvc_embed_desc* d, const void* x, const void* w_packed_bf16,
