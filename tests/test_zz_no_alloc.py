@@ -111,3 +111,34 @@ def test_static_scratch_allocates_nothing_and_rejects_oversize():
     with pytest.raises(ValueError):
         _lib.check(rc, "lvc_patch_embed_static")
     assert lib.lvc_patch_embed_static(None, None, None, None, None, None, None, None) == _lib.E_INVAL
+
+
+def test_static_scratch_under_stream_capture():
+    """What the entry point is for: inside a CUDA graph capture nothing may allocate.  One warm call outside the capture
+    (resolves the array's address, loads the kernels), then the call is captured and the graph replayed twice on new inputs."""
+    from lvc_b200 import _lib
+
+    lib, d, x, w, bias, ln_w, ln_b, packed, M, st = _setup(_lib.EMBED_SWIN, 1, 4, 224, 224, (2, 4, 4), 128,
+                                                           _lib.LAYOUT_BCTHW, 41)
+    need = lib.lvc_patch_embed_workspace(C.byref(d))
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    want = torch.empty((M, 128), dtype=torch.bfloat16, device="cuda")
+    got = torch.zeros((M, 128), dtype=torch.bfloat16, device="cuda")
+    args = (C.byref(d), x.data_ptr(), packed.data_ptr(), bias.data_ptr(), ln_w.data_ptr(), ln_b.data_ptr(), got.data_ptr())
+    _lib.check(lib.lvc_patch_embed_static(*args, st), "warm")
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            _lib.check(lib.lvc_patch_embed_static(*args, torch.cuda.current_stream().cuda_stream), "captured")
+    torch.cuda.current_stream().wait_stream(side)
+    for seed in (7, 8):
+        x.copy_(_rand(tuple(x.shape), seed).cuda())
+        got.zero_()
+        g.replay()
+        _lib.check(lib.lvc_patch_embed(C.byref(d), x.data_ptr(), packed.data_ptr(), bias.data_ptr(), ln_w.data_ptr(), ln_b.data_ptr(),
+                                       want.data_ptr(), ws.data_ptr(), torch.cuda.current_stream().cuda_stream), "lvc_patch_embed")
+        torch.cuda.synchronize()
+        assert torch.equal(want.view(torch.int16), got.view(torch.int16)), seed
