@@ -914,7 +914,7 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
         const int s = it % p.stages;
-        mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
+        if (p.ready) mb_wait_backoff(&empty[s], ((it / p.stages) & 1u) ^ 1u); else mb_wait(&empty[s], ((it / p.stages) & 1u) ^ 1u);
         if (p.diag & 4) { mb_arrive(&full[s]); continue; }
         if (p.ready) {   // the clip kernel is still writing A: wait for this tile's token rows, then order the TMA read
           const unsigned need = (unsigned)min(BM, p.M - tile * BM) * p.ready_need;   // the last tile may be partial
@@ -941,8 +941,13 @@ lvc_embed_swin_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
         const uint32_t acc = it % NA, acc_phase = (it / NA) & 1u;
         const int s = it % p.stages;
-        mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
-        mb_wait(&full[s], (it / p.stages) & 1u);
+        if (p.ready) {   // beside the clip kernel: tiles arrive at ITS pace, and a bare spin would take issue slots from its warps
+          mb_wait_backoff(&tmem_empty[acc], acc_phase ^ 1u);
+          mb_wait_backoff(&full[s], (it / p.stages) & 1u);
+        } else {
+          mb_wait(&tmem_empty[acc], acc_phase ^ 1u);
+          mb_wait(&full[s], (it / p.stages) & 1u);
+        }
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (uint32_t)N;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
@@ -1451,7 +1456,10 @@ extern "C" int lvc_clip_swin_embed_forward(const lvc_clip_desc* cd, const lvc_vi
   p.ready_need = (unsigned)(g.kt * g.kh);   // per token: all kt * kh row slices (3 channels x kw columns each) are stored
   const int a_tile = BM * g.K * 2, b_all = g.N * g.K * 2;
   const int fixed3 = 1024 + 4 * kSwinGroupsFused * 4096 + b_all + (BM + g.N) * 64 + 512 + 3 * g.N * 4 + 64;
-  p.stages = env_i("LVC_FUSED_EMBED_STAGES", 2);
+  // ONE stage of A: the embedding has slack, the clip kernel does not -- every 24 KB given back to its source-row ring
+  // counts (with two stages the ring no longer holds two 8-row stages of a full 720p frame, the kernel falls back to
+  // 7-row stages and loses the whole-sector token stores: pair 138 us instead of 109)
+  p.stages = env_i("LVC_FUSED_EMBED_STAGES", 1);
   const size_t smem3 = (size_t)fixed3 + (size_t)p.stages * a_tile;
   // what is left of the SM for the clip kernel: the opt-in maximum minus the embedding CTA and the per-CTA reserve
   const int clip_cap = max_smem - (int)smem3 - 2048;

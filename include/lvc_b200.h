@@ -345,8 +345,8 @@ int lvc_embeddings_forward(const lvc_embed_desc* d, const void* x, const void* w
  * lvc_clip_swin_embed_workspace reports (ready is cleared by the call).  clip_desc: LVC_RESAMPLE_CV2, LVC_LAYOUT_TOKENS,
  * LVC_DT_BF16, tok_* = the embedding's patch; embed_desc: LVC_EMBED_SWIN, x_layout LVC_LAYOUT_TOKENS, 224 x 224.
  * Results are bit-identical to the two separate calls.  Other arguments as lvc_clip_forward / lvc_patch_embed.
- * EXPERIMENTAL, NOT THE DEFAULT PATH: on BASELINE config 4 the pair measures 138 us against 100 us for the two launches
- * (sharing the SM slows the clip stage to 113 us and the embedding ends 14 us after it);
+ * EXPERIMENTAL, NOT THE DEFAULT PATH: on BASELINE config 4 the pair measures 109 us against 100 us for the two launches
+ * (the clip stage runs on a smaller ring, 80 instead of 68 us, and the embedding ends 16 us after it);
  * pipeline.ClipEmbedPipeline and bench.py keep the two launches.  Correctness never depends on co-residency: the clip
  * kernel does not wait for the embedding kernel, which simply runs afterwards when the two do not fit on an SM together. */
 int lvc_clip_swin_embed_workspace(const lvc_embed_desc* embed_desc, int64_t* tokens_bytes, int64_t* ready_bytes);
