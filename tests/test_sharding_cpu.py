@@ -20,7 +20,9 @@ def _worker(rank, world, port, q):
     table = sharding.plan_epoch(n_frames, "random_window", 32)
     checksum = int(table[mine].astype(np.int64).sum())
     stats = sharding.gather_stats(len(mine), 0.5 + rank, checksum)
-    q.put((rank, mine, table[mine].tolist(), stats))
+    # shards for the next pass sized by what every rank measured (seconds per clip), identical on every rank
+    counts = sharding.weighted_counts(128, sharding.ingest_weights([sec / n for n, sec, _ in stats]))
+    q.put((rank, mine, table[mine].tolist(), stats, counts))
     dist.destroy_process_group()
 
 
@@ -41,10 +43,12 @@ def test_world_size_2_gloo():
     # the sharded index rows are those of ONE sequential reference stream (seed 42), whatever the world size
     rng = random.Random(42)
     want = [osm.dataset_indices("random_window", n, 32, rng) for n in n_frames]
-    for rank, mine, rows, stats in res:
+    for rank, mine, rows, stats, counts in res:
         assert rows == [want[v] for v in mine]
         assert len(stats) == world and [s[0] for s in stats] == [4.0, 3.0]
         assert stats == res[0][3]  # every rank holds the same gathered report
+        # rank 0: 0.5 s / 4 clips, rank 1: 1.5 s / 3 clips -> rates 8 : 2 clips/s, clamped to 2 x the median (5): 8 : 2.5
+        assert counts == res[0][4] == [97, 31] and sum(counts) == 128
     assert sum(s[2] for s in res[0][3]) == float(sum(sum(w) for w in want))
 
 
