@@ -75,6 +75,24 @@ def test_plan_is_byte_granular_and_bounded():
         clip_plan(_desc(max_width=40000), False, _lib.B200_SMS, _lib.B200_MAX_SMEM)
 
 
+def test_plan_keeps_eight_row_stages_for_swin_token_batches():
+    """The whole-sector token stores of the Video Swin layout (4 x 4 patches: one patch row per consumer group and stage)
+    need 8-row stages: ROI batches get them up to 1080p sources (two stages of the widest rows must fit the ring), and
+    the bands are whole patch rows."""
+    from lvc_b200 import _lib
+    from lvc_b200.clips import clip_plan
+
+    for width in (320, 640, 1280, 1920):
+        d = _lib.ClipDesc(_lib.RESAMPLE_CV2, _lib.LAYOUT_TOKENS, _lib.DT_BF16, 224, 8, 32, width, 2, 4, 4,
+                          (C.c_float * 3)(0, 0, 0), (C.c_float * 3)(1, 1, 1), 0, 0)
+        p = clip_plan(d, True, _lib.B200_SMS, _lib.B200_MAX_SMEM)
+        assert p["rows_per_stage"] == 8 and p["rows_per_band"] % 4 == 0 and p["stages_of_widest"] >= 2, (width, p)
+    # full-frame 720p batches (no boxes) prefer the finely sliced ring: 4-row stages (HBM-bound there, the stores do not matter)
+    d = _lib.ClipDesc(_lib.RESAMPLE_CV2, _lib.LAYOUT_TOKENS, _lib.DT_BF16, 224, 8, 32, 1280, 2, 4, 4,
+                      (C.c_float * 3)(0, 0, 0), (C.c_float * 3)(1, 1, 1), 0, 0)
+    assert clip_plan(d, False, _lib.B200_SMS, _lib.B200_MAX_SMEM)["rows_per_stage"] == 4
+
+
 _KNOB_PROBE = """
 import ctypes as C, json, sys
 sys.path.insert(0, {root!r})
