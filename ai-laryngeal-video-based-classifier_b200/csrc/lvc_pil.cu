@@ -26,6 +26,10 @@ constexpr int KT = 24;        // most taps per output sample: ceil(scale)*2+1 <=
 constexpr int kMaxThreads = 512;
 constexpr int kCH = 32;       // source rows per staged block: one row per lane in the horizontal pass
 constexpr int IP = S + 1;     // words per row of the intermediate ring (odd: lane = row writes hit 32 banks)
+#ifndef LVC_PIL_WORD_LOADS_FROM
+#define LVC_PIL_WORD_LOADS_FROM 6
+#endif
+constexpr int kPilWordLoadsFrom = LVC_PIL_WORD_LOADS_FROM;   // tap count from which the horizontal pass reads words instead of bytes
 
 struct PilParams {
   const lvc_video* videos;
@@ -278,6 +282,35 @@ __global__ void __launch_bounds__(kMaxThreads, (NT <= 9 ? 2 : 1)) lvc_pil_kernel
         int rslot = ring0 + lane;
         if (rslot >= p.ir) rslot -= p.ir;   // kCH <= ir: one wrap at most
         uint32_t* irow = inter + (size_t)rslot * IP;
+        // Filters of six taps and more (down-scales from 2.5x: 720p, 1080p): the window's 3 * NT bytes are read as aligned 32-bit
+        // words + funnel shift and split with PRMT -- the kernel is bound by the LSU / MIO queue (ncu at 1080p: mio_throttle 1.7
+        // stall cycles per issue, LSU pipe 62 % with one LDS.U8 per sample) while the ALU pipe idles at 28 %.  Measured, 8 x 32
+        // frames: 1080p -> 256 (NT = 9) 0.606 -> 0.564 ms, 720p -> 256 (NT = 6) 0.352 -> 0.341, 720p -> 224 (NT = 7) 0.418 -> 0.400;
+        // narrower filters measure the same either way and keep the byte loads.
+        const uint32_t rowp_s = s32(rowp);
+        if constexpr (NT >= kPilWordLoadsFrom)
+        for (int x = xa + warp; x < xa + xseg; x += kWarps) {
+          const uint32_t boff = rowp_s + (uint32_t)((hmin[x] - c0) * 3);
+          const uint32_t wa = boff & ~3u, sh = boff << 3;   // the funnel shift wraps at 32: (boff & 3) * 8
+          const int* k = hk + x;
+          int a[3] = {1 << 21, 1 << 21, 1 << 21};
+          uint32_t cur, nxt;
+          asm volatile("ld.shared.u32 %0, [%1];" : "=r"(cur) : "r"(wa));
+#pragma unroll
+          for (int j = 0; j < (3 * NT + 3) / 4; ++j) {
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(nxt) : "r"(wa + 4u * (uint32_t)(j + 1)));
+            const uint32_t sw = __funnelshift_r(cur, nxt, sh);   // bytes 4j .. 4j + 3 of the window
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int b = 4 * j + q;   // byte b of the window = channel b % 3 of tap b / 3
+              if (b < 3 * NT) a[b % 3] += (int)__byte_perm(sw, 0u, 0x4440u + q) * k[(b / 3) * S];
+            }
+            cur = nxt;
+          }
+          // non-negative weights summing to 2^22 (+- n/2): the result is already inside [0, 255]
+          irow[x] = (uint32_t)(a[0] >> 22) | ((uint32_t)(a[1] >> 22) << 8) | ((uint32_t)(a[2] >> 22) << 16);
+        }
+        else
         for (int x = xa + warp; x < xa + xseg; x += kWarps) {
           const uint8_t* src = rowp + (hmin[x] - c0) * 3;
           const int* k = hk + x;
